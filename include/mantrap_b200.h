@@ -1,0 +1,149 @@
+/*
+ * mantrap_b200 -- C ABI of the B200-native planning hot path of simon-schaefer/mantrap.
+ *
+ * This is the drop-in boundary: plain C, raw DEVICE pointers + sizes + a cudaStream_t passed as void*, an int
+ * return code (0 = ok, otherwise a cudaError_t or a negative MTB_ERR_* code). No torch types, no host
+ * synchronisation inside, the caller owns all memory. One call evaluates S scenes x C candidate control
+ * sequences. The reference has no FFI for this path (it is pure Python); each entry point cites the reference
+ * Python interface whose work it replaces (paths relative to the reference repository root):
+ *
+ *   mtb_evaluate            mantrap/solver/base/trajopt.py:368-434   TrajOptSolver.objective / constraints
+ *                           mantrap/solver/ipopt.py:118-135          IPOPTSolver.gradient
+ *                           mantrap/solver/base/search.py:98-103     SearchIntermediate.evaluate
+ *                           mantrap/environment/base/graph_based.py:362-381  compute_distributions (+ _wo_ego)
+ *                           mantrap/agents/base/linear.py:68-105     LinearDTAgent.unroll_trajectory
+ *   mtb_constraint_jacobian mantrap/solver/ipopt.py:140-154          IPOPTSolver.jacobian (MinDistance rows;
+ *                           mantrap/modules/base/optimization_module.py:258-307, :428-434)
+ *   mtb_argmin              mantrap/solver/baselines/random_search.py:28-35  keep-best-feasible candidate
+ *
+ * Layouts are row-major float32, exactly the flattening the reference uses: controls z = (t, xy)
+ * (trajopt.py:439-444), states (px, py, vx, vy), means mus = (mu_px, mu_py, mu_vx, mu_vy) per (ado, t).
+ */
+#ifndef MANTRAP_B200_H
+#define MANTRAP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MTB_ABI_VERSION 1
+
+/* environment kinds: mantrap/environment/social_forces.py, simplified/potential_field.py, simplified/kalman.py */
+#define MTB_ENV_SOCIAL_FORCES 0
+#define MTB_ENV_POTENTIAL_FIELD 1
+#define MTB_ENV_KALMAN 2
+/* ego kinds: mantrap/agents/integrator_double.py, integrator_single.py; NONE = rollout without ego
+ * (ParticleEnvironment._compute_distributions_wo_ego, particle.py:185-198) */
+#define MTB_EGO_DOUBLE_INTEGRATOR 0
+#define MTB_EGO_SINGLE_INTEGRATOR 1
+#define MTB_EGO_NONE 2
+
+#define MTB_MAX_ADOS 64
+#define MTB_MAX_HORIZON 64
+
+#define MTB_ERR_BAD_ARGUMENT (-1)
+#define MTB_ERR_TOO_LARGE (-2)
+#define MTB_ERR_WORKSPACE (-3)
+
+/* Scene batch + candidate controls. All pointers are device pointers. */
+typedef struct mtb_problem {
+    int32_t num_scenes;     /* S */
+    int32_t num_candidates; /* C candidates per scene (all share the scene's particle parameters) */
+    int32_t t_horizon;      /* T = t_planning = number of controls; ego trajectory has T+1 rows, means have T */
+    int32_t num_ados;       /* N <= MTB_MAX_ADOS */
+    int32_t num_particles;  /* P particles per ado (mantrap/constants.py:45) */
+    int32_t env_kind;       /* MTB_ENV_* */
+    int32_t ego_kind;       /* MTB_EGO_* */
+    float dt;               /* environment time step (constants.py:39) */
+    float sf_tau;           /* constants.py:50 */
+    float ped_speed_max;    /* constants.py:28 (force clamp + particle control clamp) */
+    float sf_goal_radius;   /* constants.py:53 */
+    float sf_interaction_radius; /* constants.py:54 */
+    float pf_theta_max;     /* constants.py:57, radians */
+    float particle_noise;   /* constants.py:46 */
+    float var_initial;      /* constants.py:43 */
+    float kalman_noise;     /* constants.py:48 */
+    const float* ego0;      /* [S,4] ego state at t0 (unused for MTB_EGO_NONE) */
+    const float* ado0;      /* [S,N,4] ado states at t0 */
+    const float* ado_goal;  /* [S,N,2] social-forces goals */
+    const float* v0;        /* [S,N,P] sampled potential amplitude (particle.py:59-61) */
+    const float* sigma;     /* [S,N,P] sampled potential range (SF only) */
+    const float* weight;    /* [S,N,P] cdf weights, already normalised over the ado axis (particle.py:62,79,141) */
+    const float* noise;     /* [S,T-1,N,P,2] U(0,1) velocity noise (particle.py:165) or NULL = no noise */
+    const float* controls;  /* [S,C,T,2] (unused for MTB_EGO_NONE) */
+} mtb_problem;
+
+/* Objective / constraint modules (mantrap/modules). A weight of 0 switches a module off. */
+typedef struct mtb_modules {
+    float w_goal;           /* GoalNormModule: weight / normaliser (goal_norm.py:37,116-118) */
+    float w_acc;            /* InteractionAccelerationModule: weight / max value (acc_interact.py:29,95) */
+    float w_vel;            /* InteractionVelocityModule */
+    float w_pos;            /* InteractionPositionModule */
+    float max_acc;          /* clamp_max of the raw cost, constants.py:103 */
+    float max_vel;          /* constants.py:102 */
+    float max_pos;          /* constants.py:101 */
+    const float* ego_goal;  /* [S,2] */
+    const float* mus_wo;    /* [S,N,T,4] means of the rollout WITHOUT ego (module __init__, acc_interact.py:33-34) */
+    const uint8_t* ado_mask;/* [S,N] 1 = ado id enters the cost (attention filter), NULL = all */
+    int32_t con_control;    /* ControlLimitModule rows (control_limits.py:23-36) */
+    int32_t con_speed;      /* SpeedLimitModule rows (speed_limits.py:26-37) */
+    int32_t con_min_distance; /* MinDistance rows ||ego_p(t) - mu_p[k,t]|| (north star; constants.py:107) */
+    float u_max;            /* normaliser + upper bound of control rows */
+    float v_max;            /* normaliser + symmetric bound of speed rows */
+    float min_distance;     /* lower bound of min-distance rows (not normalised) */
+    float violation_eps;    /* constants.py:108 */
+} mtb_modules;
+
+/* Outputs; every pointer may be NULL (= not wanted). */
+typedef struct mtb_outputs {
+    float* obj;        /* [S,C,4] weighted+normalised goal, acc, vel, pos objectives (what module.objective returns) */
+    float* obj_raw;    /* [S,C,4] raw, un-clamped costs */
+    float* total;      /* [S,C] sum of obj */
+    float* grad;       /* [S,C,T,2] gradient of total w.r.t. controls; NULL = forward only */
+    float* cons;       /* [S,C,R] normalised constraint rows: control (2T or T) | speed 2(T+1) | min-distance N*T */
+    float* violation;  /* [S,C] summed constraint violation (optimization_module.py:512-533) */
+    float* ego_traj;   /* [S,C,T+1,4] */
+    float* mus;        /* [S,C,N,T,4] */
+    float* sigmas;     /* [S,C,N,T,2] velocity "scale" (= variance, reference quirk) */
+    unsigned long long* stats; /* [4] optional counters: evaluated ado pairs, ego pairs, saturated evals, poisoned */
+} mtb_outputs;
+
+typedef struct mtb_launch_info {
+    int32_t grid, block, evals_per_block, group_size;
+    int32_t smem_bytes, tape_in_smem;
+    int32_t num_items, blocks_per_sm;
+} mtb_launch_info;
+
+int mtb_abi_version(void);
+const char* mtb_error_string(int code);
+
+/* number of constraint rows R for the enabled constraint modules */
+int mtb_num_constraint_rows(const mtb_problem* problem, const mtb_modules* modules);
+
+/* bytes of device scratch mtb_evaluate needs (0 when everything fits in shared memory) */
+size_t mtb_workspace_bytes(const mtb_problem* problem, int want_grad);
+
+/* forward rollout (+ objectives, constraints) and, when out->grad != NULL, the adjoint pass in the same kernel */
+int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const mtb_outputs* out,
+                 void* workspace, size_t workspace_bytes, void* stream);
+
+/* launch geometry mtb_evaluate would use (for benchmarks / docs) */
+int mtb_query_launch(const mtb_problem* problem, int want_grad, mtb_launch_info* info);
+
+/* dense Jacobian of the min-distance rows w.r.t. the controls: jac[S,C,N*T,2T] (forward-mode tangents) */
+int mtb_constraint_jacobian(const mtb_problem* problem, const mtb_modules* modules, float* cons /*[S,C,N*T]*/,
+                            float* jac, void* workspace, size_t workspace_bytes, void* stream);
+size_t mtb_jacobian_workspace_bytes(const mtb_problem* problem);
+
+/* per scene: index / value / controls of the best candidate with violation < feas_tol (index -1 if none) */
+int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, int32_t num_candidates,
+               float feas_tol, const float* controls, int32_t t_horizon, int32_t* best_idx, float* best_val,
+               float* best_controls, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MANTRAP_B200_H */

@@ -1,0 +1,960 @@
+// mantrap_b200: fused rollout + objective + adjoint kernel for mantrap's particle environments (sm_100a).
+//
+// One thread per particle (ado m, particle i); a "group" of N*P threads (padded to a power of two <= 32 or to a
+// multiple of 32) owns one (scene, candidate) evaluation and keeps the ego trajectory, the collapsed ado means
+// of every time step, the per-step particle tape and the adjoint accumulators in shared memory. A thread block
+// holds E groups (E candidates of the same scene) and the grid is persistent: blocks loop over work items.
+//
+//   forward   t = 0..T-2 : every particle evaluates its step model against mus[:, t] and the ego state at t,
+//                          particles of an ado are collapsed to mean / variance      (particle.py:151-175)
+//   epilogue             : goal / interaction objectives, constraint rows, violation  (modules/*.py)
+//   backward  t = T-2..0 : hand-derived adjoint of the step model, seeds from the objective, ego adjoint is
+//                          folded through the integrator dynamics into the control gradient; no autograd graph.
+//
+// The same source compiles for the host emulation used by the CPU tests (tests/host_emul, -DMTB_HOST_EMUL).
+#ifdef MTB_HOST_EMUL
+#include "cuda_shim.h"
+#else
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#define MTB_SHARED_FLOAT4(name) extern __shared__ float4 name[]
+#define MTB_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
+#endif
+
+#include <cfloat>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+
+#include "mantrap_b200.h"
+#include "mtb_math.cuh"
+
+namespace mtb {
+
+constexpr int kMaxThreads = 1024;
+constexpr int kDefaultBlock = 256;
+
+struct KParams {
+    mtb_problem pb;
+    mtb_modules md;
+    mtb_outputs out;
+    int T, N, P, G, GP, E, MW;
+    int num_items;
+    long long num_evals;
+    int has_ego, want_grad, want_env_adjoint, use_tape;
+    float pair_cut2;                 // largest d^2 with sqrtf(d^2) <= interaction radius
+    // shared-memory layout (float units, per evaluation) -------------------------------------------------
+    int off_ctl, off_ego, off_egobar, off_mus, off_abar, off_q, off_misc, off_tape, off_mask;
+    int per_eval_f, red_f;
+    int tape_in_smem;
+    float4* tape_global;             // [grid][T-1][block]   when the tape does not fit in shared memory
+    unsigned* mask_global;           // [grid][T-1][block][MW]
+    int rows_control, rows_speed, rows_mind, R;
+};
+
+// misc slots (per evaluation)
+enum { kCoefAcc = 0, kCoefVel = 1, kCoefPos = 2, kNeedAdjoint = 3, kMiscFloats = 8 };
+
+struct Red4 {
+    float a, b, c, d;
+};
+
+// Sum over the GP threads of a group; result valid in every thread of the group. For GP > 32 this contains two
+// __syncthreads(), so it must be reached by all threads of the block (GP is uniform across the block).
+MTB_DEV Red4 group_reduce4(Red4 v, int GP, int e, float* red) {
+    if (GP <= 32) {
+        for (int off = GP >> 1; off > 0; off >>= 1) {
+            v.a += __shfl_xor_sync(0xffffffffu, v.a, off);
+            v.b += __shfl_xor_sync(0xffffffffu, v.b, off);
+            v.c += __shfl_xor_sync(0xffffffffu, v.c, off);
+            v.d += __shfl_xor_sync(0xffffffffu, v.d, off);
+        }
+        return v;
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        v.a += __shfl_xor_sync(0xffffffffu, v.a, off);
+        v.b += __shfl_xor_sync(0xffffffffu, v.b, off);
+        v.c += __shfl_xor_sync(0xffffffffu, v.c, off);
+        v.d += __shfl_xor_sync(0xffffffffu, v.d, off);
+    }
+    const int warp = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) {
+        red[warp * 4 + 0] = v.a;
+        red[warp * 4 + 1] = v.b;
+        red[warp * 4 + 2] = v.c;
+        red[warp * 4 + 3] = v.d;
+    }
+    __syncthreads();
+    const int w0 = (e * GP) >> 5, nw = GP >> 5;
+    Red4 r = {0.f, 0.f, 0.f, 0.f};
+    for (int w = 0; w < nw; ++w) {
+        r.a += red[(w0 + w) * 4 + 0];
+        r.b += red[(w0 + w) * 4 + 1];
+        r.c += red[(w0 + w) * 4 + 2];
+        r.d += red[(w0 + w) * 4 + 3];
+    }
+    __syncthreads();
+    return r;
+}
+
+MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py:446)
+    if (is_nan(x)) return 0.f;
+    if (x > FLT_MAX) return FLT_MAX;
+    if (x < -FLT_MAX) return -FLT_MAX;
+    return x;
+}
+
+MTB_DEV float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+
+// Adjoint seed of the interaction objectives on mus[k, level] (level >= 1): (d/d mu_p, d/d mu_v).
+MTB_DEV float4 objective_seed(const KParams& prm, const float* misc, const float4* mus, const float* wo_scene,
+                              int k, int level, bool in_cost) {
+    float4 sd = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!in_cost) return sd;
+    const int T = prm.T, N = prm.N;
+    const float cacc = misc[kCoefAcc], cvel = misc[kCoefVel], cpos = misc[kCoefPos];
+    const float4 cur = mus[level * N + k];
+    const float4 wcur = ld4(wo_scene + (k * T + level) * 4);
+    if (cacc != 0.f) {
+        const float4 prev = mus[(level - 1) * N + k];
+        const float4 wprev = ld4(wo_scene + (k * T + level - 1) * 4);
+        float dx = ((cur.z - prev.z) - (wcur.z - wprev.z));
+        float dy = ((cur.w - prev.w) - (wcur.w - wprev.w));
+        float nn = sqrtf(dx * dx + dy * dy);
+        if (nn > 0.f) { sd.z += cacc * dx / nn; sd.w += cacc * dy / nn; }
+        if (level <= T - 2) {
+            const float4 nxt = mus[(level + 1) * N + k];
+            const float4 wnxt = ld4(wo_scene + (k * T + level + 1) * 4);
+            dx = ((nxt.z - cur.z) - (wnxt.z - wcur.z));
+            dy = ((nxt.w - cur.w) - (wnxt.w - wcur.w));
+            nn = sqrtf(dx * dx + dy * dy);
+            if (nn > 0.f) { sd.z -= cacc * dx / nn; sd.w -= cacc * dy / nn; }
+        }
+    }
+    if (cvel != 0.f) {
+        const float dx = cur.z - wcur.z, dy = cur.w - wcur.w;
+        const float nn = sqrtf(dx * dx + dy * dy);
+        if (nn > 0.f) { sd.z += cvel * dx / nn; sd.w += cvel * dy / nn; }
+    }
+    if (cpos != 0.f) {   // positions vs. ego-free VELOCITIES (pos_interact.py:34-36), |.| per component
+        sd.x += cpos * sgn(cur.x - wcur.z);
+        sd.y += cpos * sgn(cur.y - wcur.w);
+    }
+    return sd;
+}
+
+template <int ENV, bool GRAD, int MAXT>
+__global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
+    MTB_SHARED_FLOAT4(smem4);
+    float* smem = reinterpret_cast<float*>(smem4);
+
+    const int T = prm.T, N = prm.N, P = prm.P, G = prm.G, GP = prm.GP, MW = prm.MW;
+    const int tid = threadIdx.x;
+    const int e = tid / GP;
+    const int g = tid - e * GP;
+    const bool active = g < G;
+    const int m = active ? g / P : 0;
+    const int i = g - m * P;
+    const bool has_ego = prm.has_ego != 0;
+    const float dt = prm.pb.dt;
+    const float u_ped = prm.pb.ped_speed_max;
+    const float inv_tau = 1.0f / prm.pb.sf_tau;
+
+    float* red = smem;                                            // [block/32][4]
+    float* sm = smem + prm.red_f + e * prm.per_eval_f;
+    float* ctl = sm + prm.off_ctl;                                // [2T] controls, later the gradient staging
+    float4* ego = reinterpret_cast<float4*>(sm + prm.off_ego);    // [T+1]
+    float4* egobar = reinterpret_cast<float4*>(sm + prm.off_egobar);  // [T+1] adjoint from the environment
+    float4* mus = reinterpret_cast<float4*>(sm + prm.off_mus);    // [T][N]
+    float4* abar = reinterpret_cast<float4*>(sm + prm.off_abar);  // [3][N] adjoint of the means (rotating)
+    float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);     // [GP]
+    float* misc = sm + prm.off_misc;
+
+    float4* tape;            // [(T-1)][stride] (p.x, p.y, u.x, u.y) of every particle before its step
+    unsigned* maskbuf;       // [(T-1)][stride][MW] interaction bit masks
+    int tape_stride, tape_idx;
+    if (prm.tape_in_smem) {
+        tape = reinterpret_cast<float4*>(sm + prm.off_tape);
+        maskbuf = reinterpret_cast<unsigned*>(sm + prm.off_mask);
+        tape_stride = GP;
+        tape_idx = g;
+    } else {
+        tape = prm.tape_global + (size_t)blockIdx.x * (size_t)(T - 1) * blockDim.x;
+        maskbuf = prm.mask_global + (size_t)blockIdx.x * (size_t)(T - 1) * blockDim.x * MW;
+        tape_stride = blockDim.x;
+        tape_idx = tid;
+    }
+
+    unsigned long long n_pairs = 0, n_ego = 0;
+
+    for (int item = blockIdx.x; item < prm.num_items; item += gridDim.x) {
+        // work item = E consecutive evaluations of the flattened (scene, candidate) index
+        const long long ev_raw = (long long)item * prm.E + e;
+        const bool eval_valid = ev_raw < prm.num_evals;
+        const size_t ev = (size_t)(eval_valid ? ev_raw : prm.num_evals - 1);
+        const int s = (int)(ev / (size_t)prm.pb.num_candidates);
+
+        // ------------------------------------------------------------------ controls -> ego trajectory
+        if (has_ego) {
+            const float* u_g = prm.pb.controls + ev * (size_t)(2 * T);
+            for (int idx = g; idx < 2 * T; idx += GP) ctl[idx] = __ldg(u_g + idx);
+        }
+        const float* ado0_s = prm.pb.ado0 + (size_t)s * N * 4;
+        for (int k = g; k < N; k += GP) mus[k] = ld4(ado0_s + k * 4);
+        if (GRAD) {
+            for (int idx = g; idx < 3 * N; idx += GP) abar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int idx = g; idx <= T; idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncthreads();
+        if (has_ego && g == 0) {
+            const float4 x0 = ld4(prm.pb.ego0 + (size_t)s * 4);
+            float px = x0.x, py = x0.y, vx = x0.z, vy = x0.w;
+            ego[0] = x0;
+            if (prm.pb.ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) {   // integrator_double.py:19-26
+                for (int t = 0; t < T; ++t) {
+                    px = fmaf(dt, vx, px);
+                    py = fmaf(dt, vy, py);
+                    vx = fmaf(dt, ctl[2 * t], vx);
+                    vy = fmaf(dt, ctl[2 * t + 1], vy);
+                    ego[t + 1] = make_float4(px, py, vx, vy);
+                }
+            } else {                                              // integrator_single.py:19-26
+                for (int t = 0; t < T; ++t) {
+                    vx = ctl[2 * t];
+                    vy = ctl[2 * t + 1];
+                    px = fmaf(dt, vx, px);
+                    py = fmaf(dt, vy, py);
+                    ego[t + 1] = make_float4(px, py, vx, vy);
+                }
+            }
+        }
+
+        // ------------------------------------------------------------------ particle state + parameters
+        V2 p = v2(0.f, 0.f), v = v2(0.f, 0.f), goal = v2(0.f, 0.f);
+        float pv0 = 1.f, psig = 1.f, pw = 0.f;
+        V2 v_init = v2(0.f, 0.f);
+        if (active) {
+            const float4 a0 = ld4(ado0_s + m * 4);
+            p = v2(a0.x, a0.y);
+            v = v2(a0.z, a0.w);
+            v_init = v;
+            if (ENV != MTB_ENV_KALMAN) {
+                const size_t pi = ((size_t)s * N + m) * P + i;
+                pv0 = __ldg(prm.pb.v0 + pi);
+                pw = __ldg(prm.pb.weight + pi);
+                if (ENV == MTB_ENV_SOCIAL_FORCES) {
+                    psig = __ldg(prm.pb.sigma + pi);
+                    goal = v2(__ldg(prm.pb.ado_goal + ((size_t)s * N + m) * 2), __ldg(prm.pb.ado_goal + ((size_t)s * N + m) * 2 + 1));
+                }
+            } else {
+                pw = 1.f;
+            }
+        }
+        float* sig_out = (prm.out.sigmas != nullptr && eval_valid) ? prm.out.sigmas + ev * (size_t)N * T * 2 : nullptr;
+        if (sig_out != nullptr && active && i == 0) {
+            sig_out[(m * T) * 2 + 0] = prm.pb.var_initial;
+            sig_out[(m * T) * 2 + 1] = prm.pb.var_initial;
+        }
+        __syncthreads();
+
+        // ================================================================== forward rollout
+        for (int t = 0; t < T - 1; ++t) {
+            const float4* mus_t = mus + t * N;
+            if (active) {
+                V2 u;
+                if (ENV == MTB_ENV_SOCIAL_FORCES) {
+                    const V2 fgoal = goal_force(p, v, goal, inv_tau, prm.pb.sf_goal_radius);
+                    unsigned mk[2] = {0u, 0u};
+                    for (int k = 0; k < N; ++k) {
+                        const float4 mu = mus_t[k];
+                        const float dx = p.x - mu.x, dy = p.y - mu.y;
+                        const float d2 = dx * dx + dy * dy;
+                        if (k != m && d2 <= prm.pair_cut2) mk[k >> 5] |= (1u << (k & 31));
+                    }
+                    V2 frep = v2(0.f, 0.f);
+                    for (int wd = 0; wd < MW; ++wd) {
+                        unsigned bits = mk[wd];
+                        if (GRAD && prm.use_tape) maskbuf[((size_t)t * tape_stride + tape_idx) * MW + wd] = bits;
+                        while (bits) {
+                            const int k = (wd << 5) + __ffs((int)bits) - 1;
+                            bits &= bits - 1;
+                            const float4 mu = mus_t[k];
+                            const RepulsionFwd o = repulsion_forward(p - v2(mu.x, mu.y), v - v2(mu.z, mu.w), pv0, psig, dt, u_ped);
+                            frep = frep - o.force;
+                            ++n_pairs;
+                        }
+                    }
+                    u = fgoal + frep;
+                    if (has_ego) {
+                        const float4 eg = ego[t];
+                        const RepulsionFwd o = repulsion_forward(p - v2(eg.x, eg.y), v - v2(eg.z, eg.w), pv0, psig, dt, u_ped);
+                        u = u - o.force;
+                        ++n_ego;
+                    }
+                } else if (ENV == MTB_ENV_POTENTIAL_FIELD) {
+                    u = v;
+                    if (has_ego) {
+                        const float4 eg = ego[t];
+                        const V2 delta = v2(eg.x - p.x, eg.y - p.y);
+                        if (pf_gate(v, delta, prm.pb.pf_theta_max)) u = u + pf_impact(delta, pv0);
+                        ++n_ego;
+                    }
+                } else {
+                    u = v;                                        // Kalman: constant velocity (kalman.py:80)
+                }
+                if (GRAD && prm.use_tape) tape[(size_t)t * tape_stride + tape_idx] = make_float4(p.x, p.y, u.x, u.y);
+                const V2 up = (ENV == MTB_ENV_KALMAN) ? u : feasible(u, u_ped);
+                v = up;
+                p = v2(fmaf(dt, up.x, p.x), fmaf(dt, up.y, p.y));
+                V2 vel = v;
+                if (ENV != MTB_ENV_KALMAN && prm.pb.noise != nullptr) {
+                    const float* nz = prm.pb.noise + ((((size_t)s * (T - 1) + t) * N + m) * P + i) * 2;
+                    vel.x = fmaf(__ldg(nz), prm.pb.particle_noise, vel.x);
+                    vel.y = fmaf(__ldg(nz + 1), prm.pb.particle_noise, vel.y);
+                }
+                qbuf[g] = make_float2(vel.x * pw, vel.y * pw);
+            }
+            __syncthreads();
+            if (active && i == 0) {                               // collapse the P particles of ado m (particle.py:171-175)
+                float sx = 0.f, sy = 0.f;
+                for (int j = 0; j < P; ++j) { sx += qbuf[g + j].x; sy += qbuf[g + j].y; }
+                const float mx = sx / (float)P, my = sy / (float)P;
+                const float4 cur = mus_t[m];
+                mus[(t + 1) * N + m] = make_float4(fmaf(cur.z, dt, cur.x), fmaf(cur.w, dt, cur.y), mx, my);
+                if (sig_out != nullptr) {
+                    float vx = prm.pb.kalman_noise, vy = prm.pb.kalman_noise;
+                    if (ENV != MTB_ENV_KALMAN) {
+                        vx = 0.f; vy = 0.f;
+                        for (int j = 0; j < P; ++j) {
+                            const float ex = qbuf[g + j].x - mx, ey = qbuf[g + j].y - my;
+                            vx = fmaf(ex, ex, vx);
+                            vy = fmaf(ey, ey, vy);
+                        }
+                        vx /= (float)(P - 1);
+                        vy /= (float)(P - 1);
+                    }
+                    sig_out[(m * T + t + 1) * 2 + 0] = vx;
+                    sig_out[(m * T + t + 1) * 2 + 1] = vy;
+                }
+            }
+            __syncthreads();
+        }
+
+        // ================================================================== objectives + constraints
+        const float* wo_scene = (prm.md.mus_wo != nullptr) ? prm.md.mus_wo + (size_t)s * N * T * 4 : nullptr;
+        const uint8_t* amask = (prm.md.ado_mask != nullptr) ? prm.md.ado_mask + (size_t)s * N : nullptr;
+        const bool want_interact = wo_scene != nullptr && (prm.md.w_acc != 0.f || prm.md.w_vel != 0.f || prm.md.w_pos != 0.f);
+        Red4 part = {0.f, 0.f, 0.f, 0.f};                         // goal, acc, vel, pos partial sums
+        if (has_ego && prm.md.w_goal != 0.f) {
+            const float gx = __ldg(prm.md.ego_goal + (size_t)s * 2), gy = __ldg(prm.md.ego_goal + (size_t)s * 2 + 1);
+            for (int t = g; t <= T; t += GP) {
+                const float4 x = ego[t];
+                part.a += (x.x - gx) * (x.x - gx) + (x.y - gy) * (x.y - gy);
+            }
+        }
+        if (want_interact) {
+            for (int idx = g; idx < N * T; idx += GP) {
+                const int k = idx / T, t = idx - k * T;
+                if (amask != nullptr && amask[k] == 0) continue;
+                const float4 cur = mus[t * N + k];
+                const float4 wcur = ld4(wo_scene + (k * T + t) * 4);
+                if (prm.md.w_acc != 0.f && t < T - 1) {
+                    const float4 nxt = mus[(t + 1) * N + k];
+                    const float4 wnxt = ld4(wo_scene + (k * T + t + 1) * 4);
+                    const float ax = (nxt.z - cur.z) / dt - (wnxt.z - wcur.z) / dt;
+                    const float ay = (nxt.w - cur.w) / dt - (wnxt.w - wcur.w) / dt;
+                    part.b += sqrtf(ax * ax + ay * ay);
+                }
+                if (prm.md.w_vel != 0.f) {
+                    const float dx = cur.z - wcur.z, dy = cur.w - wcur.w;
+                    part.c += sqrtf(dx * dx + dy * dy);
+                }
+                if (prm.md.w_pos != 0.f) part.d += fabsf(cur.x - wcur.z) + fabsf(cur.y - wcur.w);
+            }
+        }
+        part = group_reduce4(part, GP, e, red);
+
+        // constraint rows + violation (optimization_module.py:512-533)
+        Red4 vio = {0.f, 0.f, 0.f, 0.f};
+        if (has_ego && prm.R > 0) {
+            float* cons = (prm.out.cons != nullptr && eval_valid) ? prm.out.cons + ev * (size_t)prm.R : nullptr;
+            int base = 0;
+            if (prm.rows_control > 0) {
+                const bool dbl = prm.pb.ego_kind == MTB_EGO_DOUBLE_INTEGRATOR;
+                for (int idx = g; idx < prm.rows_control; idx += GP) {
+                    float val;
+                    if (dbl) {                                    // |v_{t+1} - v_t| / dt per component
+                        const int t = idx >> 1;
+                        const float4 a = ego[t], b = ego[t + 1];
+                        val = fabsf(((idx & 1) ? (b.w - a.w) : (b.z - a.z)) / dt);
+                    } else {                                      // ||p_{t+1} - p_t|| / dt
+                        const float4 a = ego[idx], b = ego[idx + 1];
+                        const float ux = (b.x - a.x) / dt, uy = (b.y - a.y) / dt;
+                        val = sqrtf(ux * ux + uy * uy);
+                    }
+                    val /= prm.md.u_max;
+                    if (cons != nullptr) cons[base + idx] = val;
+                    vio.a += fmaxf(val - 1.0f, 0.f);
+                }
+                base += prm.rows_control;
+            }
+            if (prm.rows_speed > 0) {
+                for (int idx = g; idx < prm.rows_speed; idx += GP) {
+                    const float4 x = ego[idx >> 1];
+                    const float val = ((idx & 1) ? x.w : x.z) / prm.md.v_max;
+                    if (cons != nullptr) cons[base + idx] = val;
+                    vio.b += fmaxf(-1.0f - val, 0.f) + fmaxf(val - 1.0f, 0.f);
+                }
+                base += prm.rows_speed;
+            }
+            if (prm.rows_mind > 0) {
+                for (int idx = g; idx < N * T; idx += GP) {
+                    const int k = idx / T, t = idx - k * T;
+                    const float4 mu = mus[t * N + k];
+                    const float4 x = ego[t];
+                    const float dx = x.x - mu.x, dy = x.y - mu.y;
+                    const float val = sqrtf(dx * dx + dy * dy);
+                    if (cons != nullptr) cons[base + idx] = val;
+                    if (amask == nullptr || amask[k] != 0) vio.c += fmaxf(prm.md.min_distance - val, 0.f);
+                }
+            }
+            vio = group_reduce4(vio, GP, e, red);
+        }
+
+        if (g == 0) {
+            int K = 0;
+            for (int k = 0; k < N; ++k) K += (amask == nullptr || amask[k] != 0) ? 1 : 0;
+            const float invK = (K > 0) ? 1.0f / (float)K : 0.f;
+            const float raw_goal = part.a / (float)(2 * (T + 1));
+            const float raw_acc = (T > 1) ? part.b * invK / (float)(T - 1) : 0.f;
+            const float raw_vel = part.c * invK / (float)T;
+            const float raw_pos = part.d * invK / (float)(2 * T);
+            const float o_goal = prm.md.w_goal * raw_goal;
+            const float o_acc = prm.md.w_acc * fminf(raw_acc, prm.md.max_acc);
+            const float o_vel = prm.md.w_vel * fminf(raw_vel, prm.md.max_vel);
+            const float o_pos = prm.md.w_pos * fminf(raw_pos, prm.md.max_pos);
+            // clamp_max passes the gradient on raw <= max (torch), saturated objectives have zero gradient
+            const float cacc = (want_interact && raw_acc <= prm.md.max_acc && T > 1) ? prm.md.w_acc * invK / ((float)(T - 1) * dt) : 0.f;
+            const float cvel = (want_interact && raw_vel <= prm.md.max_vel) ? prm.md.w_vel * invK / (float)T : 0.f;
+            const float cpos = (want_interact && raw_pos <= prm.md.max_pos) ? prm.md.w_pos * invK / (float)(2 * T) : 0.f;
+            misc[kCoefAcc] = cacc;
+            misc[kCoefVel] = cvel;
+            misc[kCoefPos] = cpos;
+            misc[kNeedAdjoint] = (cacc != 0.f || cvel != 0.f || cpos != 0.f) ? 1.f : 0.f;
+            if (eval_valid) {
+                if (prm.out.obj != nullptr) {
+                    float* o = prm.out.obj + ev * 4;
+                    o[0] = o_goal; o[1] = o_acc; o[2] = o_vel; o[3] = o_pos;
+                }
+                if (prm.out.obj_raw != nullptr) {
+                    float* o = prm.out.obj_raw + ev * 4;
+                    o[0] = raw_goal; o[1] = raw_acc; o[2] = raw_vel; o[3] = raw_pos;
+                }
+                if (prm.out.total != nullptr) prm.out.total[ev] = ((o_goal + o_acc) + o_vel) + o_pos;
+                if (prm.out.violation != nullptr) {
+                    const float eps = prm.md.violation_eps;
+                    const float va = (fabsf(vio.a) < eps) ? 0.f : vio.a;
+                    const float vb = (fabsf(vio.b) < eps) ? 0.f : vio.b;
+                    const float vc = (fabsf(vio.c) < eps) ? 0.f : vio.c;
+                    prm.out.violation[ev] = (va + vb) + vc;
+                }
+                if (prm.out.stats != nullptr && want_interact &&
+                    (raw_acc > prm.md.max_acc || raw_vel > prm.md.max_vel || raw_pos > prm.md.max_pos))
+                    atomicAdd(prm.out.stats + 2, 1ull);
+            }
+        }
+        // optional rollout outputs
+        if (eval_valid && prm.out.mus != nullptr) {
+            float4* mo = reinterpret_cast<float4*>(prm.out.mus + ev * (size_t)N * T * 4);
+            for (int idx = g; idx < N * T; idx += GP) {
+                const int k = idx / T, t = idx - k * T;
+                mo[idx] = mus[t * N + k];
+            }
+        }
+        if (eval_valid && has_ego && prm.out.ego_traj != nullptr) {
+            float4* eo = reinterpret_cast<float4*>(prm.out.ego_traj + ev * (size_t)(T + 1) * 4);
+            for (int t = g; t <= T; t += GP) eo[t] = ego[t];
+        }
+        __syncthreads();                                          // misc visible, ctl free for the gradient
+
+        // ================================================================== backward (adjoint) pass
+        if (GRAD) {
+            // per group: anything to back-propagate through the environment? (saturated objectives have zero
+            // gradient). prm.want_env_adjoint is uniform for the block, so every thread reaches the barriers.
+            const bool env_adjoint = prm.want_env_adjoint != 0 && misc[kNeedAdjoint] != 0.f;
+            V2 pbar = v2(0.f, 0.f), vbar = v2(0.f, 0.f);
+            const bool in_cost = active && (amask == nullptr || amask[m] != 0);
+            const float w_over_p = pw / (float)P;
+            for (int t = T - 2; t >= 0 && prm.want_env_adjoint != 0; --t) {
+                __syncthreads();                                  // level t+1 adjoints complete
+                const int b_next = (t + 1) % 3, b_cur = t % 3, b_free = (t + 2) % 3;
+                for (int k = g; k < N; k += GP) abar[b_free * N + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                V2 eb_p = v2(0.f, 0.f), eb_v = v2(0.f, 0.f);      // this particle's share of the ego adjoint at t
+                if (active && env_adjoint) {
+                    float4 tot = abar[b_next * N + m];
+                    const float4 sd = objective_seed(prm, misc, mus, wo_scene, m, t + 1, in_cost);
+                    tot.x += sd.x; tot.y += sd.y; tot.z += sd.z; tot.w += sd.w;
+                    if (i == 0 && t >= 1) {                       // mu_p[t+1] = mu_p[t] + dt mu_v[t]
+                        float* ac = reinterpret_cast<float*>(abar + b_cur * N + m);
+                        atomicAdd(ac + 0, tot.x);
+                        atomicAdd(ac + 1, tot.y);
+                        atomicAdd(ac + 2, dt * tot.x);
+                        atomicAdd(ac + 3, dt * tot.y);
+                    }
+                    // mu_v[t+1] = (1/P) sum_i w_i (v'_i + noise)
+                    vbar.x = fmaf(tot.z, w_over_p, vbar.x);
+                    vbar.y = fmaf(tot.w, w_over_p, vbar.y);
+                    // v' = u', p' = p + dt u'
+                    const V2 upbar = v2(fmaf(dt, pbar.x, vbar.x), fmaf(dt, pbar.y, vbar.y));
+                    const float4 tp = tape[(size_t)t * tape_stride + tape_idx];
+                    const V2 pt = v2(tp.x, tp.y), ut = v2(tp.z, tp.w);
+                    V2 vt = v_init;
+                    if (t > 0) {
+                        const float4 tq = tape[(size_t)(t - 1) * tape_stride + tape_idx];
+                        vt = feasible(v2(tq.z, tq.w), u_ped);
+                    }
+                    const V2 ubar = feasible_adjoint(ut, u_ped, upbar);
+                    V2 pb = pbar;                                 // p carries through p' = p + dt u'
+                    V2 vb = v2(0.f, 0.f);
+                    if (ENV == MTB_ENV_SOCIAL_FORCES) {
+                        const float4* mus_t = mus + t * N;
+                        goal_force_adjoint(pt, vt, goal, inv_tau, prm.pb.sf_goal_radius, ubar, pb, vb);
+                        const V2 fbar = v2(-ubar.x, -ubar.y);     // u = f_goal - sum F_k - F_ego
+                        {
+                            const float4 eg = ego[t];
+                            const V2 r = pt - v2(eg.x, eg.y), w = vt - v2(eg.z, eg.w);
+                            const RepulsionFwd o = repulsion_forward(r, w, pv0, psig, dt, u_ped);
+                            V2 rb, wb;
+                            repulsion_adjoint(o, r, w, dt, fbar, rb, wb);
+                            pb = pb + rb; vb = vb + wb;
+                            eb_p = eb_p - rb; eb_v = eb_v - wb;
+                        }
+                        for (int wd = 0; wd < MW; ++wd) {
+                            unsigned bits = maskbuf[((size_t)t * tape_stride + tape_idx) * MW + wd];
+                            while (bits) {
+                                const int k = (wd << 5) + __ffs((int)bits) - 1;
+                                bits &= bits - 1;
+                                const float4 mu = mus_t[k];
+                                const V2 r = pt - v2(mu.x, mu.y), w = vt - v2(mu.z, mu.w);
+                                const RepulsionFwd o = repulsion_forward(r, w, pv0, psig, dt, u_ped);
+                                V2 rb, wb;
+                                repulsion_adjoint(o, r, w, dt, fbar, rb, wb);
+                                pb = pb + rb; vb = vb + wb;
+                                if (t >= 1) {                     // mus[:, 0] are constants
+                                    float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
+                                    atomicAdd(ac + 0, -rb.x);
+                                    atomicAdd(ac + 1, -rb.y);
+                                    atomicAdd(ac + 2, -wb.x);
+                                    atomicAdd(ac + 3, -wb.y);
+                                }
+                            }
+                        }
+                    } else if (ENV == MTB_ENV_POTENTIAL_FIELD) {  // u = v + gate * impact(ego_p - p)
+                        vb = vb + ubar;
+                        const float4 eg = ego[t];
+                        const V2 delta = v2(eg.x - pt.x, eg.y - pt.y);
+                        if (pf_gate(vt, delta, prm.pb.pf_theta_max)) {
+                            const V2 db = pf_impact_adjoint(delta, pv0, ubar);
+                            pb = pb - db;
+                            eb_p = eb_p + db;
+                        }
+                    }
+                    pbar = pb;
+                    vbar = vb;
+                }
+                // ego adjoint of step t: sum over the particles of the group (all lanes take part)
+                float* ebt = reinterpret_cast<float*>(egobar + t);
+                if (GP <= 32) {
+                    for (int off = GP >> 1; off > 0; off >>= 1) {
+                        eb_p.x += __shfl_xor_sync(0xffffffffu, eb_p.x, off);
+                        eb_p.y += __shfl_xor_sync(0xffffffffu, eb_p.y, off);
+                        eb_v.x += __shfl_xor_sync(0xffffffffu, eb_v.x, off);
+                        eb_v.y += __shfl_xor_sync(0xffffffffu, eb_v.y, off);
+                    }
+                    if (g == 0) { ebt[0] = eb_p.x; ebt[1] = eb_p.y; ebt[2] = eb_v.x; ebt[3] = eb_v.y; }
+                } else {
+                    for (int off = 16; off > 0; off >>= 1) {
+                        eb_p.x += __shfl_xor_sync(0xffffffffu, eb_p.x, off);
+                        eb_p.y += __shfl_xor_sync(0xffffffffu, eb_p.y, off);
+                        eb_v.x += __shfl_xor_sync(0xffffffffu, eb_v.x, off);
+                        eb_v.y += __shfl_xor_sync(0xffffffffu, eb_v.y, off);
+                    }
+                    if ((tid & 31) == 0) {
+                        atomicAdd(ebt + 0, eb_p.x);
+                        atomicAdd(ebt + 1, eb_p.y);
+                        atomicAdd(ebt + 2, eb_v.x);
+                        atomicAdd(ebt + 3, eb_v.y);
+                    }
+                }
+            }
+            __syncthreads();
+
+            // ------------------------------------------------ fold ego adjoints through the ego dynamics
+            if (has_ego && g == 0) {
+                const float cg = prm.md.w_goal / (float)(T + 1);  // d/dp_t of w * mean((p - g)^2) = w (p_t - g) / (T+1)
+                float gx = 0.f, gy = 0.f;
+                if (prm.md.w_goal != 0.f) { gx = __ldg(prm.md.ego_goal + (size_t)s * 2); gy = __ldg(prm.md.ego_goal + (size_t)s * 2 + 1); }
+                float apx = 0.f, apy = 0.f, avx = 0.f, avy = 0.f;     // environment part
+                float gpx = 0.f, gpy = 0.f, gvx = 0.f, gvy = 0.f;     // goal part (kept apart: separate nan_to_num)
+                const bool dbl = prm.pb.ego_kind == MTB_EGO_DOUBLE_INTEGRATOR;
+                for (int t = T; t >= 1; --t) {
+                    const float4 eb = egobar[t];
+                    const float4 x = ego[t];
+                    const float bpx = cg * (x.x - gx), bpy = cg * (x.y - gy);
+                    float outx, outy, goutx, gouty;
+                    if (dbl) {
+                        avx += eb.z + dt * apx; avy += eb.w + dt * apy;
+                        gvx += dt * gpx;        gvy += dt * gpy;
+                        outx = dt * avx; outy = dt * avy; goutx = dt * gvx; gouty = dt * gvy;
+                        apx += eb.x; apy += eb.y; gpx += bpx; gpy += bpy;
+                    } else {
+                        apx += eb.x; apy += eb.y; gpx += bpx; gpy += bpy;
+                        outx = eb.z + dt * apx; outy = eb.w + dt * apy; goutx = dt * gpx; gouty = dt * gpy;
+                    }
+                    ctl[2 * (t - 1) + 0] = sanitize(outx) + goutx;
+                    ctl[2 * (t - 1) + 1] = sanitize(outy) + gouty;
+                }
+            }
+            __syncthreads();
+            if (has_ego && eval_valid) {
+                float* go = prm.out.grad + ev * (size_t)(2 * T);
+                for (int idx = g; idx < 2 * T; idx += GP) go[idx] = ctl[idx];
+            }
+        }
+        __syncthreads();
+    }
+
+    if (prm.out.stats != nullptr) {
+        atomicAdd(prm.out.stats + 0, n_pairs);
+        atomicAdd(prm.out.stats + 1, n_ego);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// best feasible candidate per scene (random_search.py:28-35 keeps the best objective with violation < limit)
+// ---------------------------------------------------------------------------------------------------------
+__global__ void argmin_kernel(const float* __restrict__ total, const float* __restrict__ violation, int C, float feas_tol,
+                              const float* __restrict__ controls, int T, int32_t* best_idx, float* best_val,
+                              float* best_controls) {
+    MTB_SHARED_FLOAT4(smem4);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem4);
+    const int s = blockIdx.x;
+    unsigned long long best = ~0ull;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const float val = total[(size_t)s * C + c];
+        const float vio = (violation != nullptr) ? violation[(size_t)s * C + c] : 0.f;
+        if (vio < feas_tol && !is_nan(val)) {
+            unsigned bits = __float_as_uint(val);
+            bits = (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u);   // order-preserving float -> uint
+            const unsigned long long key = ((unsigned long long)bits << 32) | (unsigned)c;
+            best = key < best ? key : best;
+        }
+    }
+    keys[threadIdx.x] = best;
+    __syncthreads();
+    for (int off = blockDim.x >> 1; off > 0; off >>= 1) {
+        if ((int)threadIdx.x < off) {
+            const unsigned long long o = keys[threadIdx.x + off];
+            if (o < keys[threadIdx.x]) keys[threadIdx.x] = o;
+        }
+        __syncthreads();
+    }
+    best = keys[0];
+    const int idx = (best == ~0ull) ? -1 : (int)(best & 0xffffffffu);
+    if (threadIdx.x == 0) {
+        best_idx[s] = idx;
+        if (best_val != nullptr) best_val[s] = (idx >= 0) ? total[(size_t)s * C + idx] : INFINITY;
+    }
+    if (best_controls != nullptr && controls != nullptr) {
+        for (int j = threadIdx.x; j < 2 * T; j += blockDim.x)
+            best_controls[(size_t)s * 2 * T + j] = (idx >= 0) ? controls[((size_t)s * C + idx) * 2 * T + j] : 0.f;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side: launch geometry
+// ---------------------------------------------------------------------------------------------------------
+static int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+struct DeviceLimits {
+    int sms;
+    int max_smem;      // opt-in dynamic shared memory per block
+    int smem_per_sm;
+};
+
+static DeviceLimits device_limits() {
+    DeviceLimits lim;
+#ifdef MTB_HOST_EMUL
+    lim.sms = 2;
+    lim.max_smem = 227 * 1024;
+    lim.smem_per_sm = 228 * 1024;
+#else
+    int dev = 0;
+    lim.sms = 148; lim.max_smem = 227 * 1024; lim.smem_per_sm = 228 * 1024;   // B200 defaults (no device present)
+    if (cudaGetDevice(&dev) == cudaSuccess) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) lim.sms = v;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) == cudaSuccess && v > 0) lim.max_smem = v;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev) == cudaSuccess && v > 0) lim.smem_per_sm = v;
+    } else {
+        (void)cudaGetLastError();
+    }
+#endif
+    return lim;
+}
+
+static int validate(const mtb_problem* pb) {
+    if (pb == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->num_scenes < 1 || pb->num_candidates < 1 || pb->t_horizon < 1 || pb->num_ados < 1) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->num_ados > MTB_MAX_ADOS || pb->t_horizon > MTB_MAX_HORIZON) return MTB_ERR_TOO_LARGE;
+    if (pb->env_kind < 0 || pb->env_kind > MTB_ENV_KALMAN || pb->ego_kind < 0 || pb->ego_kind > MTB_EGO_NONE) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->env_kind != MTB_ENV_KALMAN && pb->num_particles < 1) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->ego_kind == MTB_EGO_NONE && pb->num_candidates != 1) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->ado0 == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->ego_kind != MTB_EGO_NONE && (pb->ego0 == nullptr || pb->controls == nullptr)) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->env_kind != MTB_ENV_KALMAN && (pb->v0 == nullptr || pb->weight == nullptr)) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->env_kind == MTB_ENV_SOCIAL_FORCES && (pb->sigma == nullptr || pb->ado_goal == nullptr)) return MTB_ERR_BAD_ARGUMENT;
+    const int particles = pb->num_ados * (pb->env_kind == MTB_ENV_KALMAN ? 1 : pb->num_particles);
+    if (particles > kMaxThreads) return MTB_ERR_TOO_LARGE;
+    return 0;
+}
+
+static float pair_cut_squared(float radius) {
+    // largest float d2 with sqrtf(d2) <= radius, so that `d2 <= cut` decides exactly like `norm <= radius`
+    float cut = radius * radius;
+    while (sqrtf(cut) > radius) cut = nextafterf(cut, 0.f);
+    for (;;) {
+        const float nxt = nextafterf(cut, INFINITY);
+        if (sqrtf(nxt) <= radius) cut = nxt; else break;
+    }
+    return cut;
+}
+
+static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs* out, bool want_grad, KParams& prm,
+                mtb_launch_info& info, size_t& workspace_bytes) {
+    const int err = validate(pb);
+    if (err != 0) return err;
+    std::memset(&prm, 0, sizeof(prm));
+    prm.pb = *pb;
+    if (md != nullptr) prm.md = *md;
+    if (out != nullptr) prm.out = *out;
+    const bool kalman = pb->env_kind == MTB_ENV_KALMAN;
+    prm.T = pb->t_horizon;
+    prm.N = pb->num_ados;
+    prm.P = kalman ? 1 : pb->num_particles;
+    prm.G = prm.N * prm.P;
+    prm.MW = (prm.N + 31) / 32;
+    prm.has_ego = pb->ego_kind != MTB_EGO_NONE;
+    prm.want_grad = want_grad ? 1 : 0;
+    prm.pair_cut2 = pair_cut_squared(pb->sf_interaction_radius);
+    if (prm.G <= 32) {
+        int gp = 1;
+        while (gp < prm.G) gp <<= 1;
+        prm.GP = gp;
+    } else {
+        prm.GP = round_up(prm.G, 32);
+    }
+    // constraint rows
+    prm.rows_control = prm.rows_speed = prm.rows_mind = 0;
+    if (md != nullptr && prm.has_ego) {
+        if (md->con_control) prm.rows_control = (pb->ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) ? 2 * prm.T : prm.T;
+        if (md->con_speed) prm.rows_speed = 2 * (prm.T + 1);
+        if (md->con_min_distance) prm.rows_mind = prm.N * prm.T;
+    }
+    prm.R = prm.rows_control + prm.rows_speed + prm.rows_mind;
+
+    const DeviceLimits lim = device_limits();
+    const bool need_tape = want_grad && !kalman && prm.has_ego && prm.T > 1;
+    const bool need_mask = need_tape && pb->env_kind == MTB_ENV_SOCIAL_FORCES;
+
+    auto layout = [&](int E, bool tape_in_smem) -> size_t {
+        int off = 0;
+        prm.off_ctl = off;    off += round_up(2 * prm.T, 4);
+        prm.off_ego = off;    off += (prm.T + 1) * 4;
+        prm.off_egobar = off; off += want_grad ? (prm.T + 1) * 4 : 0;
+        prm.off_mus = off;    off += prm.T * prm.N * 4;
+        prm.off_abar = off;   off += want_grad ? 3 * prm.N * 4 : 0;
+        prm.off_q = off;      off += round_up(prm.GP * 2, 4);
+        prm.off_misc = off;   off += kMiscFloats;
+        prm.off_tape = off;   off += (need_tape && tape_in_smem) ? (prm.T - 1) * prm.GP * 4 : 0;
+        prm.off_mask = off;   off += (need_mask && tape_in_smem) ? round_up((prm.T - 1) * prm.GP * prm.MW, 4) : 0;
+        prm.per_eval_f = off;
+        const int block = E * prm.GP;
+        prm.red_f = round_up(((block + 31) / 32) * 4, 4);
+        return (size_t)(prm.red_f + E * prm.per_eval_f) * sizeof(float);
+    };
+
+    int E = (prm.GP >= kDefaultBlock) ? 1 : kDefaultBlock / prm.GP;
+    const long long total_evals = (long long)pb->num_scenes * pb->num_candidates;
+    if ((long long)E > total_evals) E = (int)total_evals;
+    // the block must be a multiple of a warp: with sub-warp groups keep E a multiple of 32 / GP
+    if (prm.GP < 32) E = round_up(E, 32 / prm.GP);
+    bool tape_in_smem = true;
+    size_t smem = layout(E, true);
+    while (smem > (size_t)lim.max_smem && E * prm.GP > 32 && E > 1) {
+        E = (prm.GP < 32) ? E - 32 / prm.GP : E - 1;
+        if (E < 1) { E = 1; break; }
+        smem = layout(E, true);
+    }
+    if (prm.GP < 32 && E < 32 / prm.GP) E = 32 / prm.GP;
+    smem = layout(E, true);
+    if (smem > (size_t)lim.max_smem) {
+        tape_in_smem = false;
+        smem = layout(E, false);
+        if (smem > (size_t)lim.max_smem) return MTB_ERR_TOO_LARGE;
+    }
+    prm.E = E;
+    prm.tape_in_smem = tape_in_smem ? 1 : 0;
+    prm.num_evals = (long long)pb->num_scenes * pb->num_candidates;
+    prm.num_items = (int)((prm.num_evals + E - 1) / E);
+    prm.use_tape = need_tape ? 1 : 0;
+    prm.want_env_adjoint = (need_tape && md != nullptr && md->mus_wo != nullptr &&
+                            (md->w_acc != 0.f || md->w_vel != 0.f || md->w_pos != 0.f)) ? 1 : 0;
+    const int block = E * prm.GP;
+    int blocks_per_sm = (int)((size_t)lim.smem_per_sm / (smem + 1024));
+    if (blocks_per_sm < 1) blocks_per_sm = 1;
+    const int by_threads = 2048 / block;
+    if (blocks_per_sm > by_threads) blocks_per_sm = by_threads < 1 ? 1 : by_threads;
+    if (blocks_per_sm > 32) blocks_per_sm = 32;
+    int grid = lim.sms * blocks_per_sm;
+    if (grid > prm.num_items) grid = prm.num_items;
+    workspace_bytes = 0;
+    if (need_tape && !tape_in_smem) {
+        const size_t tape_b = (size_t)grid * (prm.T - 1) * block * sizeof(float4);
+        const size_t mask_b = need_mask ? (size_t)grid * (prm.T - 1) * block * prm.MW * sizeof(unsigned) : 0;
+        workspace_bytes = tape_b + mask_b;
+    }
+    info.grid = grid;
+    info.block = block;
+    info.evals_per_block = E;
+    info.group_size = prm.GP;
+    info.smem_bytes = (int)smem;
+    info.tape_in_smem = prm.tape_in_smem;
+    info.num_items = prm.num_items;
+    info.blocks_per_sm = blocks_per_sm;
+    return 0;
+}
+
+template <int ENV, bool GRAD, int MAXT>
+static int launch_evaluate_t(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
+#ifndef MTB_HOST_EMUL
+    cudaError_t err = cudaFuncSetAttribute(evaluate_kernel<ENV, GRAD, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, info.smem_bytes);
+    if (err != cudaSuccess) return (int)err;
+#endif
+    MTB_LAUNCH((evaluate_kernel<ENV, GRAD, MAXT>), info.grid, info.block, (size_t)info.smem_bytes, stream, prm);
+#ifndef MTB_HOST_EMUL
+    return (int)cudaGetLastError();
+#else
+    return 0;
+#endif
+}
+
+// two register budgets: blocks of <= 256 threads (the common case) may use up to 255 registers per thread
+template <int ENV, bool GRAD>
+static int launch_evaluate(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
+    if (info.block <= kDefaultBlock) return launch_evaluate_t<ENV, GRAD, kDefaultBlock>(prm, info, stream);
+    return launch_evaluate_t<ENV, GRAD, kMaxThreads>(prm, info, stream);
+}
+
+}  // namespace mtb
+
+// =============================================================================================================
+// C ABI
+// =============================================================================================================
+extern "C" {
+
+int mtb_abi_version(void) { return MTB_ABI_VERSION; }
+
+const char* mtb_error_string(int code) {
+    switch (code) {
+        case 0: return "ok";
+        case MTB_ERR_BAD_ARGUMENT: return "mantrap_b200: bad argument";
+        case MTB_ERR_TOO_LARGE: return "mantrap_b200: problem exceeds the supported size (N <= 64, T <= 64, N*P <= 1024)";
+        case MTB_ERR_WORKSPACE: return "mantrap_b200: workspace missing or too small";
+        default: break;
+    }
+#ifndef MTB_HOST_EMUL
+    if (code > 0) return cudaGetErrorString((cudaError_t)code);
+#endif
+    return "mantrap_b200: unknown error";
+}
+
+int mtb_num_constraint_rows(const mtb_problem* problem, const mtb_modules* modules) {
+    mtb::KParams prm;
+    mtb_launch_info info;
+    size_t ws;
+    const int err = mtb::plan(problem, modules, nullptr, false, prm, info, ws);
+    return err != 0 ? err : prm.R;
+}
+
+size_t mtb_workspace_bytes(const mtb_problem* problem, int want_grad) {
+    mtb::KParams prm;
+    mtb_launch_info info;
+    size_t ws = 0;
+    if (mtb::plan(problem, nullptr, nullptr, want_grad != 0, prm, info, ws) != 0) return 0;
+    return ws;
+}
+
+int mtb_query_launch(const mtb_problem* problem, int want_grad, mtb_launch_info* info) {
+    if (info == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    mtb::KParams prm;
+    size_t ws = 0;
+    return mtb::plan(problem, nullptr, nullptr, want_grad != 0, prm, *info, ws);
+}
+
+int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const mtb_outputs* out, void* workspace,
+                 size_t workspace_bytes, void* stream) {
+    if (out == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    const bool want_grad = out->grad != nullptr;
+    mtb::KParams prm;
+    mtb_launch_info info;
+    size_t ws = 0;
+    const int err = mtb::plan(problem, modules, out, want_grad, prm, info, ws);
+    if (err != 0) return err;
+    if (want_grad && problem->ego_kind == MTB_EGO_NONE) return MTB_ERR_BAD_ARGUMENT;
+    if (modules != nullptr && (modules->w_acc != 0.f || modules->w_vel != 0.f || modules->w_pos != 0.f) &&
+        modules->mus_wo == nullptr)
+        return MTB_ERR_BAD_ARGUMENT;
+    if (modules != nullptr && modules->w_goal != 0.f && modules->ego_goal == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    if (ws > 0) {
+        if (workspace == nullptr || workspace_bytes < ws) return MTB_ERR_WORKSPACE;
+        const size_t tape_b = (size_t)info.grid * (prm.T - 1) * info.block * sizeof(float4);
+        prm.tape_global = reinterpret_cast<float4*>(workspace);
+        prm.mask_global = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(workspace) + tape_b);
+    }
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    switch (problem->env_kind) {
+        case MTB_ENV_SOCIAL_FORCES:
+            return want_grad ? mtb::launch_evaluate<MTB_ENV_SOCIAL_FORCES, true>(prm, info, st)
+                             : mtb::launch_evaluate<MTB_ENV_SOCIAL_FORCES, false>(prm, info, st);
+        case MTB_ENV_POTENTIAL_FIELD:
+            return want_grad ? mtb::launch_evaluate<MTB_ENV_POTENTIAL_FIELD, true>(prm, info, st)
+                             : mtb::launch_evaluate<MTB_ENV_POTENTIAL_FIELD, false>(prm, info, st);
+        default:
+            return want_grad ? mtb::launch_evaluate<MTB_ENV_KALMAN, true>(prm, info, st)
+                             : mtb::launch_evaluate<MTB_ENV_KALMAN, false>(prm, info, st);
+    }
+}
+
+int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, int32_t num_candidates, float feas_tol,
+               const float* controls, int32_t t_horizon, int32_t* best_idx, float* best_val, float* best_controls,
+               void* stream) {
+    if (total == nullptr || best_idx == nullptr || num_scenes < 1 || num_candidates < 1) return MTB_ERR_BAD_ARGUMENT;
+    const int block = 256;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    MTB_LAUNCH(mtb::argmin_kernel, num_scenes, block, (size_t)block * sizeof(unsigned long long), st, total, violation,
+               num_candidates, feas_tol, controls, t_horizon, best_idx, best_val, best_controls);
+#ifndef MTB_HOST_EMUL
+    return (int)cudaGetLastError();
+#else
+    return 0;
+#endif
+}
+
+size_t mtb_jacobian_workspace_bytes(const mtb_problem*) { return 0; }
+
+int mtb_constraint_jacobian(const mtb_problem*, const mtb_modules*, float*, float*, void*, size_t, void*) {
+    return MTB_ERR_BAD_ARGUMENT;   // implemented in mtb_jacobian.cu (forward-mode tangent kernel)
+}
+
+}  // extern "C"

@@ -1,0 +1,181 @@
+// Per-particle step models of mantrap's particle environments and their hand-derived adjoints.
+//
+// Every function is a straight restatement of a few lines of the reference (paths relative to the reference
+// repository root) plus the reverse-mode derivative the reference obtains from torch.autograd:
+//   repulsion      mantrap/environment/social_forces.py:94-126   (_repulsive_force; force = dV/dr via autograd)
+//   goal force     mantrap/environment/social_forces.py:137-144
+//   control clamp  mantrap/agents/base/discrete.py:358-370        (make_controls_feasible, pedestrian L2 clamp)
+//   potential field mantrap/environment/simplified/potential_field.py:70-86
+// Kink conventions follow torch 2.x autograd (probe-verified): norm'(0) = 0, clamp passes the
+// gradient on the closed interval, sign' = 0, |x|' = sign(x).
+#pragma once
+
+#ifndef MTB_HOST_EMUL
+#include <cuda_runtime.h>
+#define MTB_DEV __device__ __forceinline__
+#else
+#define MTB_DEV static inline
+#endif
+
+namespace mtb {
+
+struct V2 {
+    float x, y;
+};
+MTB_DEV V2 v2(float x, float y) { V2 r; r.x = x; r.y = y; return r; }
+MTB_DEV V2 operator+(V2 a, V2 b) { return v2(a.x + b.x, a.y + b.y); }
+MTB_DEV V2 operator-(V2 a, V2 b) { return v2(a.x - b.x, a.y - b.y); }
+MTB_DEV V2 operator*(float s, V2 a) { return v2(s * a.x, s * a.y); }
+MTB_DEV float dot(V2 a, V2 b) { return a.x * b.x + a.y * b.y; }
+MTB_DEV void axpy(V2& y, float a, V2 x) { y.x = fmaf(a, x.x, y.x); y.y = fmaf(a, x.y, y.y); }
+MTB_DEV bool is_nan(float x) { return x != x; }
+
+// ---------------------------------------------------------------------------------------------------------
+// Social-forces repulsion  F = dV/dr,  V = v0 exp(-b/sigma),  b = 1/2 sqrt((|r| + |r - w dt|)^2 - (dt |w|)^2)
+// ---------------------------------------------------------------------------------------------------------
+struct RepulsionFwd {
+    V2 force;      // clamped, NaN -> 0
+    bool dead;     // force was NaN: the reference returns a constant zeros(2), no gradient path (:123-124)
+    bool pass_x;   // clamp passes the gradient for this component (closed interval, :122)
+    bool pass_y;
+    // intermediates kept for the adjoint
+    V2 s, t1, t2;
+    float inv_n1, inv_n2, a, sb, inv_sb, pot, k, inv_sigma;
+};
+
+MTB_DEV RepulsionFwd repulsion_forward(V2 r, V2 w, float v0, float sigma, float dt, float f_max) {
+    RepulsionFwd o;
+    o.s = v2(fmaf(-dt, w.x, r.x), fmaf(-dt, w.y, r.y));
+    const float n1 = sqrtf(dot(r, r));
+    const float n2 = sqrtf(dot(o.s, o.s));
+    const float n3sq = dot(w, w);
+    o.inv_n1 = 1.0f / n1;
+    o.inv_n2 = 1.0f / n2;
+    o.a = n1 + n2;
+    const float big_b = fmaf(o.a, o.a, -(dt * dt) * n3sq);
+    o.sb = sqrtf(big_b);                       // b = sb / 2
+    o.inv_sb = 1.0f / o.sb;
+    o.inv_sigma = 1.0f / sigma;
+    o.pot = v0 * expf(-0.5f * o.sb * o.inv_sigma);
+    // k = dV/dn1 = dV/dn2 = -(V/sigma) * (n1+n2) / (4 b)
+    o.k = -(o.pot * o.inv_sigma) * (o.a * 0.5f * o.inv_sb);
+    o.t1 = o.inv_n1 * r;
+    o.t2 = o.inv_n2 * o.s;
+    // Two separate products, as autograd accumulates them: with V = inf (sampled sigma <= 0) opposite-signed
+    // terms give inf - inf = NaN, which the reference turns into a zero force.
+    const float fx = o.k * o.t1.x + o.k * o.t2.x;
+    const float fy = o.k * o.t1.y + o.k * o.t2.y;
+    o.dead = is_nan(fx) || is_nan(fy);
+    o.pass_x = (fx >= -f_max) && (fx <= f_max);
+    o.pass_y = (fy >= -f_max) && (fy <= f_max);
+    o.force = o.dead ? v2(0.f, 0.f) : v2(fminf(fmaxf(fx, -f_max), f_max), fminf(fmaxf(fy, -f_max), f_max));
+    return o;
+}
+
+// Adjoint of the (clamped) force w.r.t. r and w for an incoming adjoint fbar of the clamped force.
+MTB_DEV void repulsion_adjoint(const RepulsionFwd& o, V2 r, V2 w, float dt, V2 fbar, V2& rbar, V2& wbar) {
+    rbar = v2(0.f, 0.f);
+    wbar = v2(0.f, 0.f);
+    if (o.dead) return;
+    fbar.x = o.pass_x ? fbar.x : 0.f;
+    fbar.y = o.pass_y ? fbar.y : 0.f;
+    // F = k t1 + k t2
+    const float kbar = dot(fbar, o.t1 + o.t2);
+    const V2 tbar = o.k * fbar;                                   // adjoint of t1 and of t2
+    // t1 = r / n1, t2 = s / n2
+    float n1bar = -dot(tbar, o.t1) * o.inv_n1;
+    float n2bar = -dot(tbar, o.t2) * o.inv_n2;
+    V2 sbar = o.inv_n2 * tbar;
+    rbar = o.inv_n1 * tbar;
+    // k = V * a * q with q = -1 / (2 sigma sb)
+    const float q = -0.5f * o.inv_sigma * o.inv_sb;
+    const float potbar = kbar * o.a * q;
+    float abar = kbar * o.pot * q;
+    float sbbar = -kbar * o.k * o.inv_sb;
+    // V = v0 exp(-sb / (2 sigma))
+    sbbar = fmaf(potbar * o.pot, -0.5f * o.inv_sigma, sbbar);
+    // sb = sqrt(B), B = a^2 - dt^2 |w|^2
+    const float bbar = 0.5f * sbbar * o.inv_sb;
+    abar = fmaf(2.0f * o.a, bbar, abar);
+    const float n3sqbar = -(dt * dt) * bbar;
+    n1bar += abar;
+    n2bar += abar;
+    axpy(rbar, n1bar, o.t1);                                     // n1 = |r|
+    axpy(sbar, n2bar, o.t2);                                     // n2 = |s|
+    wbar = (2.0f * n3sqbar) * w;                                 // |w|^2
+    rbar = rbar + sbar;                                          // s = r - dt w
+    axpy(wbar, -dt, sbar);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Goal (destination) force  f = ((d/|d|) |v| - v) / tau  with d = goal - p, zero inside the goal radius
+// ---------------------------------------------------------------------------------------------------------
+MTB_DEV V2 goal_force(V2 p, V2 v, V2 goal, float inv_tau, float goal_radius) {
+    const V2 d = goal - p;
+    const float nd = sqrtf(dot(d, d));
+    if (nd < goal_radius) return v2(0.f, 0.f);
+    const float sp = sqrtf(dot(v, v));
+    const float inv_nd = 1.0f / nd;
+    return v2((d.x * inv_nd * sp - v.x) * inv_tau, (d.y * inv_nd * sp - v.y) * inv_tau);
+}
+
+MTB_DEV void goal_force_adjoint(V2 p, V2 v, V2 goal, float inv_tau, float goal_radius, V2 fbar, V2& pbar, V2& vbar) {
+    const V2 d = goal - p;
+    const float nd = sqrtf(dot(d, d));
+    if (nd < goal_radius) return;
+    const float inv_nd = 1.0f / nd;
+    const float sp = sqrtf(dot(v, v));
+    const V2 dir = inv_nd * d;
+    const V2 h = inv_tau * fbar;
+    vbar = vbar - h;
+    const float spbar = dot(h, dir);
+    const V2 dirbar = sp * h;
+    const V2 dbar = inv_nd * (dirbar - dot(dirbar, dir) * dir);
+    pbar = pbar - dbar;
+    if (sp > 0.f) axpy(vbar, spbar / sp, v);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Pedestrian control clamp  u' = u / max(|u|, 1e-6) * clamp(|u|, -u_max, u_max)
+// ---------------------------------------------------------------------------------------------------------
+MTB_DEV V2 feasible(V2 u, float u_max) {
+    const float nu = sqrtf(dot(u, u));
+    const float d = fmaxf(nu, 1e-6f);
+    const float cl = fminf(nu, u_max);
+    return v2(u.x / d * cl, u.y / d * cl);
+}
+
+MTB_DEV V2 feasible_adjoint(V2 u, float u_max, V2 upbar) {
+    const float nu = sqrtf(dot(u, u));
+    const float d = fmaxf(nu, 1e-6f);
+    const float cl = fminf(nu, u_max);
+    const float inv_d = 1.0f / d;
+    V2 ubar = (cl * inv_d) * upbar;
+    const float du = dot(upbar, u);
+    float nubar = 0.f;
+    if (nu >= 1e-6f) nubar -= du * cl * inv_d * inv_d;           // d = |u| branch of clamp(min=1e-6)
+    if (nu <= u_max) nubar += du * inv_d;                        // cl = |u| branch of clamp(-u_max, u_max)
+    if (nu > 0.f) axpy(ubar, nubar / nu, u);
+    return ubar;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Potential field: u = v + [ |atan2(v) - atan2(delta)| < theta ] * (-v0 sign(delta) exp(-|delta|)), delta = ego_p - p
+// ---------------------------------------------------------------------------------------------------------
+MTB_DEV bool pf_gate(V2 v, V2 delta, float theta_max) {
+    const float theta = atan2f(v.y, v.x) - atan2f(delta.y, delta.x);
+    return fabsf(theta) < theta_max;
+}
+MTB_DEV float sgn(float x) { return (x > 0.f) ? 1.f : ((x < 0.f) ? -1.f : 0.f); }
+MTB_DEV V2 pf_impact(V2 delta, float v0) {
+    const float v0c = fmaxf(v0, 1e-3f);
+    return v2(-v0c * sgn(delta.x) * expf(-fabsf(delta.x)), -v0c * sgn(delta.y) * expf(-fabsf(delta.y)));
+}
+// d impact / d delta (diagonal): v0 exp(-|delta|) where delta != 0
+MTB_DEV V2 pf_impact_adjoint(V2 delta, float v0, V2 ubar) {
+    const float v0c = fmaxf(v0, 1e-3f);
+    const float sx = sgn(delta.x), sy = sgn(delta.y);
+    return v2(ubar.x * v0c * sx * sx * expf(-fabsf(delta.x)), ubar.y * v0c * sy * sy * expf(-fabsf(delta.y)));
+}
+
+}  // namespace mtb

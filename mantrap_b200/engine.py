@@ -1,0 +1,247 @@
+"""Batched scene data model and the launcher of the fused CUDA hot path.
+
+`SceneBatch` is the HBM layout of S scenes (structure of arrays, float32); `launch_evaluate` fills
+the C-ABI structs of `include/mantrap_b200.h` from it and launches `mtb_evaluate` on the current stream. It is
+pointer plumbing only. `Engine` is what the product uses: it binds the CUDA library and refuses anything that is
+not a CUDA tensor (there is no CPU path).
+"""
+import ctypes
+import dataclasses
+import math
+import typing
+
+import torch
+
+from . import _cabi, constants
+
+ENV_KINDS = {"sf": _cabi.ENV_SOCIAL_FORCES, "pf": _cabi.ENV_POTENTIAL_FIELD, "kalman": _cabi.ENV_KALMAN}
+EGO_KINDS = {"double": _cabi.EGO_DOUBLE_INTEGRATOR, "single": _cabi.EGO_SINGLE_INTEGRATOR, None: _cabi.EGO_NONE}
+OBJECTIVE_KEYS = ("goal", "acc", "vel", "pos")
+
+
+@dataclasses.dataclass
+class SceneBatch:
+    """S scenes with N ados and P particles per ado. All tensors float32, contiguous, on one device.
+
+    ego0 [S,4], ego_goal [S,2], ado0 [S,N,4], ado_goal [S,N,2] (social forces), v0 / sigma / weight [S,N,P]
+    (one `create_particles` draw per scene, mantrap/environment/base/particle.py:17-79; weights normalised over
+    the ado axis, :141), noise [S,T-1,N,P,2] or None.
+    """
+    env_kind: str
+    ego_kind: typing.Optional[str]
+    dt: float
+    ego0: typing.Optional[torch.Tensor]
+    ego_goal: typing.Optional[torch.Tensor]
+    ado0: torch.Tensor
+    ado_goal: typing.Optional[torch.Tensor] = None
+    v0: typing.Optional[torch.Tensor] = None
+    sigma: typing.Optional[torch.Tensor] = None
+    weight: typing.Optional[torch.Tensor] = None
+    noise: typing.Optional[torch.Tensor] = None
+    axes_diag: float = math.sqrt(20.0 ** 2 + 20.0 ** 2)
+
+    @property
+    def num_scenes(self) -> int:
+        return self.ado0.shape[0]
+
+    @property
+    def num_ados(self) -> int:
+        return self.ado0.shape[1]
+
+    @property
+    def num_particles(self) -> int:
+        return 1 if self.v0 is None else self.v0.shape[2]
+
+    @property
+    def device(self) -> torch.device:
+        return self.ado0.device
+
+    def to(self, device) -> "SceneBatch":
+        def mv(x):
+            return None if x is None else x.to(device=device, dtype=torch.float32).contiguous()
+        return dataclasses.replace(self, ego0=mv(self.ego0), ego_goal=mv(self.ego_goal), ado0=mv(self.ado0),
+                                   ado_goal=mv(self.ado_goal), v0=mv(self.v0), sigma=mv(self.sigma),
+                                   weight=mv(self.weight), noise=mv(self.noise))
+
+    def without_ego(self) -> "SceneBatch":
+        return dataclasses.replace(self, ego_kind=None)
+
+
+@dataclasses.dataclass
+class ModuleSpec:
+    """Which objective / constraint modules enter the evaluation, in the reference's conventions:
+    `weights[key]` is the module weight (goal_norm.py:37 -> 0.5, interaction modules 1.0); normalisation
+    (goal: / environment diagonal, interaction: / clamp maximum) is applied by the launcher."""
+    weights: typing.Dict[str, float] = dataclasses.field(default_factory=dict)
+    mus_wo: typing.Optional[torch.Tensor] = None          # [S,N,T,4]
+    ado_mask: typing.Optional[torch.Tensor] = None        # [S,N] uint8
+    control_limits: bool = False
+    speed_limits: bool = False
+    min_distance: bool = False
+    u_max: float = constants.ROBOT_ACC_MAX
+    v_max: float = constants.ROBOT_SPEED_MAX
+    d_min: float = constants.CONSTRAINT_MIN_L2_DISTANCE
+
+
+def _problem_struct(scene: SceneBatch, controls: typing.Optional[torch.Tensor], t_horizon: int) -> _cabi.MtbProblem:
+    pb = _cabi.MtbProblem()
+    pb.num_scenes = scene.num_scenes
+    pb.num_candidates = 1 if controls is None else controls.shape[1]
+    pb.t_horizon = t_horizon
+    pb.num_ados = scene.num_ados
+    pb.num_particles = scene.num_particles
+    pb.env_kind = ENV_KINDS[scene.env_kind]
+    pb.ego_kind = EGO_KINDS[scene.ego_kind if controls is not None else None]
+    pb.dt = scene.dt
+    pb.sf_tau = constants.SOCIAL_FORCES_DEFAULT_TAU
+    pb.ped_speed_max = constants.PED_SPEED_MAX
+    pb.sf_goal_radius = constants.SOCIAL_FORCES_MAX_GOAL_DISTANCE
+    pb.sf_interaction_radius = constants.SOCIAL_FORCES_MAX_INTERACTION_DISTANCE
+    pb.pf_theta_max = constants.POTENTIAL_FIELD_MAX_THETA / 180.0 * math.pi
+    pb.particle_noise = constants.ENV_PARTICLE_NOISE
+    pb.var_initial = constants.ENV_VAR_INITIAL
+    pb.kalman_noise = constants.KALMAN_ADDITIVE_NOISE
+    pb.ego0 = _cabi.ptr(scene.ego0)
+    pb.ado0 = _cabi.ptr(scene.ado0)
+    pb.ado_goal = _cabi.ptr(scene.ado_goal)
+    pb.v0 = _cabi.ptr(scene.v0)
+    pb.sigma = _cabi.ptr(scene.sigma)
+    pb.weight = _cabi.ptr(scene.weight)
+    pb.noise = _cabi.ptr(scene.noise)
+    pb.controls = _cabi.ptr(controls)
+    return pb
+
+
+def _module_struct(scene: SceneBatch, spec: ModuleSpec) -> _cabi.MtbModules:
+    md = _cabi.MtbModules()
+    w = spec.weights
+    md.w_goal = w.get("goal", 0.0) / scene.axes_diag
+    md.w_acc = w.get("acc", 0.0) / constants.OBJECTIVE_ACC_INTERACT_MAX
+    md.w_vel = w.get("vel", 0.0) / constants.OBJECTIVE_VEL_INTERACT_MAX
+    md.w_pos = w.get("pos", 0.0) / constants.OBJECTIVE_POS_INTERACT_MAX
+    md.max_acc = constants.OBJECTIVE_ACC_INTERACT_MAX
+    md.max_vel = constants.OBJECTIVE_VEL_INTERACT_MAX
+    md.max_pos = constants.OBJECTIVE_POS_INTERACT_MAX
+    md.ego_goal = _cabi.ptr(scene.ego_goal)
+    md.mus_wo = _cabi.ptr(spec.mus_wo)
+    md.ado_mask = _cabi.ptr(spec.ado_mask, dtype=torch.uint8)
+    md.con_control = int(spec.control_limits)
+    md.con_speed = int(spec.speed_limits)
+    md.con_min_distance = int(spec.min_distance)
+    md.u_max, md.v_max, md.min_distance = spec.u_max, spec.v_max, spec.d_min
+    md.violation_eps = constants.CONSTRAINT_VIOLATION_PRECISION
+    return md
+
+
+OUTPUT_SHAPES = {
+    "obj": lambda s, c, t, n, r: (s, c, 4), "obj_raw": lambda s, c, t, n, r: (s, c, 4),
+    "total": lambda s, c, t, n, r: (s, c), "grad": lambda s, c, t, n, r: (s, c, t, 2),
+    "cons": lambda s, c, t, n, r: (s, c, r), "violation": lambda s, c, t, n, r: (s, c),
+    "ego_traj": lambda s, c, t, n, r: (s, c, t + 1, 4), "mus": lambda s, c, t, n, r: (s, c, n, t, 4),
+    "sigmas": lambda s, c, t, n, r: (s, c, n, t, 2),
+}
+
+
+def launch_evaluate(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Optional[torch.Tensor],
+                    spec: typing.Optional[ModuleSpec], want: typing.Sequence[str], t_horizon: int = None,
+                    stream: int = 0, out: typing.Dict[str, torch.Tensor] = None, stats: torch.Tensor = None,
+                    workspace: torch.Tensor = None) -> typing.Dict[str, torch.Tensor]:
+    """One `mtb_evaluate` launch. controls [S,C,T,2] (None = rollout without ego, needs `t_horizon`).
+    `want` names the output arrays to produce (keys of OUTPUT_SHAPES); `out` may supply pre-allocated tensors."""
+    spec = spec if spec is not None else ModuleSpec()
+    if controls is not None:
+        t_horizon = controls.shape[2]
+    pb = _problem_struct(scene, controls, t_horizon)
+    md = _module_struct(scene, spec)
+    rows = lib.mtb_num_constraint_rows(ctypes.byref(pb), ctypes.byref(md))
+    if rows < 0:
+        _cabi.check(lib, rows, "mtb_num_constraint_rows")
+    s, c, n = pb.num_scenes, pb.num_candidates, pb.num_ados
+    res = {} if out is None else dict(out)
+    outs = _cabi.MtbOutputs()
+    for key in want:
+        if key not in res:
+            res[key] = torch.empty(OUTPUT_SHAPES[key](s, c, t_horizon, n, rows), dtype=torch.float32, device=scene.device)
+        setattr(outs, key, _cabi.ptr(res[key]))
+    if stats is not None:
+        outs.stats = _cabi.ptr(stats, dtype=torch.int64)
+    need = lib.mtb_workspace_bytes(ctypes.byref(pb), int("grad" in want))
+    ws_ptr, ws_bytes = None, 0
+    if need > 0:
+        if workspace is None or workspace.numel() * workspace.element_size() < need:
+            workspace = torch.empty(need, dtype=torch.uint8, device=scene.device)
+        res["_workspace"] = workspace
+        ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    code = lib.mtb_evaluate(ctypes.byref(pb), ctypes.byref(md), ctypes.byref(outs), ws_ptr, ws_bytes, stream)
+    _cabi.check(lib, code, "mtb_evaluate")
+    return res
+
+
+def query_launch(lib: ctypes.CDLL, scene: SceneBatch, controls: torch.Tensor, want_grad: bool) -> typing.Dict[str, int]:
+    pb = _problem_struct(scene, controls, controls.shape[2])
+    info = _cabi.MtbLaunchInfo()
+    _cabi.check(lib, lib.mtb_query_launch(ctypes.byref(pb), int(want_grad), ctypes.byref(info)), "mtb_query_launch")
+    return {name: getattr(info, name) for name, _ in info._fields_}
+
+
+def launch_argmin(lib: ctypes.CDLL, total: torch.Tensor, violation: typing.Optional[torch.Tensor],
+                  controls: typing.Optional[torch.Tensor], feas_tol: float, stream: int = 0):
+    """Per scene: best feasible candidate (index -1 when none is feasible)."""
+    s, c = total.shape
+    best_idx = torch.empty(s, dtype=torch.int32, device=total.device)
+    best_val = torch.empty(s, dtype=torch.float32, device=total.device)
+    t_horizon = 0 if controls is None else controls.shape[2]
+    best_controls = None if controls is None else torch.empty((s, t_horizon, 2), dtype=torch.float32, device=total.device)
+    code = lib.mtb_argmin(_cabi.ptr(total), _cabi.ptr(violation), s, c, feas_tol, _cabi.ptr(controls), t_horizon,
+                          _cabi.ptr(best_idx, dtype=torch.int32), _cabi.ptr(best_val), _cabi.ptr(best_controls), stream)
+    _cabi.check(lib, code, "mtb_argmin")
+    return best_idx, best_val, best_controls
+
+
+class Engine:
+    """The product entry point of the batched hot path: binds the CUDA library (no fallback) and counts launches."""
+
+    def __init__(self, device: typing.Union[str, torch.device] = "cuda:0"):
+        from . import _lib
+        if not torch.cuda.is_available():
+            raise RuntimeError("mantrap_b200 needs a CUDA device (there is no CPU path)")
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        self.launches = 0
+        self._workspace = None
+
+    def _check(self, *tensors):
+        for t in tensors:
+            if t is not None and not t.is_cuda:
+                raise RuntimeError("mantrap_b200.Engine only accepts CUDA tensors")
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def evaluate(self, scene: SceneBatch, controls: torch.Tensor, spec: ModuleSpec = None,
+                 want: typing.Sequence[str] = ("obj", "total", "grad"), out=None, stats=None):
+        self._check(scene.ado0, controls)
+        with torch.cuda.device(self.device):
+            res = launch_evaluate(self.lib, scene, controls, spec, want, stream=self._stream(), out=out, stats=stats,
+                                  workspace=self._workspace)
+        self._workspace = res.pop("_workspace", self._workspace)
+        self.launches += 1
+        return res
+
+    def rollout_wo_ego(self, scene: SceneBatch, t_horizon: int, want=("mus", "sigmas")):
+        """Ego-free prediction (`compute_distributions_wo_ego`): mus [S,N,T,4], sigmas [S,N,T,2]."""
+        self._check(scene.ado0)
+        with torch.cuda.device(self.device):
+            res = launch_evaluate(self.lib, scene.without_ego(), None, None, want, t_horizon=t_horizon, stream=self._stream())
+        self.launches += 1
+        return {k: v[:, 0] for k, v in res.items() if not k.startswith("_")}
+
+    def argmin(self, total, violation, controls, feas_tol: float = constants.SOLVER_CONSTRAINT_LIMIT):
+        self._check(total, violation, controls)
+        with torch.cuda.device(self.device):
+            out = launch_argmin(self.lib, total, violation, controls, feas_tol, stream=self._stream())
+        self.launches += 1
+        return out
+
+    def launch_info(self, scene: SceneBatch, controls: torch.Tensor, want_grad: bool = True):
+        return query_launch(self.lib, scene, controls, want_grad)

@@ -1,0 +1,159 @@
+"""Shared body of the kernel parity tests. The same checks run
+  * on the CPU against the host emulation of the kernel source (tests/test_kernel_emulation.py, no GPU needed),
+  * on the B200 through the real C-ABI library (tests/test_gpu_parity.py, -m gpu).
+`lib` is a bound C-ABI library, `device` where the tensors live."""
+import numpy as np
+import torch
+
+import golden_io as gio
+from mantrap_b200 import engine
+
+MODULE_WEIGHT = {"goal": 0.5, "acc": 1.0, "vel": 1.0, "pos": 1.0}
+
+
+def scene_from_golden(g, device, wo=False):
+    tag = "_wo" if wo else ""
+    env = str(g["env"])
+    kw = {}
+    if env != "kalman":
+        kw = dict(v0=gio.t(g["v0" + tag])[None], sigma=gio.t(g["sigma" + tag])[None],
+                  weight=gio.t(g["weights" + tag])[None], noise=gio.t(g["noise" + tag])[None])
+    scene = engine.SceneBatch(env_kind=env, ego_kind=str(g["ego_kind"]), dt=float(g["dt"]), ego0=gio.t(g["ego0"])[None],
+                              ego_goal=gio.t(g["ego_goal"])[None], ado0=gio.t(g["ado0"])[None],
+                              ado_goal=gio.t(g["goal"])[None], **kw)
+    return scene.to(device)
+
+
+def np_(x):
+    return x.detach().cpu().numpy()
+
+
+def check_rollout(lib, device, name):
+    g = gio.load(name)
+    scene = scene_from_golden(g, device)
+    controls = gio.t(g["controls"])[None, None].to(device).contiguous()
+    res = engine.launch_evaluate(lib, scene, controls, None, want=("ego_traj", "mus", "sigmas"))
+    if device != "cpu":
+        torch.cuda.synchronize()
+    gio.assert_parity(np_(res["ego_traj"][0, 0]), g["ego_traj"][:, :4], gio.RTOL_ROLLOUT, "ego_traj")
+    gio.assert_parity(np_(res["mus"][0, 0, ..., 0:2]), g["mus"][..., 0:2], gio.RTOL_ROLLOUT, "mu_p")
+    gio.assert_parity(np_(res["mus"][0, 0, ..., 2:4]), g["mus"][..., 2:4], gio.RTOL_ROLLOUT, "mu_v")
+    gio.assert_parity(np_(res["sigmas"][0, 0]), g["sigmas"], gio.RTOL_ROLLOUT, "sigmas")
+    # rollout without ego (compute_distributions_wo_ego)
+    scene_wo = scene_from_golden(g, device, wo=True)
+    res = engine.launch_evaluate(lib, scene_wo, None, None, want=("mus", "sigmas"), t_horizon=int(g["T"]))
+    if device != "cpu":
+        torch.cuda.synchronize()
+    gio.assert_parity(np_(res["mus"][0, 0]), g["mus_wo"], gio.RTOL_ROLLOUT, "mus_wo")
+    gio.assert_parity(np_(res["sigmas"][0, 0]), g["sigmas_wo"], gio.RTOL_ROLLOUT, "sigmas_wo")
+
+
+def check_modules(lib, device, name):
+    g = gio.load(name)
+    scene = scene_from_golden(g, device)
+    controls = gio.t(g["controls"])[None, None].to(device).contiguous()
+    mus_wo = gio.t(g["mus_wo"])[None].to(device).contiguous()
+    n = g["ado0"].shape[0]
+    worst = {}
+    for key in engine.OBJECTIVE_KEYS:
+        if f"obj_{key}" not in g:
+            continue
+        for suffix in ("", "_sub2"):
+            if f"obj_{key}{suffix}" not in g:
+                continue
+            mask = None
+            if suffix:
+                mask = (torch.arange(n)[None] < 2).to(torch.uint8).to(device).contiguous()
+            spec = engine.ModuleSpec(weights={key: MODULE_WEIGHT[key]}, mus_wo=mus_wo, ado_mask=mask)
+            res = engine.launch_evaluate(lib, scene, controls, spec, want=("obj", "obj_raw", "total", "grad"))
+            if device != "cpu":
+                torch.cuda.synchronize()
+            col = engine.OBJECTIVE_KEYS.index(key)
+            e1 = gio.assert_parity(np_(res["obj"][0, 0, col]), g[f"obj_{key}{suffix}"], gio.RTOL_ROLLOUT, f"obj_{key}{suffix}", atol=gio.ATOL_OBJ)
+            gio.assert_parity(np_(res["total"][0, 0]), g[f"obj_{key}{suffix}"], gio.RTOL_ROLLOUT, f"total_{key}{suffix}", atol=gio.ATOL_OBJ)
+            e2 = gio.assert_parity(np_(res["grad"][0, 0]).flatten(), g[f"grad_{key}{suffix}"], gio.RTOL_GRAD, f"grad_{key}{suffix}")
+            if suffix == "" and key != "goal":
+                gio.assert_parity(np_(res["obj_raw"][0, 0, col]), g[f"raw_{key}"], gio.RTOL_ROLLOUT, f"raw_{key}", atol=gio.ATOL_OBJ)
+            worst[key + suffix] = (e1, e2)
+    return worst
+
+
+def check_constraints(lib, device, name):
+    g = gio.load(name)
+    scene = scene_from_golden(g, device)
+    t_hor = int(g["T"])
+    controls = gio.t(g["controls"])[None, None].to(device).contiguous()
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance="con_min_distance" in g)
+    res = engine.launch_evaluate(lib, scene, controls, spec, want=("cons", "violation"))
+    if device != "cpu":
+        torch.cuda.synchronize()
+    cons = np_(res["cons"][0, 0])
+    n_ctl = g["con_control_limits"].shape[0]
+    gio.assert_parity(cons[:n_ctl], g["con_control_limits"], gio.RTOL_ROLLOUT, "control rows")
+    gio.assert_parity(cons[n_ctl:n_ctl + 2 * (t_hor + 1)], g["con_speed_limits"], gio.RTOL_ROLLOUT, "speed rows")
+    expect_vio = float(g["vio_control_limits"]) + float(g["vio_speed_limits"])
+    if "con_min_distance" in g:
+        gio.assert_parity(cons[n_ctl + 2 * (t_hor + 1):], g["con_min_distance"], gio.RTOL_ROLLOUT, "min-distance rows")
+        expect_vio += float(np.maximum(0.5 - g["con_min_distance"], 0).sum())
+    gio.assert_parity(np_(res["violation"][0, 0]), expect_vio, 1e-4, "violation", atol=1e-6)
+
+
+def oracle_scene(scene, num_candidates):
+    """Expand a SceneBatch (CPU copy) to the oracle's per-evaluation batch layout [S*C, ...]."""
+    from oracle import torch_oracle as to
+
+    def rep(x):
+        return None if x is None else x.detach().cpu().repeat_interleave(num_candidates, dim=0)
+    sc = scene.to("cpu")
+    n, p = sc.num_ados, sc.num_particles
+    ones = torch.ones((sc.num_scenes, n, p))
+    return to.Scene(sc.env_kind, sc.ego_kind, sc.dt, rep(sc.ego0), rep(sc.ego_goal), rep(sc.ado0),
+                    rep(sc.ado_goal if sc.ado_goal is not None else torch.zeros((sc.num_scenes, n, 2))),
+                    rep(sc.v0 if sc.v0 is not None else ones), rep(sc.sigma if sc.sigma is not None else ones),
+                    rep(sc.weight if sc.weight is not None else ones), rep(sc.noise), sc.axes_diag)
+
+
+def check_batched_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, weights,
+                            seed=0, rtol_roll=gio.RTOL_ROLLOUT, rtol_grad=gio.RTOL_GRAD):
+    """Random batch (S scenes x C candidates) through the kernel vs. the CPU oracle on the same inputs."""
+    from oracle import torch_oracle as to
+    from mantrap_b200 import scenarios
+    scene_cpu = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=100 + seed,
+                                           param_seed=200 + seed, regular_sigma=True)
+    controls_cpu = scenarios.candidate_controls(num_scenes, num_candidates, t_hor, seed=300 + seed, u_max=1.0)
+    scene = scene_cpu.to(device)
+    controls = controls_cpu.to(device).contiguous()
+    # ego-free baseline from the kernel itself, checked against the oracle
+    res_wo = engine.launch_evaluate(lib, scene.without_ego(), None, None, want=("mus",), t_horizon=t_hor)
+    mus_wo = res_wo["mus"][:, 0].contiguous()
+    osc1 = oracle_scene(scene_cpu, 1)
+    if env_kind != "kalman":
+        ref_wo, _ = to.rollout(env_kind, osc1.ado0, osc1.goal, osc1.v0, osc1.sigma, osc1.weights, None, t_hor, scene_cpu.dt)
+        gio.assert_parity(np_(mus_wo), ref_wo.numpy(), rtol_roll, "mus_wo")
+    spec = engine.ModuleSpec(weights=weights, mus_wo=mus_wo, control_limits=True, speed_limits=True, min_distance=True)
+    stats = torch.zeros(4, dtype=torch.int64, device=device)
+    res = engine.launch_evaluate(lib, scene, controls, spec, want=("obj", "obj_raw", "total", "grad", "mus", "sigmas", "violation", "cons"),
+                                 stats=stats)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    osc = oracle_scene(scene_cpu, num_candidates)
+    ref = to.evaluate(osc, controls_cpu.reshape(-1, t_hor, 2), mus_wo.detach().cpu().repeat_interleave(num_candidates, dim=0), weights)
+    b = num_scenes * num_candidates
+    gio.assert_parity(np_(res["mus"]).reshape(b, n, t_hor, 4), ref["mus"].numpy(), rtol_roll, "mus")
+    if env_kind != "kalman":
+        gio.assert_parity(np_(res["sigmas"]).reshape(b, n, t_hor, 2), ref["sigmas"].numpy(), rtol_roll, "sigmas")
+    gio.assert_parity(np_(res["obj"]).reshape(b, 4), ref["obj"].numpy(), rtol_roll, "obj", atol=gio.ATOL_OBJ)
+    gio.assert_parity(np_(res["total"]).reshape(b), ref["total"].numpy(), rtol_roll, "total", atol=gio.ATOL_OBJ)
+    gio.assert_parity(np_(res["grad"]).reshape(b, t_hor, 2), ref["grad"].numpy(), rtol_grad, "grad")
+    # constraint rows
+    et = ref["ego_traj"]
+    rows = [to.control_limit_raw(et, scene_cpu.dt, ego_kind) / to.ROBOT_ACC_MAX, to.speed_limit_raw(et) / to.ROBOT_SPEED_MAX,
+            to.min_distance_raw(et, ref["mus"]).flatten(start_dim=1)]
+    ref_cons = torch.cat(rows, dim=1).numpy()
+    gio.assert_parity(np_(res["cons"]).reshape(b, -1), ref_cons, rtol_roll, "cons")
+    n_ctl = rows[0].shape[1]
+    n_spd = rows[1].shape[1]
+    vio = to.violation(ref_cons[:, :n_ctl], None, 1.0) + to.violation(ref_cons[:, n_ctl:n_ctl + n_spd], -1.0, 1.0) + \
+        to.violation(ref_cons[:, n_ctl + n_spd:], to.MIN_L2_DISTANCE, None)
+    gio.assert_parity(np_(res["violation"]).reshape(b), vio, 1e-4, "violation", atol=1e-5)
+    return res, ref, stats

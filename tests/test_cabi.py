@@ -1,0 +1,52 @@
+"""CPU tests of the boundary: the CUDA library builds for sm_100a, loads, and exports every symbol that
+include/mantrap_b200.h declares (no compute calls here: there is no GPU in the build container)."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+
+from mantrap_b200 import _cabi, build
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib_path():
+    return build.build()
+
+
+def test_header_symbols_exported(lib_path):
+    header = open(os.path.join(ROOT, "include", "mantrap_b200.h")).read()
+    declared = set(re.findall(r"\b(mtb_[a-z_]+)\s*\(", header))
+    assert declared == set(_cabi.EXPORTED_SYMBOLS), declared ^ set(_cabi.EXPORTED_SYMBOLS)
+    lib = _cabi.bind(ctypes.CDLL(lib_path))
+    assert lib.mtb_abi_version() == 1
+    assert b"bad argument" in lib.mtb_error_string(-1)
+
+
+def test_struct_sizes_match_header(lib_path, tmp_path):
+    """sizeof of the ctypes mirrors == sizeof of the C structs (compiled with gcc from the public header)."""
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "mantrap_b200.h"\nint main(){printf("%zu %zu %zu %zu\\n",'
+                   "sizeof(mtb_problem),sizeof(mtb_modules),sizeof(mtb_outputs),sizeof(mtb_launch_info));return 0;}\n")
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    assert sizes == [ctypes.sizeof(_cabi.MtbProblem), ctypes.sizeof(_cabi.MtbModules), ctypes.sizeof(_cabi.MtbOutputs),
+                     ctypes.sizeof(_cabi.MtbLaunchInfo)]
+
+
+def test_sass_is_sm100(lib_path):
+    out = subprocess.run(["cuobjdump", "-lelf", lib_path], capture_output=True, text=True).stdout
+    assert "sm_100a" in out, out
+
+
+def test_engine_requires_gpu():
+    import torch
+    from mantrap_b200 import engine
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(RuntimeError):
+        engine.Engine()

@@ -1,0 +1,107 @@
+"""GPU parity tests (run with -m gpu on the B200): the CUDA library, through the C ABI, against
+  * the golden vectors recorded from the unmodified reference (tests/golden/*.npz),
+  * the CPU oracle on seeded random batches,
+  * size-independent properties at the full BASELINE sizes."""
+import numpy as np
+import pytest
+import torch
+
+import golden_io as gio
+import kernel_cases as kc
+from mantrap_b200 import engine, scenarios
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from mantrap_b200 import build
+    build.build()
+    return engine.Engine(DEV)
+
+
+@pytest.mark.parametrize("name", gio.case_names())
+def test_rollout_golden(eng, name):
+    kc.check_rollout(eng.lib, DEV, name)
+
+
+@pytest.mark.parametrize("name", gio.case_names())
+def test_modules_golden(eng, name):
+    kc.check_modules(eng.lib, DEV, name)
+
+
+@pytest.mark.parametrize("name", gio.case_names())
+def test_constraints_golden(eng, name):
+    kc.check_constraints(eng.lib, DEV, name)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor,weights", [
+    ("sf", "double", 5, 37, 4, 3, 10, {"goal": 0.5, "acc": 1.0}),
+    ("sf", "single", 3, 9, 12, 3, 8, {"goal": 0.5, "vel": 1.0, "pos": 1.0}),
+    ("sf", "double", 4, 16, 20, 3, 12, {"goal": 0.5, "acc": 1.0}),           # config-4 shape
+    ("sf", "double", 2, 8, 10, 4, 20, {"goal": 0.5, "pos": 1.0, "acc": 1.0}),  # config-3 shape
+    ("sf", "double", 2, 3, 33, 2, 6, {"goal": 0.5, "acc": 1.0}),             # two mask words
+    ("pf", "double", 2, 64, 5, 5, 15, {"goal": 0.5, "acc": 1.0, "vel": 1.0}),  # config-2 shape
+    ("pf", "single", 3, 7, 7, 2, 9, {"goal": 0.5, "pos": 1.0}),
+    ("kalman", "double", 2, 5, 5, 1, 15, {"goal": 0.5, "acc": 1.0}),
+])
+def test_batched_vs_oracle(eng, env_kind, ego_kind, s, c, n, p, t_hor, weights):
+    kc.check_batched_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)
+
+
+def test_argmin(eng):
+    total = torch.tensor([[3.0, 1.0, 2.0, 0.5], [4.0, -1.0, 5.0, 6.0], [1.0, 2.0, 3.0, 4.0]], device=DEV)
+    vio = torch.tensor([[0.0, 0.0, 0.0, 1.0], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]], device=DEV)
+    controls = torch.arange(3 * 4 * 2 * 2, dtype=torch.float32, device=DEV).reshape(3, 4, 2, 2).contiguous()
+    idx, val, best = eng.argmin(total, vio, controls, 1e-3)
+    assert idx.tolist() == [1, 0, -1]
+    assert torch.equal(best[0], controls[0, 1]) and torch.equal(best[1], controls[1, 0])
+
+
+def test_full_size_properties(eng):
+    """Config-4 shape at a large batch: properties that do not need the oracle.
+    (1) duplicated candidates give bit-identical results wherever they land in the grid (objectives; gradients up to
+        the order of shared-memory atomics), (2) the interaction gradient w.r.t. the last two controls of a double
+        integrator is exactly zero, (3) total == sum of module objectives, (4) argmin picks the minimum of
+        the feasible set, (5) sampled evaluations agree with the CPU oracle."""
+    s, c, n, p, t_hor = 512, 256, 20, 3, 12
+    scene_cpu = scenarios.synthetic_scenes(s, n, p, regular_sigma=True)
+    scene = scene_cpu.to(DEV)
+    controls_cpu = scenarios.candidate_controls(s, c, t_hor)
+    controls_cpu[:, c // 2:] = controls_cpu[:, :c // 2]           # second half duplicates the first
+    controls = controls_cpu.to(DEV)
+    mus_wo = eng.rollout_wo_ego(scene, t_hor)["mus"].contiguous()
+    spec = engine.ModuleSpec(weights={"acc": 1.0}, mus_wo=mus_wo, control_limits=True, speed_limits=True)
+    res = eng.evaluate(scene, controls, spec, want=("obj", "obj_raw", "total", "grad", "violation"))
+    torch.cuda.synchronize()
+    total, grad = res["total"], res["grad"]
+    assert torch.equal(total[:, :c // 2], total[:, c // 2:])
+    assert torch.allclose(grad[:, :c // 2], grad[:, c // 2:], rtol=1e-4, atol=1e-7)
+    assert torch.count_nonzero(grad[:, :, -2:, :]) == 0
+    assert float(grad.abs().max()) > 0 and bool(torch.isfinite(grad).all())
+    assert torch.allclose(total, res["obj"].sum(dim=-1), rtol=1e-6, atol=1e-7)
+    idx, val, _ = eng.argmin(total, res["violation"], controls)
+    feas = res["violation"] < 1e-3
+    masked = torch.where(feas, total, torch.full_like(total, float("inf")))
+    assert torch.equal(val, masked.min(dim=1).values)
+    # sampled evaluations against the oracle
+    from oracle import torch_oracle as to
+    pick_s = torch.tensor([0, 17, 255, 511])
+    pick_c = torch.tensor([0, 3, 100, 127])
+    sub = engine.SceneBatch(**{**scene_cpu.__dict__, **{k: getattr(scene_cpu, k)[pick_s] for k in
+                            ("ego0", "ego_goal", "ado0", "ado_goal", "v0", "sigma", "weight")}})
+    osc = kc.oracle_scene(sub, len(pick_c))
+    ref = to.evaluate(osc, controls_cpu[pick_s][:, pick_c].reshape(-1, t_hor, 2),
+                      mus_wo[pick_s.to(DEV)].cpu().repeat_interleave(len(pick_c), dim=0), {"acc": 1.0})
+    got_total = total[pick_s.to(DEV)][:, pick_c.to(DEV)].reshape(-1).cpu().numpy()
+    got_grad = grad[pick_s.to(DEV)][:, pick_c.to(DEV)].reshape(-1, t_hor, 2).cpu().numpy()
+    gio.assert_parity(got_total, ref["total"].numpy(), gio.RTOL_ROLLOUT, "sampled total", atol=gio.ATOL_OBJ)
+    unsat = ref["raw"][:, 1].numpy() < 1.0
+    gio.assert_parity(got_grad[unsat], ref["grad"].numpy()[unsat], gio.RTOL_GRAD, "sampled grad")
+
+
+def test_rejects_cpu_tensors(eng):
+    scene = scenarios.synthetic_scenes(1, 3, 2)
+    with pytest.raises(RuntimeError):
+        eng.evaluate(scene, scenarios.candidate_controls(1, 1, 4), None, want=("total",))

@@ -1,0 +1,61 @@
+"""CPU tests of the ACTUAL kernel source: `mantrap_b200/csrc/mtb_kernels.cu` compiled with g++ against the host
+emulation shim (tests/host_emul/cuda_shim.h; every CUDA thread = one OS thread) and driven through the same
+C ABI as the CUDA library. Catches indexing / synchronisation / adjoint bugs without a GPU; the GPU run of the same
+checks is tests/test_gpu_parity.py."""
+import ctypes
+import os
+import sys
+
+import pytest
+import torch
+
+import golden_io as gio
+import kernel_cases as kc
+from mantrap_b200 import _cabi, engine
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "host_emul"))
+import build_emul  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def emul_lib():
+    return _cabi.bind(ctypes.CDLL(build_emul.build()))
+
+
+def test_exports(emul_lib):
+    assert emul_lib.mtb_abi_version() == 1
+
+
+@pytest.mark.parametrize("name", gio.case_names())
+def test_rollout(emul_lib, name):
+    kc.check_rollout(emul_lib, "cpu", name)
+
+
+@pytest.mark.parametrize("name", gio.case_names())
+def test_modules(emul_lib, name):
+    kc.check_modules(emul_lib, "cpu", name)
+
+
+@pytest.mark.parametrize("name", gio.case_names())
+def test_constraints(emul_lib, name):
+    kc.check_constraints(emul_lib, "cpu", name)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor,weights", [
+    ("sf", "double", 3, 5, 4, 3, 6, {"goal": 0.5, "acc": 1.0}),            # sub-warp groups, partial last item
+    ("sf", "single", 2, 3, 12, 3, 5, {"goal": 0.5, "vel": 1.0, "pos": 1.0}),  # two warps per evaluation
+    ("pf", "double", 2, 4, 5, 5, 7, {"goal": 0.5, "acc": 1.0, "vel": 1.0}),
+    ("kalman", "double", 2, 3, 5, 1, 6, {"goal": 0.5, "acc": 1.0}),
+])
+def test_batched_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor, weights):
+    kc.check_batched_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights)
+
+
+def test_argmin(emul_lib):
+    total = torch.tensor([[3.0, 1.0, 2.0, 0.5], [4.0, -1.0, 5.0, 6.0], [1.0, 2.0, 3.0, 4.0]])
+    vio = torch.tensor([[0.0, 0.0, 0.0, 1.0], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]])
+    controls = torch.arange(3 * 4 * 2 * 2, dtype=torch.float32).reshape(3, 4, 2, 2).contiguous()
+    idx, val, best = engine.launch_argmin(emul_lib, total, vio, controls, 1e-3)
+    assert idx.tolist() == [1, 0, -1]
+    assert val[:2].tolist() == [1.0, 4.0] and torch.isinf(val[2])
+    assert torch.equal(best[0], controls[0, 1]) and torch.equal(best[1], controls[1, 0])
