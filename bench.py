@@ -1,0 +1,344 @@
+"""Benchmark of the mantrap_b200 hot path: rollout + objective + control-gradient evaluations per second.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (N>1: launched by torchrun)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference algorithm on the host CPU cores
+
+Workload (BASELINE.json config 4, "synthetic ETH-shaped scenes"): social-forces environment, 20 pedestrians x 3
+particles, t_planning = 12, dt = 0.4 s, double-integrator ego, goal + interaction-acceleration objectives, 256 random
+control candidates per scene, 8192 scenes PER GPU (65536 scenes x 256 candidates on 8 GPUs; weak scaling). One step =
+one pass of the hot path over the rank's whole batch: fused rollout/objective/adjoint kernel + per-scene argmin of the
+best feasible candidate (+ one small NCCL all-gather of the winners when N > 1).
+
+The JSON line follows the driver contract; see DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_ADOS, N_PARTICLES, T_HORIZON, N_CANDIDATES = 20, 3, 12, 256
+WEIGHTS = {"goal": 0.5, "acc": 1.0}
+METRIC = "rollout+gradient evals/sec (scenes x candidates)"
+UNIT = "evals/s"
+
+
+def flops_per_eval(t_hor, n, p):
+    """Algorithmic work model of SURVEY §8(d): 150 (T-1) N P (N+1) FLOP per social-forces evaluation
+    (forward 50 FLOP per pair term incl. 7 SFU ops, reverse sweep counted 2x)."""
+    return 150.0 * (t_hor - 1) * n * p * (n + 1)
+
+
+def sfu_per_eval(t_hor, n, p):
+    return 3.0 * (t_hor - 1) * n * p * (7 * n + 5)
+
+
+def bytes_per_eval(t_hor, n_mod):
+    return 16.0 * t_hor + 4.0 * n_mod
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference algorithm on the host cores (cpu_baseline and --impl reference)
+# ---------------------------------------------------------------------------------------------------------------
+def _cpu_worker(args):
+    worker, n_batches, batch, seed = args
+    import torch
+    torch.set_num_threads(1)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle import torch_oracle as to
+    from mantrap_b200 import scenarios
+    import kernel_cases as kc
+    scene = scenarios.synthetic_scenes(batch, N_ADOS, N_PARTICLES, seed=seed + worker, param_seed=seed + 1000 + worker)
+    controls = scenarios.candidate_controls(batch, 1, T_HORIZON, seed=seed + 2000 + worker)[:, 0]
+    osc = kc.oracle_scene(scene, 1)
+    mus_wo, _ = to.rollout("sf", osc.ado0, osc.goal, osc.v0, osc.sigma, osc.weights, None, T_HORIZON, scene.dt)
+    t0 = time.perf_counter()
+    for _ in range(n_batches):
+        to.evaluate(osc, controls, mus_wo, WEIGHTS)
+    return time.perf_counter() - t0
+
+
+def cpu_arm(seconds_target=12.0, batch=32, workers=None):
+    """Times the CPU oracle (vectorised float32 torch port of the reference algorithm, one process per core, one
+    thread each) on a bounded sample of the bench workload. Returns (evals/s, cores, description)."""
+    import multiprocessing as mp
+    workers = workers or os.cpu_count() or 1
+    ctx = mp.get_context("fork")
+    with ctx.Pool(workers) as pool:
+        warm = pool.map(_cpu_worker, [(w, 1, batch, 7) for w in range(workers)])
+        per_batch = max(warm)
+        n_batches = max(1, int(seconds_target / per_batch))
+        t0 = time.perf_counter()
+        pool.map(_cpu_worker, [(w, n_batches, batch, 7) for w in range(workers)])
+        wall = time.perf_counter() - t0
+    evals = workers * n_batches * batch
+    sample = (f"{evals} evaluations of the bench workload (SF N={N_ADOS} P={N_PARTICLES} T={T_HORIZON}, goal+acc objective "
+              f"+ autograd gradient) = {workers} processes x {n_batches} batches x {batch}, wall {wall:.1f} s")
+    return evals / wall, workers, sample
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    values = []
+    sample = ""
+    cores = os.cpu_count() or 1
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        cpu_arm(seconds_target=2.0)
+    t0 = time.perf_counter()
+    for _ in range(max(1, args.steps)):
+        v, cores, sample = cpu_arm(seconds_target=max(2.0, 40.0 / max(1, args.steps)))
+        values.append(v)
+    value = sum(values) / len(values)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": (time.perf_counter() - t0) * 1e3 / max(1, args.steps),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference algorithm = oracle/torch_oracle.py (the Python reference cannot travel to the GPU box; "
+                "its own per-call cost is ~0.3 evals/s/core, BASELINE.md §2)",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def workload_config(args, world):
+    return {"workload": f"BASELINE config 4 (ETH-shaped): SocialForces N={N_ADOS} ados x P={N_PARTICLES} particles, "
+                        f"t_planning={T_HORIZON}, dt=0.4, double-integrator ego, goal+interaction-acceleration objective, "
+                        f"{args.scenes_per_gpu} scenes/GPU x {args.candidates} candidates",
+            "scenes_per_gpu": args.scenes_per_gpu, "candidates": args.candidates, "global_evals_per_step":
+                args.scenes_per_gpu * args.candidates * world, "parallelism": f"scene-sharded x{world}",
+            "cache": "inputs+outputs per step (controls 96 B + gradient 96 B + 12 B per eval) exceed the 126 MB L2; "
+                     "no explicit flush"}
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit())
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 7:
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+        smax = max((float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()), default=None)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measure_peaks(eng, torch):
+    """FP32 FMA and MUFU throughput of this device (dependent chains, 8-way ILP, 16 warps... per SM)."""
+    lib, dev = eng.lib, eng.device
+    grid, iters = 148 * 16, 20000
+    out = torch.empty(grid * 256, dtype=torch.float32, device=dev)
+    res = {}
+    for kind, name, per_iter in ((0, "fp32_tflops", 16.0), (1, "mufu_tops", 8.0)):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        lib.mtb_probe_launch(kind, out.data_ptr(), grid, 100, stream)
+        best = 1e30
+        for _ in range(3):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            lib.mtb_probe_launch(kind, out.data_ptr(), grid, iters, stream)
+            b.record()
+            torch.cuda.synchronize(dev)
+            best = min(best, a.elapsed_time(b))
+        res[name] = grid * 256 * iters * per_iter / (best * 1e-3) / 1e12
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scenes-per-gpu", type=int, default=8192)
+    ap.add_argument("--candidates", type=int, default=N_CANDIDATES)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 and world == 1:      # convenience: re-launch under torchrun as the driver would
+        os.execvp(sys.executable, [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+                                   f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1", "--master-port", "29541",
+                                   os.path.abspath(__file__), *sys.argv[1:]])
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    # CPU baseline first (fork-based pool, before CUDA is initialised in this process); rank 0 at N = 1 only.
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        v, cores, sample = cpu_arm(seconds_target=12.0)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+
+    import torch
+    import torch.distributed as dist
+    from mantrap_b200 import api, build, engine, scenarios
+    build.build()
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    eng = engine.Engine(dev)
+
+    s_g, c, t_hor = args.scenes_per_gpu, args.candidates, T_HORIZON
+    scene = scenarios.synthetic_scenes(s_g, N_ADOS, N_PARTICLES, seed=1234 + rank, param_seed=5678 + rank).to(dev)
+    controls_host = scenarios.candidate_controls(s_g, c, t_hor, seed=4321 + rank, pinned=True)
+    controls = controls_host.to(dev)
+    mus_wo = eng.rollout_wo_ego(scene, t_hor)["mus"].contiguous()
+    spec = engine.ModuleSpec(weights=WEIGHTS, mus_wo=mus_wo, control_limits=True, speed_limits=True)
+    want = ("total", "grad", "violation")
+    stats = torch.zeros(4, dtype=torch.int64, device=dev)
+    bufs = eng.evaluate(scene, controls, spec, want=want, stats=stats)          # allocates outputs; counts pairs once
+    torch.cuda.synchronize(dev)
+    pair_stats = stats.tolist()
+    gathered = torch.empty((world, s_g, 2 + 2 * t_hor), dtype=torch.float32, device=dev) if world > 1 else None
+    launches_per_step = 2
+
+    def step(kernel_events=None):
+        if kernel_events is not None:
+            kernel_events[0].record()
+        eng.evaluate(scene, controls, spec, want=want, out=bufs)
+        if kernel_events is not None:
+            kernel_events[1].record()
+        idx, val, best = eng.argmin(bufs["total"], bufs["violation"], controls)
+        if world > 1:   # the only exchange on the path: every rank learns every scene's best candidate
+            packed = torch.cat((val[:, None], idx.float()[:, None], best.reshape(s_g, -1)), dim=1)
+            dist.all_gather_into_tensor(gathered, packed)
+        return idx, val, best
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        start.record()
+        for k in range(args.steps):
+            step(ev[k])
+        stop.record()
+        barrier()
+    ms_total = start.elapsed_time(stop)
+    kernel_ms = sum(a.elapsed_time(b) for a, b in ev) / args.steps
+    t_ms = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t_ms.item()) / args.steps
+    evals_per_step = s_g * c * world
+    value = evals_per_step / (ms_per_step * 1e-3)
+
+    # ---- end to end through the public host-buffer API: pinned controls in, results (objective, violation,
+    # gradient per evaluation + best candidate per scene) back to pinned host memory, every step.
+    host_out = api.HostBuffers(s_g, c, t_hor)
+    for _ in range(2):
+        api.evaluate_candidates_host(eng, scene, controls_host, spec, host_out, device_buffers=bufs, device_controls=controls)
+    barrier()
+    e_start, e_stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e_start.record()
+    for _ in range(args.steps):
+        api.evaluate_candidates_host(eng, scene, controls_host, spec, host_out, device_buffers=bufs, device_controls=controls)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, host_out.last_packed_device)
+    e_stop.record()
+    barrier()
+    e_ms = torch.tensor([e_start.elapsed_time(e_stop)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
+    e2e_value = evals_per_step / (float(e_ms.item()) / args.steps * 1e-3)
+
+    if rank == 0:
+        peaks = measure_peaks(eng, torch)
+        sm_clock = None
+        try:
+            measured = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            hbm_peak, peak_src = measured["hbm_gbs"], "MEASURED_PEAKS.json"
+            sm_clock = measured.get("sm_max_mhz")
+        except Exception:
+            hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        spec_fp32 = 2 * 148 * 128 * (sm_clock or 1965.0) * 1e6 / 1e12
+        fp32_peak = min(spec_fp32, peaks["fp32_tflops"])
+        evals_per_launch = s_g * c
+        f_eval = flops_per_eval(t_hor, N_ADOS, N_PARTICLES)
+        achieved = evals_per_launch * f_eval / (kernel_ms * 1e-3) / 1e12
+        # work actually executed: pairs inside the 2 m interaction radius + ego pairs (the reference skips the rest too)
+        exec_pairs = (pair_stats[0] + pair_stats[1]) / evals_per_launch
+        executed = evals_per_launch * exec_pairs * 150.0 / (kernel_ms * 1e-3) / 1e12
+        hbm_achieved = evals_per_launch * bytes_per_eval(t_hor, 3) / (kernel_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": workload_config(args, world),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": host_out.h2d_bytes(controls_host),
+                    "d2h_bytes_per_step": host_out.d2h_bytes()},
+            "gpu_launches": launches_per_step * args.steps,
+            "clocks": clocks.summary(),
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
+                         "frac": achieved / fp32_peak, "traffic": None,
+                         "kernel": "mtb::evaluate_kernel<SF, GRAD>", "kernel_ms": kernel_ms,
+                         "kernel_share_of_step": kernel_ms / ms_per_step,
+                         "work_model": "SURVEY 8(d): 150 (T-1) N P (N+1) FLOP per eval, all N+1 pair terms counted",
+                         "executed_tflops": executed, "executed_frac": executed / fp32_peak,
+                         "executed_pairs_per_eval": exec_pairs, "model_pairs_per_eval": (t_hor - 1) * N_ADOS * N_PARTICLES * (N_ADOS + 1),
+                         "peak_source": f"min(2*148*128*f_max = {spec_fp32:.1f}, measured FMA probe = {peaks['fp32_tflops']:.1f}) TFLOP/s",
+                         "mufu_frac": evals_per_launch * sfu_per_eval(t_hor, N_ADOS, N_PARTICLES) / (kernel_ms * 1e-3) / 1e12 / peaks["mufu_tops"],
+                         "mufu_peak_tops": peaks["mufu_tops"],
+                         "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
+                                 "peak_source": peak_src}},
+            "saturated_fraction": pair_stats[2] / evals_per_launch,
+            "launch": eng.launch_info(scene, controls, True),
+        }
+        if cpu_baseline is not None:
+            line["cpu_baseline"] = cpu_baseline
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

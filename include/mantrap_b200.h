@@ -143,6 +143,10 @@ int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, i
                float feas_tol, const float* controls, int32_t t_horizon, int32_t* best_idx, float* best_val,
                float* best_controls, void* stream);
 
+/* benchmark support: launches `grid` blocks of 256 threads running 8 dependent chains of `iters` FP32 FMAs
+ * (kind 0, 16*iters flop per thread) or MUFU rsqrt (kind 1, 8*iters ops per thread); out[grid*256] floats. */
+int mtb_probe_launch(int kind, float* out, int grid, int iters, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -46,7 +46,7 @@ class MtbLaunchInfo(ctypes.Structure):
 
 EXPORTED_SYMBOLS = ("mtb_abi_version", "mtb_error_string", "mtb_num_constraint_rows", "mtb_workspace_bytes",
                     "mtb_evaluate", "mtb_query_launch", "mtb_constraint_jacobian", "mtb_jacobian_workspace_bytes",
-                    "mtb_argmin")
+                    "mtb_argmin", "mtb_probe_launch")
 
 
 def bind(lib: ctypes.CDLL) -> ctypes.CDLL:
@@ -66,6 +66,8 @@ def bind(lib: ctypes.CDLL) -> ctypes.CDLL:
     lib.mtb_constraint_jacobian.restype = ctypes.c_int
     lib.mtb_constraint_jacobian.argtypes = [pp, pm, _p, _p, _p, ctypes.c_size_t, _p]
     lib.mtb_jacobian_workspace_bytes.restype, lib.mtb_jacobian_workspace_bytes.argtypes = ctypes.c_size_t, [pp]
+    lib.mtb_probe_launch.restype = ctypes.c_int
+    lib.mtb_probe_launch.argtypes = [ctypes.c_int, _p, ctypes.c_int, ctypes.c_int, _p]
     lib.mtb_argmin.restype = ctypes.c_int
     lib.mtb_argmin.argtypes = [_p, _p, _i, _i, _f, _p, _i, _p, _p, _p, _p]
     return lib

@@ -6,7 +6,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 LIB_PATH = os.path.join(HERE, "libmantrap_b200.so")
-SOURCES = [os.path.join(HERE, "csrc", name) for name in ("mtb_kernels.cu",)]
+SOURCES = [os.path.join(HERE, "csrc", name) for name in ("mtb_kernels.cu", "mtb_probe.cu")]
 DEPS = SOURCES + [os.path.join(HERE, "csrc", "mtb_math.cuh"), os.path.join(ROOT, "include", "mantrap_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
               "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]

@@ -957,4 +957,8 @@ int mtb_constraint_jacobian(const mtb_problem*, const mtb_modules*, float*, floa
     return MTB_ERR_BAD_ARGUMENT;   // implemented in mtb_jacobian.cu (forward-mode tangent kernel)
 }
 
+#ifdef MTB_HOST_EMUL
+int mtb_probe_launch(int, float*, int, int, void*) { return MTB_ERR_BAD_ARGUMENT; }   // CUDA-only benchmark helper
+#endif
+
 }  // extern "C"

@@ -55,7 +55,6 @@ def ego_unroll(x0: torch.Tensor, controls: torch.Tensor, dt: float, ego_kind: st
     :param x0: [..., 4] = (px, py, vx, vy), :param controls: [..., T, 2] -> trajectory [..., T+1, 4].
     """
     p0, v0 = x0[..., None, 0:2], x0[..., None, 2:4]
-    zeros = torch.zeros_like(controls[..., :1, :])
     if ego_kind == "double":
         v = torch.cat((v0, v0 + dt * torch.cumsum(controls, dim=-2)), dim=-2)          # [.., T+1, 2]
         p = torch.cat((p0, p0 + dt * torch.cumsum(v[..., :-1, :], dim=-2)), dim=-2)
@@ -64,7 +63,6 @@ def ego_unroll(x0: torch.Tensor, controls: torch.Tensor, dt: float, ego_kind: st
         p = torch.cat((p0, p0 + dt * torch.cumsum(controls, dim=-2)), dim=-2)
     else:
         raise ValueError(ego_kind)
-    del zeros
     return torch.cat((p, v), dim=-1)
 
 
@@ -114,7 +112,7 @@ def _repulsion(r, w, v0, sigma, dt, active):
     """Closed form of `_repulsive_force` (social_forces.py:94-126): F = dV/dr with V = v0 exp(-b/sigma),
     clamp to +-PED_SPEED_MAX element-wise (:122), NaN -> zeros(2) (:123-124).
     `active` masks pairs that the reference never evaluates (they must not contribute values or gradients)."""
-    safe_r = torch.tensor([1.0, 0.0])
+    safe_r = r.new_tensor([1.0, 0.0])
     r = torch.where(active, r, safe_r.expand_as(r))
     w = torch.where(active, w, torch.zeros_like(w))
 
@@ -182,7 +180,7 @@ def pf_controls(p, v, v0, ego_t):
     v0c = v0.clamp(min=1e-3)
     delta = ego_t[:, None, None, 0:2] - p
     theta = torch.atan2(v[..., 1:2], v[..., 0:1]) - torch.atan2(delta[..., 1:2], delta[..., 0:1])
-    gate = theta.detach().abs() < torch.tensor(PF_MAX_THETA / 180.0 * math.pi, dtype=torch.float32)
+    gate = theta.detach().abs() < torch.tensor(PF_MAX_THETA / 180.0 * math.pi, dtype=theta.dtype)
     impact = -v0c * torch.sign(delta) * torch.exp(-delta.abs())
     return v + torch.where(gate, impact, torch.zeros_like(impact))
 
@@ -202,11 +200,11 @@ def rollout(env_kind: str, ado0, goal, v0, sigma, weights, noise, ego_traj, dt, 
         t_horizon = ego_traj.shape[-2] - 1
     b, n = ado0.shape[0], ado0.shape[1]
     if env_kind == "kalman":
-        t = torch.arange(t_horizon, dtype=torch.float32)[None, None, :, None]
+        t = torch.arange(t_horizon, dtype=ado0.dtype)[None, None, :, None]
         mu_v = ado0[:, :, None, 2:4].expand(b, n, t_horizon, 2)
         mu_p = ado0[:, :, None, 0:2] + (t * dt) * ado0[:, :, None, 2:4]
         # P_k = F P F^T + Q with F = diag(1,1,0,0): velocity variance is reset to Q every step (kalman.py:79-92).
-        sig_v = torch.full((b, n, t_horizon, 2), KALMAN_ADDITIVE_NOISE)
+        sig_v = torch.full((b, n, t_horizon, 2), KALMAN_ADDITIVE_NOISE, dtype=ado0.dtype)
         sig_v[:, :, 0, :] = ENV_VAR_INITIAL
         return torch.cat((mu_p, mu_v), dim=-1), sig_v
 
@@ -215,7 +213,7 @@ def rollout(env_kind: str, ado0, goal, v0, sigma, weights, noise, ego_traj, dt, 
     v = ado0[:, :, None, 2:4].expand(b, n, num_p, 2)
     v0_, sigma_, w_ = v0[..., None], sigma[..., None], weights[..., None]
     mu_t = ado0[..., 0:4]
-    mus, sigmas = [mu_t], [torch.full((b, n, 2), ENV_VAR_INITIAL)]
+    mus, sigmas = [mu_t], [torch.full((b, n, 2), ENV_VAR_INITIAL, dtype=ado0.dtype)]
     for t in range(t_horizon - 1):
         ego_t = None if ego_traj is None else ego_traj[:, t, :]
         if env_kind == "sf":
@@ -314,6 +312,11 @@ def violation(values: np.ndarray, lower, upper) -> np.ndarray:
 ###########################################################################
 # Whole evaluations #######################################################
 ###########################################################################
+def scene_to(scene: "Scene", dtype) -> "Scene":
+    """Cast every tensor of a Scene (float64 copies are used to measure float32 conditioning in the tests)."""
+    return scene._replace(**{k: v.to(dtype) for k, v in scene._asdict().items() if isinstance(v, torch.Tensor)})
+
+
 class Scene(typing.NamedTuple):
     env_kind: str           # sf | pf | kalman
     ego_kind: str           # double | single
@@ -342,21 +345,20 @@ def evaluate(scene: Scene, controls: torch.Tensor, mus_wo: typing.Optional[torch
     mus, sigmas = rollout(scene.env_kind, scene.ado0, scene.goal, scene.v0, scene.sigma, scene.weights,
                           scene.noise, ego_traj, scene.dt)
     b = controls.shape[0]
-    obj = torch.zeros((b, 4))
-    raw = torch.zeros((b, 4))
+    raw = torch.zeros((b, 4), dtype=controls.dtype)
     cols = []
     for i, key in enumerate(("goal", "acc", "vel", "pos")):
         wgt = weights.get(key, 0.0)
         if key == "goal":
             if key not in weights:
-                cols.append(torch.zeros(b))
+                cols.append(torch.zeros(b, dtype=controls.dtype))
                 continue
             j = goal_norm_raw(ego_traj, scene.ego_goal)
             raw[:, i] = j.detach()
             cols.append(wgt * j / scene.axes_diag)
         else:
             if key not in weights or mus_wo is None:
-                cols.append(torch.zeros(b))
+                cols.append(torch.zeros(b, dtype=controls.dtype))
                 continue
             jc, ju = interaction_raw(key, mus, mus_wo, scene.dt, ado_mask)
             raw[:, i] = ju.detach()

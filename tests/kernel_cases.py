@@ -113,6 +113,17 @@ def oracle_scene(scene, num_candidates):
                     rep(sc.weight if sc.weight is not None else ones), rep(sc.noise), sc.axes_diag)
 
 
+def conditioning_floor(osc, controls, mus_wo, weights):
+    """max |float32 oracle - float64 oracle| of the total objective and the gradient on the same inputs: how much
+    float32 rounding alone moves the answer (the step model amplifies perturbations). Parity cannot be
+    tighter than this, so it is added (x2) to the absolute tolerance of oracle comparisons on random scenes."""
+    from oracle import torch_oracle as to
+    r32 = to.evaluate(osc, controls, mus_wo, weights)
+    r64 = to.evaluate(to.scene_to(osc, torch.float64), controls.double(), mus_wo.double(), weights)
+    return (float((r32["total"].double() - r64["total"]).abs().max()), float((r32["grad"].double() - r64["grad"]).abs().max()),
+            float((r32["mus"].double() - r64["mus"]).abs().max()))
+
+
 def check_batched_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, weights,
                             seed=0, rtol_roll=gio.RTOL_ROLLOUT, rtol_grad=gio.RTOL_GRAD):
     """Random batch (S scenes x C candidates) through the kernel vs. the CPU oracle on the same inputs."""
@@ -137,14 +148,16 @@ def check_batched_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_can
     if device != "cpu":
         torch.cuda.synchronize()
     osc = oracle_scene(scene_cpu, num_candidates)
-    ref = to.evaluate(osc, controls_cpu.reshape(-1, t_hor, 2), mus_wo.detach().cpu().repeat_interleave(num_candidates, dim=0), weights)
+    wo_rep = mus_wo.detach().cpu().repeat_interleave(num_candidates, dim=0)
+    ref = to.evaluate(osc, controls_cpu.reshape(-1, t_hor, 2), wo_rep, weights)
+    f_obj, f_grad, f_mus = conditioning_floor(osc, controls_cpu.reshape(-1, t_hor, 2), wo_rep, weights)
     b = num_scenes * num_candidates
-    gio.assert_parity(np_(res["mus"]).reshape(b, n, t_hor, 4), ref["mus"].numpy(), rtol_roll, "mus")
+    gio.assert_parity(np_(res["mus"]).reshape(b, n, t_hor, 4), ref["mus"].numpy(), rtol_roll, "mus", atol=gio.ATOL + 2 * f_mus)
     if env_kind != "kalman":
-        gio.assert_parity(np_(res["sigmas"]).reshape(b, n, t_hor, 2), ref["sigmas"].numpy(), rtol_roll, "sigmas")
-    gio.assert_parity(np_(res["obj"]).reshape(b, 4), ref["obj"].numpy(), rtol_roll, "obj", atol=gio.ATOL_OBJ)
-    gio.assert_parity(np_(res["total"]).reshape(b), ref["total"].numpy(), rtol_roll, "total", atol=gio.ATOL_OBJ)
-    gio.assert_parity(np_(res["grad"]).reshape(b, t_hor, 2), ref["grad"].numpy(), rtol_grad, "grad")
+        gio.assert_parity(np_(res["sigmas"]).reshape(b, n, t_hor, 2), ref["sigmas"].numpy(), rtol_roll, "sigmas", atol=gio.ATOL + 2 * f_mus)
+    gio.assert_parity(np_(res["obj"]).reshape(b, 4), ref["obj"].numpy(), rtol_roll, "obj", atol=gio.ATOL_OBJ + 2 * f_obj)
+    gio.assert_parity(np_(res["total"]).reshape(b), ref["total"].numpy(), rtol_roll, "total", atol=gio.ATOL_OBJ + 2 * f_obj)
+    gio.assert_parity(np_(res["grad"]).reshape(b, t_hor, 2), ref["grad"].numpy(), rtol_grad, "grad", atol=gio.ATOL + 2 * f_grad)
     # constraint rows
     et = ref["ego_traj"]
     rows = [to.control_limit_raw(et, scene_cpu.dt, ego_kind) / to.ROBOT_ACC_MAX, to.speed_limit_raw(et) / to.ROBOT_SPEED_MAX,
