@@ -20,9 +20,11 @@ def nvcc() -> str:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and os.path.exists(LIB_PATH) and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in DEPS):
+    extra = os.environ.get("MTB_NVCC_EXTRA", "").split()      # development knob (e.g. --use_fast_math experiments)
+    if not force and not extra and os.path.exists(LIB_PATH) and \
+            all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in DEPS):
         return LIB_PATH
-    cmd = [nvcc(), *NVCC_FLAGS, "-I", os.path.join(ROOT, "include"), "-I", os.path.join(HERE, "csrc"), "-o", LIB_PATH, *SOURCES]
+    cmd = [nvcc(), *NVCC_FLAGS, *extra, "-I", os.path.join(ROOT, "include"), "-I", os.path.join(HERE, "csrc"), "-o", LIB_PATH, *SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

@@ -77,7 +77,10 @@ def test_full_size_properties(eng):
     torch.cuda.synchronize()
     total, grad = res["total"], res["grad"]
     assert torch.equal(total[:, :c // 2], total[:, c // 2:])
-    assert torch.allclose(grad[:, :c // 2], grad[:, c // 2:], rtol=1e-4, atol=1e-7)
+    # gradients: shared-memory atomics accumulate the ado adjoints in arrival order, so duplicates agree to float32
+    # rounding of the sums, not bit-for-bit: per evaluation max|a-b| <= 1e-5 * max|b|
+    ga, gb = grad[:, :c // 2].reshape(s * c // 2, -1), grad[:, c // 2:].reshape(s * c // 2, -1)
+    assert bool(((ga - gb).abs().amax(dim=1) <= 1e-5 * gb.abs().amax(dim=1) + 1e-10).all())
     assert torch.count_nonzero(grad[:, :, -2:, :]) == 0
     assert float(grad.abs().max()) > 0 and bool(torch.isfinite(grad).all())
     assert torch.allclose(total, res["obj"].sum(dim=-1), rtol=1e-6, atol=1e-7)
