@@ -19,6 +19,10 @@
 #include <math_constants.h>
 #define MTB_SHARED_FLOAT4(name) extern __shared__ float4 name[]
 #define MTB_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
+// named barrier over `count` threads (a multiple of 32): synchronises one evaluation group, not the whole block
+static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
 #endif
 
 #include <cfloat>
@@ -59,8 +63,15 @@ struct Red4 {
     float a, b, c, d;
 };
 
-// Sum over the GP threads of a group; result valid in every thread of the group. For GP > 32 this contains two
-// __syncthreads(), so it must be reached by all threads of the block (GP is uniform across the block).
+// Barrier over the threads of one evaluation group. Sub-warp groups live inside one warp (all groups of a warp run in
+// lock step), larger groups use one named barrier each (id 1 + e; at most 8 groups of >= 64 threads per block).
+MTB_DEV void group_sync(int GP, int e) {
+    if (GP <= 32) __syncwarp();
+    else mtb_bar_sync(1 + e, GP);
+}
+
+// Sum over the GP threads of a group; result valid in every thread of the group. Must be reached by all threads of
+// the group (for GP <= 32: by all lanes of the warp).
 MTB_DEV Red4 group_reduce4(Red4 v, int GP, int e, float* red) {
     if (GP <= 32) {
         for (int off = GP >> 1; off > 0; off >>= 1) {
@@ -84,7 +95,7 @@ MTB_DEV Red4 group_reduce4(Red4 v, int GP, int e, float* red) {
         red[warp * 4 + 2] = v.c;
         red[warp * 4 + 3] = v.d;
     }
-    __syncthreads();
+    group_sync(GP, e);
     const int w0 = (e * GP) >> 5, nw = GP >> 5;
     Red4 r = {0.f, 0.f, 0.f, 0.f};
     for (int w = 0; w < nw; ++w) {
@@ -93,8 +104,21 @@ MTB_DEV Red4 group_reduce4(Red4 v, int GP, int e, float* red) {
         r.c += red[(w0 + w) * 4 + 2];
         r.d += red[(w0 + w) * 4 + 3];
     }
-    __syncthreads();
+    group_sync(GP, e);
     return r;
+}
+
+// shared-memory float2 accumulation with one 64-bit compare-and-swap loop (there is no native FP32 shared atomic add)
+MTB_DEV void atomic_add_f2(float* addr, float a, float b) {
+    unsigned long long* p = reinterpret_cast<unsigned long long*>(addr);
+    unsigned long long old = *reinterpret_cast<volatile unsigned long long*>(p), assumed;
+    do {
+        assumed = old;
+        const float x = __uint_as_float((unsigned)(assumed & 0xffffffffull)) + a;
+        const float y = __uint_as_float((unsigned)(assumed >> 32)) + b;
+        const unsigned long long nw = ((unsigned long long)__float_as_uint(y) << 32) | (unsigned long long)__float_as_uint(x);
+        old = atomicCAS(p, assumed, nw);
+    } while (old != assumed);
 }
 
 MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py:446)
@@ -150,7 +174,7 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
 
     const int T = prm.T, N = prm.N, P = prm.P, G = prm.G, GP = prm.GP, MW = prm.MW;
     const int tid = threadIdx.x;
-    const int e = tid / GP;
+    const int e = tid / GP;                                       // evaluation group within the block
     const int g = tid - e * GP;
     const bool active = g < G;
     const int m = active ? g / P : 0;
@@ -187,9 +211,17 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
 
     unsigned long long n_pairs = 0, n_ego = 0;
 
-    for (int item = blockIdx.x; item < prm.num_items; item += gridDim.x) {
-        // work item = E consecutive evaluations of the flattened (scene, candidate) index
-        const long long ev_raw = (long long)item * prm.E + e;
+    // Work distribution: a "unit" is the set of threads that must run in lock step -- one warp holding 32/GP
+    // sub-warp groups, or one group of GP >= 32 threads. Units loop over work items independently of each other;
+    // there is no block-wide barrier anywhere in this kernel.
+    const int unit = (GP <= 32) ? (tid >> 5) : e;
+    const int units_per_block = (GP <= 32) ? (blockDim.x >> 5) : prm.E;
+    const int evals_per_unit = (GP <= 32) ? (32 / GP) : 1;
+    const int e_in_unit = (GP <= 32) ? ((tid & 31) / GP) : 0;
+
+    for (long long item = (long long)blockIdx.x * units_per_block + unit; item < prm.num_items;
+         item += (long long)gridDim.x * units_per_block) {
+        const long long ev_raw = item * evals_per_unit + e_in_unit;
         const bool eval_valid = ev_raw < prm.num_evals;
         const size_t ev = (size_t)(eval_valid ? ev_raw : prm.num_evals - 1);
         const int s = (int)(ev / (size_t)prm.pb.num_candidates);
@@ -205,7 +237,7 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
             for (int idx = g; idx < 3 * N; idx += GP) abar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int idx = g; idx <= T; idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        __syncthreads();
+        group_sync(GP, e);
         if (has_ego && g == 0) {
             const float4 x0 = ld4(prm.pb.ego0 + (size_t)s * 4);
             float px = x0.x, py = x0.y, vx = x0.z, vy = x0.w;
@@ -255,7 +287,7 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
             sig_out[(m * T) * 2 + 0] = prm.pb.var_initial;
             sig_out[(m * T) * 2 + 1] = prm.pb.var_initial;
         }
-        __syncthreads();
+        group_sync(GP, e);
 
         // ================================================================== forward rollout
         for (int t = 0; t < T - 1; ++t) {
@@ -264,16 +296,26 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
                 V2 u;
                 if (ENV == MTB_ENV_SOCIAL_FORCES) {
                     const V2 fgoal = goal_force(p, v, goal, inv_tau, prm.pb.sf_goal_radius);
-                    unsigned mk[2] = {0u, 0u};
-                    for (int k = 0; k < N; ++k) {
-                        const float4 mu = mus_t[k];
-                        const float dx = p.x - mu.x, dy = p.y - mu.y;
-                        const float d2 = dx * dx + dy * dy;
-                        if (k != m && d2 <= prm.pair_cut2) mk[k >> 5] |= (1u << (k & 31));
+                    // which ado means are inside the interaction radius (social_forces.py:148-153)
+                    unsigned mk0 = 0u, mk1 = 0u;
+                    {
+                        const int n0 = N < 32 ? N : 32;
+#pragma unroll 4
+                        for (int k = 0; k < n0; ++k) {
+                            const float4 mu = mus_t[k];
+                            const float dx = p.x - mu.x, dy = p.y - mu.y;
+                            if (fmaf(dx, dx, dy * dy) <= prm.pair_cut2) mk0 |= (1u << k);
+                        }
+                        for (int k = 32; k < N; ++k) {
+                            const float4 mu = mus_t[k];
+                            const float dx = p.x - mu.x, dy = p.y - mu.y;
+                            if (fmaf(dx, dx, dy * dy) <= prm.pair_cut2) mk1 |= (1u << (k - 32));
+                        }
+                        if (m < 32) mk0 &= ~(1u << m); else mk1 &= ~(1u << (m - 32));   // never the own ado
                     }
                     V2 frep = v2(0.f, 0.f);
                     for (int wd = 0; wd < MW; ++wd) {
-                        unsigned bits = mk[wd];
+                        unsigned bits = wd == 0 ? mk0 : mk1;
                         if (GRAD && prm.use_tape) maskbuf[((size_t)t * tape_stride + tape_idx) * MW + wd] = bits;
                         while (bits) {
                             const int k = (wd << 5) + __ffs((int)bits) - 1;
@@ -314,7 +356,7 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
                 }
                 qbuf[g] = make_float2(vel.x * pw, vel.y * pw);
             }
-            __syncthreads();
+            group_sync(GP, e);
             if (active && i == 0) {                               // collapse the P particles of ado m (particle.py:171-175)
                 float sx = 0.f, sy = 0.f;
                 for (int j = 0; j < P; ++j) { sx += qbuf[g + j].x; sy += qbuf[g + j].y; }
@@ -337,7 +379,7 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
                     sig_out[(m * T + t + 1) * 2 + 1] = vy;
                 }
             }
-            __syncthreads();
+            group_sync(GP, e);
         }
 
         // ================================================================== objectives + constraints
@@ -475,32 +517,31 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
             float4* eo = reinterpret_cast<float4*>(prm.out.ego_traj + ev * (size_t)(T + 1) * 4);
             for (int t = g; t <= T; t += GP) eo[t] = ego[t];
         }
-        __syncthreads();                                          // misc visible, ctl free for the gradient
+        group_sync(GP, e);                                        // misc visible, ctl free for the gradient
 
         // ================================================================== backward (adjoint) pass
         if (GRAD) {
             // per group: anything to back-propagate through the environment? (saturated objectives have zero
-            // gradient). prm.want_env_adjoint is uniform for the block, so every thread reaches the barriers.
+            // gradient). For sub-warp groups the other groups of the warp may differ, so no early exit: the
+            // shuffles below are executed by every lane.
             const bool env_adjoint = prm.want_env_adjoint != 0 && misc[kNeedAdjoint] != 0.f;
+            bool any_adjoint = env_adjoint;
+            if (GP <= 32) any_adjoint = __ballot_sync(0xffffffffu, env_adjoint) != 0u;
             V2 pbar = v2(0.f, 0.f), vbar = v2(0.f, 0.f);
+            float4 rec = make_float4(0.f, 0.f, 0.f, 0.f);         // adjoint flowing along mu_p[t+1] = mu_p[t] + dt mu_v[t]
             const bool in_cost = active && (amask == nullptr || amask[m] != 0);
             const float w_over_p = pw / (float)P;
-            for (int t = T - 2; t >= 0 && prm.want_env_adjoint != 0; --t) {
-                __syncthreads();                                  // level t+1 adjoints complete
+            for (int t = T - 2; t >= 0 && any_adjoint; --t) {
+                group_sync(GP, e);                                // level t+1 adjoints complete
                 const int b_next = (t + 1) % 3, b_cur = t % 3, b_free = (t + 2) % 3;
                 for (int k = g; k < N; k += GP) abar[b_free * N + k] = make_float4(0.f, 0.f, 0.f, 0.f);
                 V2 eb_p = v2(0.f, 0.f), eb_v = v2(0.f, 0.f);      // this particle's share of the ego adjoint at t
                 if (active && env_adjoint) {
-                    float4 tot = abar[b_next * N + m];
+                    float4 tot = abar[b_next * N + m];            // pair terms of step t+1 ...
                     const float4 sd = objective_seed(prm, misc, mus, wo_scene, m, t + 1, in_cost);
-                    tot.x += sd.x; tot.y += sd.y; tot.z += sd.z; tot.w += sd.w;
-                    if (i == 0 && t >= 1) {                       // mu_p[t+1] = mu_p[t] + dt mu_v[t]
-                        float* ac = reinterpret_cast<float*>(abar + b_cur * N + m);
-                        atomicAdd(ac + 0, tot.x);
-                        atomicAdd(ac + 1, tot.y);
-                        atomicAdd(ac + 2, dt * tot.x);
-                        atomicAdd(ac + 3, dt * tot.y);
-                    }
+                    tot.x += sd.x + rec.x; tot.y += sd.y + rec.y; // ... + objective seed + mean-position recurrence
+                    tot.z += sd.z + rec.z; tot.w += sd.w + rec.w;
+                    rec = make_float4(tot.x, tot.y, dt * tot.x, dt * tot.y);   // (identical in the P threads of ado m)
                     // mu_v[t+1] = (1/P) sum_i w_i (v'_i + noise)
                     vbar.x = fmaf(tot.z, w_over_p, vbar.x);
                     vbar.y = fmaf(tot.w, w_over_p, vbar.y);
@@ -542,10 +583,8 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
                                 pb = pb + rb; vb = vb + wb;
                                 if (t >= 1) {                     // mus[:, 0] are constants
                                     float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
-                                    atomicAdd(ac + 0, -rb.x);
-                                    atomicAdd(ac + 1, -rb.y);
-                                    atomicAdd(ac + 2, -wb.x);
-                                    atomicAdd(ac + 3, -wb.y);
+                                    atomic_add_f2(ac, -rb.x, -rb.y);
+                                    atomic_add_f2(ac + 2, -wb.x, -wb.y);
                                 }
                             }
                         }
@@ -580,14 +619,12 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
                         eb_v.y += __shfl_xor_sync(0xffffffffu, eb_v.y, off);
                     }
                     if ((tid & 31) == 0) {
-                        atomicAdd(ebt + 0, eb_p.x);
-                        atomicAdd(ebt + 1, eb_p.y);
-                        atomicAdd(ebt + 2, eb_v.x);
-                        atomicAdd(ebt + 3, eb_v.y);
+                        atomic_add_f2(ebt, eb_p.x, eb_p.y);
+                        atomic_add_f2(ebt + 2, eb_v.x, eb_v.y);
                     }
                 }
             }
-            __syncthreads();
+            group_sync(GP, e);
 
             // ------------------------------------------------ fold ego adjoints through the ego dynamics
             if (has_ego && g == 0) {
@@ -615,13 +652,13 @@ __global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
                     ctl[2 * (t - 1) + 1] = sanitize(outy) + gouty;
                 }
             }
-            __syncthreads();
+            group_sync(GP, e);
             if (has_ego && eval_valid) {
                 float* go = prm.out.grad + ev * (size_t)(2 * T);
                 for (int idx = g; idx < 2 * T; idx += GP) go[idx] = ctl[idx];
             }
         }
-        __syncthreads();
+        group_sync(GP, e);
     }
 
     if (prm.out.stats != nullptr) {
@@ -806,7 +843,8 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     prm.E = E;
     prm.tape_in_smem = tape_in_smem ? 1 : 0;
     prm.num_evals = (long long)pb->num_scenes * pb->num_candidates;
-    prm.num_items = (int)((prm.num_evals + E - 1) / E);
+    const int evals_per_unit = (prm.GP <= 32) ? 32 / prm.GP : 1;          // unit = warp of sub-warp groups, or one group
+    prm.num_items = (int)((prm.num_evals + evals_per_unit - 1) / evals_per_unit);
     prm.use_tape = need_tape ? 1 : 0;
     prm.want_env_adjoint = (need_tape && md != nullptr && md->mus_wo != nullptr &&
                             (md->w_acc != 0.f || md->w_vel != 0.f || md->w_pos != 0.f)) ? 1 : 0;
@@ -817,7 +855,9 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     if (blocks_per_sm > by_threads) blocks_per_sm = by_threads < 1 ? 1 : by_threads;
     if (blocks_per_sm > 32) blocks_per_sm = 32;
     int grid = lim.sms * blocks_per_sm;
-    if (grid > prm.num_items) grid = prm.num_items;
+    const int units_per_block = (prm.GP <= 32) ? block / 32 : E;
+    const int max_grid = (prm.num_items + units_per_block - 1) / units_per_block;
+    if (grid > max_grid) grid = max_grid;
     workspace_bytes = 0;
     if (need_tape && !tape_in_smem) {
         const size_t tape_b = (size_t)grid * (prm.T - 1) * block * sizeof(float4);

@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -46,6 +47,14 @@ struct Block {
     std::barrier<> bar;
     std::vector<Warp> warps;
     char* smem;
+    // named barriers (bar.sync id, count), created on first use
+    std::mutex named_mutex;
+    std::unique_ptr<std::barrier<>> named[16];
+    std::barrier<>& named_barrier(int id, int count) {
+        std::lock_guard<std::mutex> lock(named_mutex);
+        if (!named[id]) named[id] = std::make_unique<std::barrier<>>(count);
+        return *named[id];
+    }
 };
 inline thread_local Block* tl_block = nullptr;
 }  // namespace emul
@@ -55,6 +64,7 @@ inline thread_local dim3 threadIdx, blockIdx, blockDim, gridDim;
 static inline void __syncthreads() { emul::tl_block->bar.arrive_and_wait(); }
 static inline emul::Warp& emul_warp() { return emul::tl_block->warps[threadIdx.x >> 5]; }
 static inline void __syncwarp(unsigned = 0xffffffffu) { emul_warp().bar.arrive_and_wait(); }
+static inline void mtb_bar_sync(int id, int count) { emul::tl_block->named_barrier(id, count).arrive_and_wait(); }
 
 template <class T>
 static inline T emul_exchange(T v, int src_lane) {
@@ -102,6 +112,10 @@ static inline float atomicAdd(float* addr, float val) {
 }
 static inline unsigned long long atomicAdd(unsigned long long* addr, unsigned long long val) {
     return __atomic_fetch_add(addr, val, __ATOMIC_RELAXED);
+}
+static inline unsigned long long atomicCAS(unsigned long long* addr, unsigned long long compare, unsigned long long val) {
+    __atomic_compare_exchange_n(addr, &compare, val, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED);
+    return compare;
 }
 static inline unsigned long long atomicMin(unsigned long long* addr, unsigned long long val) {
     unsigned long long old = __atomic_load_n(addr, __ATOMIC_RELAXED);
