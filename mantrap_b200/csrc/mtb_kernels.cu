@@ -110,6 +110,11 @@ MTB_DEV Red4 group_reduce4(Red4 v, int GP, int e, float* red) {
 
 // shared-memory float2 accumulation with one 64-bit compare-and-swap loop (there is no native FP32 shared atomic add)
 MTB_DEV void atomic_add_f2(float* addr, float a, float b) {
+#if !MTB_USE_CAS64
+    atomicAdd(addr, a);
+    atomicAdd(addr + 1, b);
+    return;
+#endif
     unsigned long long* p = reinterpret_cast<unsigned long long*>(addr);
     unsigned long long old = *reinterpret_cast<volatile unsigned long long*>(p), assumed;
     do {
@@ -167,8 +172,14 @@ MTB_DEV float4 objective_seed(const KParams& prm, const float* misc, const float
     return sd;
 }
 
-template <int ENV, bool GRAD, int MAXT>
-__global__ void __launch_bounds__(MAXT) evaluate_kernel(const KParams prm) {
+#ifndef MTB_USE_CAS64
+#define MTB_USE_CAS64 1
+#endif
+
+// MAXT / MINB: register budget of the instantiation (__launch_bounds__). Blocks of <= 256 threads come in two
+// flavours: MINB = 3 (<= 80 registers) when shared memory allows three or more resident blocks per SM, else MINB = 2.
+template <int ENV, bool GRAD, int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm) {
     MTB_SHARED_FLOAT4(smem4);
     float* smem = reinterpret_cast<float*>(smem4);
 
@@ -875,13 +886,13 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     return 0;
 }
 
-template <int ENV, bool GRAD, int MAXT>
+template <int ENV, bool GRAD, int MAXT, int MINB>
 static int launch_evaluate_t(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
 #ifndef MTB_HOST_EMUL
-    cudaError_t err = cudaFuncSetAttribute(evaluate_kernel<ENV, GRAD, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, info.smem_bytes);
+    cudaError_t err = cudaFuncSetAttribute(evaluate_kernel<ENV, GRAD, MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, info.smem_bytes);
     if (err != cudaSuccess) return (int)err;
 #endif
-    MTB_LAUNCH((evaluate_kernel<ENV, GRAD, MAXT>), info.grid, info.block, (size_t)info.smem_bytes, stream, prm);
+    MTB_LAUNCH((evaluate_kernel<ENV, GRAD, MAXT, MINB>), info.grid, info.block, (size_t)info.smem_bytes, stream, prm);
 #ifndef MTB_HOST_EMUL
     return (int)cudaGetLastError();
 #else
@@ -889,11 +900,11 @@ static int launch_evaluate_t(const KParams& prm, const mtb_launch_info& info, cu
 #endif
 }
 
-// two register budgets: blocks of <= 256 threads (the common case) may use up to 255 registers per thread
 template <int ENV, bool GRAD>
 static int launch_evaluate(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
-    if (info.block <= kDefaultBlock) return launch_evaluate_t<ENV, GRAD, kDefaultBlock>(prm, info, stream);
-    return launch_evaluate_t<ENV, GRAD, kMaxThreads>(prm, info, stream);
+    if (info.block > kDefaultBlock) return launch_evaluate_t<ENV, GRAD, kMaxThreads, 1>(prm, info, stream);
+    if (info.blocks_per_sm >= 3) return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 3>(prm, info, stream);
+    return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 2>(prm, info, stream);
 }
 
 }  // namespace mtb
