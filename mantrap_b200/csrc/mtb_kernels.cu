@@ -33,6 +33,10 @@ static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
 #include "mantrap_b200.h"
 #include "mtb_math.cuh"
 
+#ifndef MTB_USE_CAS64
+#define MTB_USE_CAS64 1
+#endif
+
 namespace mtb {
 
 constexpr int kMaxThreads = 1024;
@@ -48,7 +52,9 @@ struct KParams {
     int has_ego, want_grad, want_env_adjoint, use_tape;
     float pair_cut2;                 // largest d^2 with sqrtf(d^2) <= interaction radius
     // shared-memory layout (float units, per evaluation) -------------------------------------------------
-    int off_ctl, off_ego, off_egobar, off_mus, off_abar, off_q, off_misc, off_tape, off_mask;
+    int off_ctl, off_ego, off_egobar, off_mus, off_abar, off_q, off_misc, off_tape, off_mask, off_srcmask;
+    int GW;                          // 32-bit words of a per-target source mask (GP / 32, at least 1)
+    int use_stage;                   // pair adjoints are staged in dead tape rows and gathered (no float atomics)
     int per_eval_f, red_f;
     int tape_in_smem;
     float4* tape_global;             // [grid][T-1][block]   when the tape does not fit in shared memory
@@ -172,10 +178,6 @@ MTB_DEV float4 objective_seed(const KParams& prm, const float* misc, const float
     return sd;
 }
 
-#ifndef MTB_USE_CAS64
-#define MTB_USE_CAS64 1
-#endif
-
 // MAXT / MINB: register budget of the instantiation (__launch_bounds__). Blocks of <= 256 threads come in two
 // flavours: MINB = 3 (<= 80 registers) when shared memory allows three or more resident blocks per SM, else MINB = 2.
 template <int ENV, bool GRAD, int MAXT, int MINB>
@@ -205,6 +207,9 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);     // [GP]
     float* misc = sm + prm.off_misc;
 
+    unsigned* srcmask = reinterpret_cast<unsigned*>(sm + prm.off_srcmask);   // [(T-1)][N][GW] sources per target
+    const int GW = prm.GW;
+    const bool use_stage = GRAD && prm.use_stage != 0;
     float4* tape;            // [(T-1)][stride] (p.x, p.y, u.x, u.y) of every particle before its step
     unsigned* maskbuf;       // [(T-1)][stride][MW] interaction bit masks
     int tape_stride, tape_idx;
@@ -247,6 +252,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
         if (GRAD) {
             for (int idx = g; idx < 3 * N; idx += GP) abar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int idx = g; idx <= T; idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (use_stage)
+                for (int idx = g; idx < (T - 1) * N * GW; idx += GP) srcmask[idx] = 0u;
         }
         group_sync(GP, e);
         if (has_ego && g == 0) {
@@ -335,6 +342,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                             const RepulsionFwd o = repulsion_forward(p - v2(mu.x, mu.y), v - v2(mu.z, mu.w), pv0, psig, dt, u_ped);
                             frep = frep - o.force;
                             ++n_pairs;
+                            if (use_stage && t >= 1) atomicOr(srcmask + ((size_t)t * N + k) * GW + (g >> 5), 1u << (g & 31));
                         }
                     }
                     u = fgoal + frep;
@@ -548,7 +556,24 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 for (int k = g; k < N; k += GP) abar[b_free * N + k] = make_float4(0.f, 0.f, 0.f, 0.f);
                 V2 eb_p = v2(0.f, 0.f), eb_v = v2(0.f, 0.f);      // this particle's share of the ego adjoint at t
                 if (active && env_adjoint) {
-                    float4 tot = abar[b_next * N + m];            // pair terms of step t+1 ...
+                    float4 tot = abar[b_next * N + m];            // pair terms of step t+1 (atomic / overflow path) ...
+                    if (use_stage && t + 1 <= T - 2) {            // ... and the staged ones: gather from the sources
+                        const int lvl = t + 1;
+                        const int cap = 1 + (T - 2 - lvl) / 2;
+                        for (int w = 0; w < GW; ++w) {
+                            unsigned src = srcmask[((size_t)lvl * N + m) * GW + w];
+                            while (src) {
+                                const int gs = (w << 5) + __ffs((int)src) - 1;
+                                src &= src - 1;
+                                const unsigned* ms = maskbuf + ((size_t)lvl * tape_stride + gs) * MW;
+                                int j = (m < 32) ? __popc(ms[0] & ((1u << m) - 1u)) : __popc(ms[0]) + __popc(ms[1] & ((1u << (m - 32)) - 1u));
+                                if (j < cap) {
+                                    const float4 c = tape[(size_t)(lvl + 2 * j) * tape_stride + gs];
+                                    tot.x += c.x; tot.y += c.y; tot.z += c.z; tot.w += c.w;
+                                }
+                            }
+                        }
+                    }
                     const float4 sd = objective_seed(prm, misc, mus, wo_scene, m, t + 1, in_cost);
                     tot.x += sd.x + rec.x; tot.y += sd.y + rec.y; // ... + objective seed + mean-position recurrence
                     tot.z += sd.z + rec.z; tot.w += sd.w + rec.w;
@@ -581,6 +606,11 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                             pb = pb + rb; vb = vb + wb;
                             eb_p = eb_p - rb; eb_v = eb_v - wb;
                         }
+                        // Adjoint w.r.t. the other ado's mean (level t). Staged: slot j of this particle lives in a tape
+                        // row that is already consumed (row t itself, then rows t+2, t+4, ...); the particles of ado k
+                        // gather them at the next step in a fixed order. Overflowing slots use the atomic path.
+                        const int cap = use_stage ? 1 + (T - 2 - t) / 2 : 0;
+                        int slot = 0;
                         for (int wd = 0; wd < MW; ++wd) {
                             unsigned bits = maskbuf[((size_t)t * tape_stride + tape_idx) * MW + wd];
                             while (bits) {
@@ -593,10 +623,15 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                                 repulsion_adjoint(o, r, w, dt, fbar, rb, wb);
                                 pb = pb + rb; vb = vb + wb;
                                 if (t >= 1) {                     // mus[:, 0] are constants
-                                    float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
-                                    atomic_add_f2(ac, -rb.x, -rb.y);
-                                    atomic_add_f2(ac + 2, -wb.x, -wb.y);
+                                    if (slot < cap) {
+                                        tape[(size_t)(t + 2 * slot) * tape_stride + tape_idx] = make_float4(-rb.x, -rb.y, -wb.x, -wb.y);
+                                    } else {
+                                        float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
+                                        atomic_add_f2(ac, -rb.x, -rb.y);
+                                        atomic_add_f2(ac + 2, -wb.x, -wb.y);
+                                    }
                                 }
+                                ++slot;
                             }
                         }
                     } else if (ENV == MTB_ENV_POTENTIAL_FIELD) {  // u = v + gate * impact(ego_p - p)
@@ -815,6 +850,9 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const bool need_tape = want_grad && !kalman && prm.has_ego && prm.T > 1;
     const bool need_mask = need_tape && pb->env_kind == MTB_ENV_SOCIAL_FORCES;
 
+    // staging needs the per-target source masks in shared memory: (T-1) * N * GP/32 words (small for the usual
+    // N * P <= 128; the big sweep points keep the atomic accumulation)
+    const bool stage_ok = (size_t)(prm.T - 1) * prm.N * ((prm.GP + 31) / 32) * 4 <= 8 * 1024;
     auto layout = [&](int E, bool tape_in_smem) -> size_t {
         int off = 0;
         prm.off_ctl = off;    off += round_up(2 * prm.T, 4);
@@ -826,6 +864,9 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         prm.off_misc = off;   off += kMiscFloats;
         prm.off_tape = off;   off += (need_tape && tape_in_smem) ? (prm.T - 1) * prm.GP * 4 : 0;
         prm.off_mask = off;   off += (need_mask && tape_in_smem) ? round_up((prm.T - 1) * prm.GP * prm.MW, 4) : 0;
+        prm.GW = (prm.GP + 31) / 32;
+        prm.use_stage = (need_mask && tape_in_smem && stage_ok) ? 1 : 0;
+        prm.off_srcmask = off; off += prm.use_stage ? round_up((prm.T - 1) * prm.N * prm.GW, 4) : 0;
         prm.per_eval_f = off;
         const int block = E * prm.GP;
         prm.red_f = round_up(((block + 31) / 32) * 4, 4);

@@ -110,6 +110,7 @@ static inline float atomicAdd(float* addr, float val) {
         if (__atomic_compare_exchange_n(a, &old_bits, new_bits, false, __ATOMIC_RELAXED, __ATOMIC_RELAXED)) return old_f;
     }
 }
+static inline unsigned atomicOr(unsigned* addr, unsigned val) { return __atomic_fetch_or(addr, val, __ATOMIC_RELAXED); }
 static inline unsigned long long atomicAdd(unsigned long long* addr, unsigned long long val) {
     return __atomic_fetch_add(addr, val, __ATOMIC_RELAXED);
 }
