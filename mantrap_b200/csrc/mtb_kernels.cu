@@ -28,14 +28,11 @@ static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
 #include <cfloat>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 
 #include "mantrap_b200.h"
 #include "mtb_math.cuh"
-
-#ifndef MTB_USE_CAS64
-#define MTB_USE_CAS64 1
-#endif
 
 namespace mtb {
 
@@ -52,9 +49,7 @@ struct KParams {
     int has_ego, want_grad, want_env_adjoint, use_tape;
     float pair_cut2;                 // largest d^2 with sqrtf(d^2) <= interaction radius
     // shared-memory layout (float units, per evaluation) -------------------------------------------------
-    int off_ctl, off_ego, off_egobar, off_mus, off_abar, off_q, off_misc, off_tape, off_mask, off_srcmask;
-    int GW;                          // 32-bit words of a per-target source mask (GP / 32, at least 1)
-    int use_stage;                   // pair adjoints are staged in dead tape rows and gathered (no float atomics)
+    int off_ctl, off_ego, off_egobar, off_mus, off_abar, off_q, off_misc, off_tape, off_mask;
     int per_eval_f, red_f;
     int tape_in_smem;
     float4* tape_global;             // [grid][T-1][block]   when the tape does not fit in shared memory
@@ -114,22 +109,12 @@ MTB_DEV Red4 group_reduce4(Red4 v, int GP, int e, float* red) {
     return r;
 }
 
-// shared-memory float2 accumulation with one 64-bit compare-and-swap loop (there is no native FP32 shared atomic add)
+// Shared-memory float accumulation. sm_100a has no native FP32 shared atomic add: this compiles to an
+// ATOMS.CAST.SPIN compare-and-swap loop. Measured alternatives (one 64-bit CAS per float2; staging the pair adjoints
+// in consumed tape rows and gathering them per target ado) were slower on the config-4 shape, see DESIGN.md.
 MTB_DEV void atomic_add_f2(float* addr, float a, float b) {
-#if !MTB_USE_CAS64
     atomicAdd(addr, a);
     atomicAdd(addr + 1, b);
-    return;
-#endif
-    unsigned long long* p = reinterpret_cast<unsigned long long*>(addr);
-    unsigned long long old = *reinterpret_cast<volatile unsigned long long*>(p), assumed;
-    do {
-        assumed = old;
-        const float x = __uint_as_float((unsigned)(assumed & 0xffffffffull)) + a;
-        const float y = __uint_as_float((unsigned)(assumed >> 32)) + b;
-        const unsigned long long nw = ((unsigned long long)__float_as_uint(y) << 32) | (unsigned long long)__float_as_uint(x);
-        old = atomicCAS(p, assumed, nw);
-    } while (old != assumed);
 }
 
 MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py:446)
@@ -207,9 +192,6 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);     // [GP]
     float* misc = sm + prm.off_misc;
 
-    unsigned* srcmask = reinterpret_cast<unsigned*>(sm + prm.off_srcmask);   // [(T-1)][N][GW] sources per target
-    const int GW = prm.GW;
-    const bool use_stage = GRAD && prm.use_stage != 0;
     float4* tape;            // [(T-1)][stride] (p.x, p.y, u.x, u.y) of every particle before its step
     unsigned* maskbuf;       // [(T-1)][stride][MW] interaction bit masks
     int tape_stride, tape_idx;
@@ -252,8 +234,6 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
         if (GRAD) {
             for (int idx = g; idx < 3 * N; idx += GP) abar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int idx = g; idx <= T; idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (use_stage)
-                for (int idx = g; idx < (T - 1) * N * GW; idx += GP) srcmask[idx] = 0u;
         }
         group_sync(GP, e);
         if (has_ego && g == 0) {
@@ -342,7 +322,6 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                             const RepulsionFwd o = repulsion_forward(p - v2(mu.x, mu.y), v - v2(mu.z, mu.w), pv0, psig, dt, u_ped);
                             frep = frep - o.force;
                             ++n_pairs;
-                            if (use_stage && t >= 1) atomicOr(srcmask + ((size_t)t * N + k) * GW + (g >> 5), 1u << (g & 31));
                         }
                     }
                     u = fgoal + frep;
@@ -556,24 +535,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 for (int k = g; k < N; k += GP) abar[b_free * N + k] = make_float4(0.f, 0.f, 0.f, 0.f);
                 V2 eb_p = v2(0.f, 0.f), eb_v = v2(0.f, 0.f);      // this particle's share of the ego adjoint at t
                 if (active && env_adjoint) {
-                    float4 tot = abar[b_next * N + m];            // pair terms of step t+1 (atomic / overflow path) ...
-                    if (use_stage && t + 1 <= T - 2) {            // ... and the staged ones: gather from the sources
-                        const int lvl = t + 1;
-                        const int cap = 1 + (T - 2 - lvl) / 2;
-                        for (int w = 0; w < GW; ++w) {
-                            unsigned src = srcmask[((size_t)lvl * N + m) * GW + w];
-                            while (src) {
-                                const int gs = (w << 5) + __ffs((int)src) - 1;
-                                src &= src - 1;
-                                const unsigned* ms = maskbuf + ((size_t)lvl * tape_stride + gs) * MW;
-                                int j = (m < 32) ? __popc(ms[0] & ((1u << m) - 1u)) : __popc(ms[0]) + __popc(ms[1] & ((1u << (m - 32)) - 1u));
-                                if (j < cap) {
-                                    const float4 c = tape[(size_t)(lvl + 2 * j) * tape_stride + gs];
-                                    tot.x += c.x; tot.y += c.y; tot.z += c.z; tot.w += c.w;
-                                }
-                            }
-                        }
-                    }
+                    float4 tot = abar[b_next * N + m];            // pair terms of step t+1 ...
                     const float4 sd = objective_seed(prm, misc, mus, wo_scene, m, t + 1, in_cost);
                     tot.x += sd.x + rec.x; tot.y += sd.y + rec.y; // ... + objective seed + mean-position recurrence
                     tot.z += sd.z + rec.z; tot.w += sd.w + rec.w;
@@ -606,11 +568,6 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                             pb = pb + rb; vb = vb + wb;
                             eb_p = eb_p - rb; eb_v = eb_v - wb;
                         }
-                        // Adjoint w.r.t. the other ado's mean (level t). Staged: slot j of this particle lives in a tape
-                        // row that is already consumed (row t itself, then rows t+2, t+4, ...); the particles of ado k
-                        // gather them at the next step in a fixed order. Overflowing slots use the atomic path.
-                        const int cap = use_stage ? 1 + (T - 2 - t) / 2 : 0;
-                        int slot = 0;
                         for (int wd = 0; wd < MW; ++wd) {
                             unsigned bits = maskbuf[((size_t)t * tape_stride + tape_idx) * MW + wd];
                             while (bits) {
@@ -622,16 +579,11 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                                 V2 rb, wb;
                                 repulsion_adjoint(o, r, w, dt, fbar, rb, wb);
                                 pb = pb + rb; vb = vb + wb;
-                                if (t >= 1) {                     // mus[:, 0] are constants
-                                    if (slot < cap) {
-                                        tape[(size_t)(t + 2 * slot) * tape_stride + tape_idx] = make_float4(-rb.x, -rb.y, -wb.x, -wb.y);
-                                    } else {
-                                        float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
-                                        atomic_add_f2(ac, -rb.x, -rb.y);
-                                        atomic_add_f2(ac + 2, -wb.x, -wb.y);
-                                    }
+                                if (t >= 1) {                     // mus[:, 0] are constants; adjoint of ado k's mean at level t
+                                    float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
+                                    atomic_add_f2(ac, -rb.x, -rb.y);
+                                    atomic_add_f2(ac + 2, -wb.x, -wb.y);
                                 }
-                                ++slot;
                             }
                         }
                     } else if (ENV == MTB_ENV_POTENTIAL_FIELD) {  // u = v + gate * impact(ego_p - p)
@@ -759,6 +711,12 @@ __global__ void argmin_kernel(const float* __restrict__ total, const float* __re
 // ---------------------------------------------------------------------------------------------------------
 static int round_up(int x, int m) { return (x + m - 1) / m * m; }
 
+// development knobs (read once per call; unset in production)
+static int env_flag(const char* name) {
+    const char* v = std::getenv(name);
+    return (v != nullptr && v[0] != '\0') ? std::atoi(v) : 0;
+}
+
 struct DeviceLimits {
     int sms;
     int max_smem;      // opt-in dynamic shared memory per block
@@ -850,9 +808,6 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const bool need_tape = want_grad && !kalman && prm.has_ego && prm.T > 1;
     const bool need_mask = need_tape && pb->env_kind == MTB_ENV_SOCIAL_FORCES;
 
-    // staging needs the per-target source masks in shared memory: (T-1) * N * GP/32 words (small for the usual
-    // N * P <= 128; the big sweep points keep the atomic accumulation)
-    const bool stage_ok = (size_t)(prm.T - 1) * prm.N * ((prm.GP + 31) / 32) * 4 <= 8 * 1024;
     auto layout = [&](int E, bool tape_in_smem) -> size_t {
         int off = 0;
         prm.off_ctl = off;    off += round_up(2 * prm.T, 4);
@@ -864,9 +819,6 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         prm.off_misc = off;   off += kMiscFloats;
         prm.off_tape = off;   off += (need_tape && tape_in_smem) ? (prm.T - 1) * prm.GP * 4 : 0;
         prm.off_mask = off;   off += (need_mask && tape_in_smem) ? round_up((prm.T - 1) * prm.GP * prm.MW, 4) : 0;
-        prm.GW = (prm.GP + 31) / 32;
-        prm.use_stage = (need_mask && tape_in_smem && stage_ok) ? 1 : 0;
-        prm.off_srcmask = off; off += prm.use_stage ? round_up((prm.T - 1) * prm.N * prm.GW, 4) : 0;
         prm.per_eval_f = off;
         const int block = E * prm.GP;
         prm.red_f = round_up(((block + 31) / 32) * 4, 4);
@@ -878,18 +830,30 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     if ((long long)E > total_evals) E = (int)total_evals;
     // the block must be a multiple of a warp: with sub-warp groups keep E a multiple of 32 / GP
     if (prm.GP < 32) E = round_up(E, 32 / prm.GP);
+    // Tape placement: shared memory when that still leaves >= 3 resident blocks per SM (registers cap the kernel at
+    // 3 x 256 threads anyway); otherwise a per-block global scratch that stays L2-resident, which trades ~30 B of L2
+    // traffic per particle step for occupancy (measured +17 % on the config-4 shape).
     bool tape_in_smem = true;
-    size_t smem = layout(E, true);
+    if (need_tape) {
+        const size_t with_tape = layout(E, true);
+        const int resident = (int)((size_t)lim.smem_per_sm / (with_tape + 1024));
+        tape_in_smem = resident >= 3 && with_tape <= (size_t)lim.max_smem;
+        const int knob = env_flag("MTB_TAPE_GLOBAL");       // development knob: 1 = global, 2 = shared
+        if (knob == 1) tape_in_smem = false;
+        if (knob == 2) tape_in_smem = true;
+    }
+    size_t smem = layout(E, tape_in_smem);
     while (smem > (size_t)lim.max_smem && E * prm.GP > 32 && E > 1) {
         E = (prm.GP < 32) ? E - 32 / prm.GP : E - 1;
         if (E < 1) { E = 1; break; }
-        smem = layout(E, true);
+        smem = layout(E, tape_in_smem);
     }
     if (prm.GP < 32 && E < 32 / prm.GP) E = 32 / prm.GP;
-    smem = layout(E, true);
+    smem = layout(E, tape_in_smem);
     if (smem > (size_t)lim.max_smem) {
         tape_in_smem = false;
         smem = layout(E, false);
+        while (smem > (size_t)lim.max_smem && E > 1 && prm.GP >= 32) smem = layout(--E, false);
         if (smem > (size_t)lim.max_smem) return MTB_ERR_TOO_LARGE;
     }
     prm.E = E;
@@ -944,7 +908,9 @@ static int launch_evaluate_t(const KParams& prm, const mtb_launch_info& info, cu
 template <int ENV, bool GRAD>
 static int launch_evaluate(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
     if (info.block > kDefaultBlock) return launch_evaluate_t<ENV, GRAD, kMaxThreads, 1>(prm, info, stream);
-    if (info.blocks_per_sm >= 3) return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 3>(prm, info, stream);
+    const int force = env_flag("MTB_MINB");
+    if (force == 4) return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 4>(prm, info, stream);
+    if (force == 3 || (force == 0 && info.blocks_per_sm >= 3)) return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 3>(prm, info, stream);
     return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 2>(prm, info, stream);
 }
 
