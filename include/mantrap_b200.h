@@ -133,8 +133,14 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
 /* launch geometry mtb_evaluate would use (for benchmarks / docs) */
 int mtb_query_launch(const mtb_problem* problem, int want_grad, mtb_launch_info* info);
 
-/* dense Jacobian of the min-distance rows w.r.t. the controls: jac[S,C,N*T,2T] (forward-mode tangents) */
-int mtb_constraint_jacobian(const mtb_problem* problem, const mtb_modules* modules, float* cons /*[S,C,N*T]*/,
+/* Dense Jacobian of every enabled constraint row w.r.t. the controls, same row order as mtb_outputs.cons:
+ * jac[S,C,R,2T] row-major with R = mtb_num_constraint_rows, columns = z index (t, xy). UN-normalised, as
+ * OptimizationModule.jacobian returns it (optimization_module.py:258-307): control rows = identity for the double
+ * integrator (control_limits.py:62-68, reference quirk) and u/||u|| for the single integrator, speed rows = velocity
+ * block of dx_du (speed_limits.py:39-81, linear.py:169-196), min-distance rows = forward-mode tangents through the
+ * ego rollout AND the environment rollout (replaces one autograd sweep per row, optimization_module.py:428-434).
+ * cons (optional, may be NULL) receives the un-normalised min-distance values [S,C,N*T]. */
+int mtb_constraint_jacobian(const mtb_problem* problem, const mtb_modules* modules, float* cons,
                             float* jac, void* workspace, size_t workspace_bytes, void* stream);
 size_t mtb_jacobian_workspace_bytes(const mtb_problem* problem);
 

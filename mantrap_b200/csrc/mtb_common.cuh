@@ -1,0 +1,101 @@
+// Shared between the translation units of libmantrap_b200.so: launch macros (CUDA or the test-only host emulation),
+// device limits, argument validation and small host helpers.
+#pragma once
+
+#ifdef MTB_HOST_EMUL
+#include "cuda_shim.h"
+#else
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#define MTB_SHARED_FLOAT4(name) extern __shared__ float4 name[]
+#define MTB_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
+// named barrier over `count` threads (a multiple of 32): synchronises one evaluation group, not the whole block
+static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+#endif
+
+#include <cfloat>
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+
+#include "mantrap_b200.h"
+
+namespace mtb {
+
+constexpr int kMaxThreads = 1024;
+
+static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+struct DeviceLimits {
+    int sms;
+    int max_smem;      // opt-in dynamic shared memory per block
+    int smem_per_sm;
+};
+
+static inline DeviceLimits device_limits() {
+    DeviceLimits lim;
+#ifdef MTB_HOST_EMUL
+    lim.sms = 2;
+    lim.max_smem = 227 * 1024;
+    lim.smem_per_sm = 228 * 1024;
+#else
+    int dev = 0;
+    lim.sms = 148; lim.max_smem = 227 * 1024; lim.smem_per_sm = 228 * 1024;   // B200 defaults (no device present)
+    if (cudaGetDevice(&dev) == cudaSuccess) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) lim.sms = v;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) == cudaSuccess && v > 0) lim.max_smem = v;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev) == cudaSuccess && v > 0) lim.smem_per_sm = v;
+    } else {
+        (void)cudaGetLastError();
+    }
+#endif
+    return lim;
+}
+
+static inline int validate(const mtb_problem* pb) {
+    if (pb == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->num_scenes < 1 || pb->num_candidates < 1 || pb->t_horizon < 1 || pb->num_ados < 1) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->num_ados > MTB_MAX_ADOS || pb->t_horizon > MTB_MAX_HORIZON) return MTB_ERR_TOO_LARGE;
+    if (pb->env_kind < 0 || pb->env_kind > MTB_ENV_KALMAN || pb->ego_kind < 0 || pb->ego_kind > MTB_EGO_NONE) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->env_kind != MTB_ENV_KALMAN && pb->num_particles < 1) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->ego_kind == MTB_EGO_NONE && pb->num_candidates != 1) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->ado0 == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->ego_kind != MTB_EGO_NONE && (pb->ego0 == nullptr || pb->controls == nullptr)) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->env_kind != MTB_ENV_KALMAN && (pb->v0 == nullptr || pb->weight == nullptr)) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->env_kind == MTB_ENV_SOCIAL_FORCES && (pb->sigma == nullptr || pb->ado_goal == nullptr)) return MTB_ERR_BAD_ARGUMENT;
+    const int particles = pb->num_ados * (pb->env_kind == MTB_ENV_KALMAN ? 1 : pb->num_particles);
+    if (particles > kMaxThreads) return MTB_ERR_TOO_LARGE;
+    return 0;
+}
+
+// largest float d2 with sqrtf(d2) <= radius, so that `d2 <= cut` decides exactly like `norm <= radius`
+static inline float pair_cut_squared(float radius) {
+    float cut = radius * radius;
+    while (sqrtf(cut) > radius) cut = nextafterf(cut, 0.f);
+    for (;;) {
+        const float nxt = nextafterf(cut, INFINITY);
+        if (sqrtf(nxt) <= radius) cut = nxt; else break;
+    }
+    return cut;
+}
+
+// constraint rows of the enabled constraint modules: control | speed | min-distance
+struct ConstraintRows {
+    int control, speed, mind, total;
+};
+static inline ConstraintRows constraint_rows(const mtb_problem* pb, const mtb_modules* md) {
+    ConstraintRows r = {0, 0, 0, 0};
+    if (md != nullptr && pb->ego_kind != MTB_EGO_NONE) {
+        if (md->con_control) r.control = (pb->ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) ? 2 * pb->t_horizon : pb->t_horizon;
+        if (md->con_speed) r.speed = 2 * (pb->t_horizon + 1);
+        if (md->con_min_distance) r.mind = pb->num_ados * pb->t_horizon;
+    }
+    r.total = r.control + r.speed + r.mind;
+    return r;
+}
+
+}  // namespace mtb

@@ -1,0 +1,390 @@
+// mantrap_b200: dense constraint Jacobian w.r.t. the controls by forward-mode tangents (sm_100a).
+//
+// Replaces IPOPTSolver.jacobian (mantrap/solver/ipopt.py:140-154) for the constraint rows of the hot path. The
+// reference obtains the Jacobian of rows that depend on the environment rollout with ONE reverse autograd sweep PER
+// ROW (mantrap/modules/base/optimization_module.py:428-434); the min-distance rows are R = N*T against 2T columns, so
+// forward mode is the cheap direction: a work item = (evaluation, chunk of D control directions). One thread per
+// particle carries its forward state and D tangent states in registers; the 2x2 Jacobians of every pair term are
+// computed once per pair per step (rows of the Jacobian = the adjoint routine of mtb_math.cuh seeded with e_x, e_y)
+// and applied to all D directions. Tangents of the collapsed means live in shared memory (two rotating levels).
+//
+// Row order and normalisation follow mtb_outputs.cons / OptimizationModule.jacobian (un-normalised):
+//   control rows  control_limits.py:38-68     identity (double integrator, reference quirk) | u/||u|| (single)
+//   speed rows    speed_limits.py:39-81       velocity rows of dx_du (agents/base/linear.py:169-196)
+//   min-distance  constants.py:107 (north star): d ||ego_p(t) - mu_p[k,t]|| / du through ego AND environment rollout
+#include "mtb_common.cuh"
+#include "mtb_math.cuh"
+
+namespace mtb {
+
+struct JParams {
+    mtb_problem pb;
+    mtb_modules md;
+    float* cons;
+    float* jac;
+    int T, N, P, G, GP, MW, n_chunks;
+    long long num_items;
+    int rows_control, rows_speed, rows_mind, R;
+    float pair_cut2;
+    int off_ctl, off_ego, off_mus, off_mud, off_q, off_qd;   // float offsets into dynamic shared memory
+};
+
+// tangent of the ego state at time index t w.r.t. control j (same component): (d p, d v)   [SURVEY A.1]
+MTB_DEV float2 ego_tangent(int ego_kind, float dt, int t, int j) {
+    if (ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) {
+        const int lag = t - 1 - j;
+        return make_float2(lag > 0 ? dt * dt * (float)lag : 0.f, j < t ? dt : 0.f);
+    }
+    return make_float2(j < t ? dt : 0.f, j == t - 1 ? 1.f : 0.f);
+}
+
+template <int ENV, int D, int MAXT>
+__global__ void __launch_bounds__(MAXT) jacobian_kernel(const JParams prm) {
+    MTB_SHARED_FLOAT4(smem4);
+    float* sm = reinterpret_cast<float*>(smem4);
+    const int T = prm.T, N = prm.N, P = prm.P, G = prm.G, R = prm.R;
+    const int g = threadIdx.x, nthreads = blockDim.x;
+    const bool active = g < G;
+    const int m = active ? g / P : 0;
+    const int i = g - m * P;
+    const float dt = prm.pb.dt;
+    const float u_ped = prm.pb.ped_speed_max;
+    const float inv_tau = 1.0f / prm.pb.sf_tau;
+    const int ego_kind = prm.pb.ego_kind;
+    const int two_t = 2 * T;
+
+    float* ctl = sm + prm.off_ctl;                                  // [2T]
+    float4* ego = reinterpret_cast<float4*>(sm + prm.off_ego);      // [T+1]
+    float4* mus = reinterpret_cast<float4*>(sm + prm.off_mus);      // [2][N]
+    float4* mud = reinterpret_cast<float4*>(sm + prm.off_mud);      // [2][N][D] tangents of the means (p.xy, v.xy)
+    float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);       // [GP]
+    float2* qd = reinterpret_cast<float2*>(sm + prm.off_qd);        // [GP][D]
+
+    for (long long item = blockIdx.x; item < prm.num_items; item += gridDim.x) {
+        const size_t ev = (size_t)(item / prm.n_chunks);
+        const int chunk = (int)(item - (long long)ev * prm.n_chunks);
+        const int d0 = chunk * D;
+        const int s = (int)(ev / (size_t)prm.pb.num_candidates);
+        float* jac = prm.jac + ev * (size_t)R * two_t;
+
+        const float* u_g = prm.pb.controls + ev * (size_t)two_t;
+        for (int idx = g; idx < two_t; idx += nthreads) ctl[idx] = __ldg(u_g + idx);
+        const float* ado0_s = prm.pb.ado0 + (size_t)s * N * 4;
+        for (int k = g; k < N; k += nthreads) mus[k] = *reinterpret_cast<const float4*>(ado0_s + k * 4);
+        for (int idx = g; idx < 2 * N * D; idx += nthreads) mud[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+        __syncthreads();
+        if (g == 0) {
+            const float4 x0 = *reinterpret_cast<const float4*>(prm.pb.ego0 + (size_t)s * 4);
+            float px = x0.x, py = x0.y, vx = x0.z, vy = x0.w;
+            ego[0] = x0;
+            for (int t = 0; t < T; ++t) {
+                if (ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) {
+                    px = fmaf(dt, vx, px); py = fmaf(dt, vy, py);
+                    vx = fmaf(dt, ctl[2 * t], vx); vy = fmaf(dt, ctl[2 * t + 1], vy);
+                } else {
+                    vx = ctl[2 * t]; vy = ctl[2 * t + 1];
+                    px = fmaf(dt, vx, px); py = fmaf(dt, vy, py);
+                }
+                ego[t + 1] = make_float4(px, py, vx, vy);
+            }
+        }
+
+        // ------------------------------------------------------------ particle state, parameters, zero tangents
+        V2 p = v2(0.f, 0.f), v = v2(0.f, 0.f), goal = v2(0.f, 0.f);
+        float pv0 = 1.f, psig = 1.f, pw = 0.f;
+        if (active) {
+            const float4 a0 = *reinterpret_cast<const float4*>(ado0_s + m * 4);
+            p = v2(a0.x, a0.y);
+            v = v2(a0.z, a0.w);
+            if (ENV != MTB_ENV_KALMAN) {
+                const size_t pi = ((size_t)s * N + m) * P + i;
+                pv0 = __ldg(prm.pb.v0 + pi);
+                pw = __ldg(prm.pb.weight + pi);
+                if (ENV == MTB_ENV_SOCIAL_FORCES) {
+                    psig = __ldg(prm.pb.sigma + pi);
+                    goal = v2(__ldg(prm.pb.ado_goal + ((size_t)s * N + m) * 2), __ldg(prm.pb.ado_goal + ((size_t)s * N + m) * 2 + 1));
+                }
+            } else {
+                pw = 1.f;
+            }
+        }
+        V2 tp[D], tv[D];
+#pragma unroll
+        for (int d = 0; d < D; ++d) { tp[d] = v2(0.f, 0.f); tv[d] = v2(0.f, 0.f); }
+        __syncthreads();
+
+        // ------------------------------------------------------------ constant rows: control | speed
+        for (int idx = g; idx < prm.rows_control * D; idx += nthreads) {
+            const int r = idx / D, d = idx - r * D, dg = d0 + d;
+            if (dg >= two_t) continue;
+            float val;
+            if (ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) {
+                val = (r == dg) ? 1.f : 0.f;                        // control_limits.py:62-68 (identity, also for u < 0)
+            } else {                                                // d ||u_r|| / d u = u / ||u|| (norm'(0) = 0)
+                val = 0.f;
+                if ((dg >> 1) == r) {
+                    const float ux = ctl[2 * r], uy = ctl[2 * r + 1];
+                    const float nu = sqrtf(ux * ux + uy * uy);
+                    if (nu > 0.f) val = ((dg & 1) ? uy : ux) / nu;
+                }
+            }
+            jac[(size_t)r * two_t + dg] = val;
+        }
+        for (int idx = g; idx < prm.rows_speed * D; idx += nthreads) {
+            const int r = idx / D, d = idx - r * D, dg = d0 + d;
+            if (dg >= two_t) continue;
+            const float val = ((r & 1) == (dg & 1)) ? ego_tangent(ego_kind, dt, r >> 1, dg >> 1).y : 0.f;
+            jac[(size_t)(prm.rows_control + r) * two_t + dg] = val;
+        }
+        const int base_mind = prm.rows_control + prm.rows_speed;
+        const bool want_mind = prm.rows_mind > 0;
+        float* cons = (prm.cons != nullptr && chunk == 0) ? prm.cons + ev * (size_t)N * T : nullptr;
+        // min-distance rows of level `level` (means complete): d ||ego_p - mu_p[k]|| for the D directions of the chunk
+        auto write_rows = [&](int level, const float4* mus_l, const float4* mud_l) {
+            if (!want_mind) return;
+            const float4 eg = ego[level];
+            for (int idx = g; idx < N * D; idx += nthreads) {
+                const int k = idx / D, d = idx - k * D, dg = d0 + d;
+                const float4 mu = mus_l[k];
+                const float dx = eg.x - mu.x, dy = eg.y - mu.y;
+                const float nn = sqrtf(dx * dx + dy * dy);
+                if (cons != nullptr && d == 0) cons[k * T + level] = nn;
+                if (dg >= two_t) continue;
+                float val = 0.f;
+                if (nn > 0.f) {
+                    const float4 md_ = mud_l[k * D + d];
+                    const float ep = ego_tangent(ego_kind, dt, level, dg >> 1).x;
+                    const float ex = (dg & 1) ? 0.f : ep, ey = (dg & 1) ? ep : 0.f;
+                    val = (dx * (ex - md_.x) + dy * (ey - md_.y)) / nn;
+                }
+                jac[(size_t)(base_mind + k * T + level) * two_t + dg] = val;
+            }
+        };
+        write_rows(0, mus, mud);
+
+        // first time index at which an ego tangent of this chunk is non-zero: control j acts on ego[t] for t >= j + 1
+        const int t_first = (d0 >> 1) + 1;
+
+        // ============================================================ forward rollout with tangents
+        for (int t = 0; t < T - 1; ++t) {
+            const int cur = t & 1, nxt = cur ^ 1;
+            const float4* mus_t = mus + cur * N;
+            const float4* mud_t = mud + cur * N * D;
+            const bool live = want_mind && t >= t_first && ENV != MTB_ENV_KALMAN;
+            if (active) {
+                V2 u;
+                float utx[D], uty[D];                               // tangent of the raw control
+#pragma unroll
+                for (int d = 0; d < D; ++d) { utx[d] = 0.f; uty[d] = 0.f; }
+                const float4 eg = ego[t];
+                // ego tangents of this chunk at time t
+                if (ENV == MTB_ENV_SOCIAL_FORCES) {
+                    const V2 fgoal = goal_force(p, v, goal, inv_tau, prm.pb.sf_goal_radius);
+                    if (live) {
+                        V2 gpx = v2(0.f, 0.f), gvx = v2(0.f, 0.f), gpy = v2(0.f, 0.f), gvy = v2(0.f, 0.f);
+                        goal_force_adjoint(p, v, goal, inv_tau, prm.pb.sf_goal_radius, v2(1.f, 0.f), gpx, gvx);
+                        goal_force_adjoint(p, v, goal, inv_tau, prm.pb.sf_goal_radius, v2(0.f, 1.f), gpy, gvy);
+#pragma unroll
+                        for (int d = 0; d < D; ++d) {
+                            utx[d] = dot(gpx, tp[d]) + dot(gvx, tv[d]);
+                            uty[d] = dot(gpy, tp[d]) + dot(gvy, tv[d]);
+                        }
+                    }
+                    V2 frep = v2(0.f, 0.f);
+                    for (int k = 0; k < N; ++k) {                   // same gate and order as evaluate_kernel
+                        if (k == m) continue;
+                        const float4 mu = mus_t[k];
+                        const float dx = p.x - mu.x, dy = p.y - mu.y;
+                        if (!(fmaf(dx, dx, dy * dy) <= prm.pair_cut2)) continue;
+                        const V2 r = p - v2(mu.x, mu.y), w = v - v2(mu.z, mu.w);
+                        const RepulsionFwd o = repulsion_forward(r, w, pv0, psig, dt, u_ped);
+                        frep = frep - o.force;
+                        if (live) {
+                            V2 rbx, wbx, rby, wby;
+                            repulsion_adjoint(o, r, w, dt, v2(1.f, 0.f), rbx, wbx);
+                            repulsion_adjoint(o, r, w, dt, v2(0.f, 1.f), rby, wby);
+#pragma unroll
+                            for (int d = 0; d < D; ++d) {
+                                const float4 md_ = mud_t[k * D + d];
+                                const V2 rd = tp[d] - v2(md_.x, md_.y), wd = tv[d] - v2(md_.z, md_.w);
+                                utx[d] -= dot(rbx, rd) + dot(wbx, wd);
+                                uty[d] -= dot(rby, rd) + dot(wby, wd);
+                            }
+                        }
+                    }
+                    u = fgoal + frep;
+                    {
+                        const V2 r = p - v2(eg.x, eg.y), w = v - v2(eg.z, eg.w);
+                        const RepulsionFwd o = repulsion_forward(r, w, pv0, psig, dt, u_ped);
+                        u = u - o.force;
+                        if (live) {
+                            V2 rbx, wbx, rby, wby;
+                            repulsion_adjoint(o, r, w, dt, v2(1.f, 0.f), rbx, wbx);
+                            repulsion_adjoint(o, r, w, dt, v2(0.f, 1.f), rby, wby);
+#pragma unroll
+                            for (int d = 0; d < D; ++d) {
+                                const int dg = d0 + d;
+                                const float2 et = ego_tangent(ego_kind, dt, t, dg >> 1);
+                                const V2 ep = (dg & 1) ? v2(0.f, et.x) : v2(et.x, 0.f);
+                                const V2 evv = (dg & 1) ? v2(0.f, et.y) : v2(et.y, 0.f);
+                                const V2 rd = tp[d] - ep, wd = tv[d] - evv;
+                                utx[d] -= dot(rbx, rd) + dot(wbx, wd);
+                                uty[d] -= dot(rby, rd) + dot(wby, wd);
+                            }
+                        }
+                    }
+                } else if (ENV == MTB_ENV_POTENTIAL_FIELD) {
+                    u = v;
+                    const V2 delta = v2(eg.x - p.x, eg.y - p.y);
+                    const bool gate = pf_gate(v, delta, prm.pb.pf_theta_max);
+                    if (gate) u = u + pf_impact(delta, pv0);
+                    if (live) {
+                        const V2 diag = gate ? pf_impact_adjoint(delta, pv0, v2(1.f, 1.f)) : v2(0.f, 0.f);
+#pragma unroll
+                        for (int d = 0; d < D; ++d) {
+                            const int dg = d0 + d;
+                            const float2 et = ego_tangent(ego_kind, dt, t, dg >> 1);
+                            const V2 ep = (dg & 1) ? v2(0.f, et.x) : v2(et.x, 0.f);
+                            utx[d] = tv[d].x + diag.x * (ep.x - tp[d].x);
+                            uty[d] = tv[d].y + diag.y * (ep.y - tp[d].y);
+                        }
+                    }
+                } else {
+                    u = v;
+                }
+                const V2 up = (ENV == MTB_ENV_KALMAN) ? u : feasible(u, u_ped);
+                if (live) {
+                    const V2 cx = feasible_adjoint(u, u_ped, v2(1.f, 0.f));
+                    const V2 cy = feasible_adjoint(u, u_ped, v2(0.f, 1.f));
+#pragma unroll
+                    for (int d = 0; d < D; ++d) {
+                        const V2 ud = v2(utx[d], uty[d]);
+                        tv[d] = v2(dot(cx, ud), dot(cy, ud));
+                        tp[d] = v2(fmaf(dt, tv[d].x, tp[d].x), fmaf(dt, tv[d].y, tp[d].y));
+                        qd[g * D + d] = make_float2(pw * tv[d].x, pw * tv[d].y);
+                    }
+                }
+                v = up;
+                p = v2(fmaf(dt, up.x, p.x), fmaf(dt, up.y, p.y));
+                V2 vel = v;
+                if (ENV != MTB_ENV_KALMAN && prm.pb.noise != nullptr) {
+                    const float* nz = prm.pb.noise + ((((size_t)s * (T - 1) + t) * N + m) * P + i) * 2;
+                    vel.x = fmaf(__ldg(nz), prm.pb.particle_noise, vel.x);
+                    vel.y = fmaf(__ldg(nz + 1), prm.pb.particle_noise, vel.y);
+                }
+                qbuf[g] = make_float2(vel.x * pw, vel.y * pw);
+            }
+            __syncthreads();
+            // collapse to the means of level t+1 and their tangents (particle.py:171-175)
+            if (active && i == 0) {
+                float sx = 0.f, sy = 0.f;
+                for (int j = 0; j < P; ++j) { sx += qbuf[g + j].x; sy += qbuf[g + j].y; }
+                const float4 c = mus_t[m];
+                mus[nxt * N + m] = make_float4(fmaf(c.z, dt, c.x), fmaf(c.w, dt, c.y), sx / (float)P, sy / (float)P);
+            }
+            for (int idx = g; idx < N * D; idx += nthreads) {
+                const int k = idx / D, d = idx - k * D;
+                const float4 c = mud_t[idx];
+                float sx = 0.f, sy = 0.f;
+                if (live) {
+                    for (int j = 0; j < P; ++j) { const float2 qq = qd[(k * P + j) * D + d]; sx += qq.x; sy += qq.y; }
+                    sx /= (float)P; sy /= (float)P;
+                }
+                mud[nxt * N * D + idx] = make_float4(fmaf(c.z, dt, c.x), fmaf(c.w, dt, c.y), sx, sy);
+            }
+            __syncthreads();
+            write_rows(t + 1, mus + nxt * N, mud + nxt * N * D);
+        }
+        __syncthreads();
+    }
+}
+
+static int plan_jacobian(const mtb_problem* pb, const mtb_modules* md, JParams& prm, int& grid, int& block, size_t& smem,
+                         int& dirs) {
+    const int err = validate(pb);
+    if (err != 0) return err;
+    if (pb->ego_kind == MTB_EGO_NONE || md == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    std::memset(&prm, 0, sizeof(prm));
+    prm.pb = *pb;
+    prm.md = *md;
+    const bool kalman = pb->env_kind == MTB_ENV_KALMAN;
+    prm.T = pb->t_horizon;
+    prm.N = pb->num_ados;
+    prm.P = kalman ? 1 : pb->num_particles;
+    prm.G = prm.N * prm.P;
+    prm.GP = round_up(prm.G, 32);
+    prm.MW = (prm.N + 31) / 32;
+    prm.pair_cut2 = pair_cut_squared(pb->sf_interaction_radius);
+    const ConstraintRows rows = constraint_rows(pb, md);
+    prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.R = rows.total;
+    if (prm.R == 0) return MTB_ERR_BAD_ARGUMENT;
+    dirs = (prm.GP <= 256) ? 8 : 4;
+    prm.n_chunks = (2 * prm.T + dirs - 1) / dirs;
+    prm.num_items = (long long)pb->num_scenes * pb->num_candidates * prm.n_chunks;
+    int off = 0;
+    prm.off_ctl = off; off += round_up(2 * prm.T, 4);
+    prm.off_ego = off; off += (prm.T + 1) * 4;
+    prm.off_mus = off; off += 2 * prm.N * 4;
+    prm.off_mud = off; off += 2 * prm.N * dirs * 4;
+    prm.off_q = off;   off += round_up(prm.GP * 2, 4);
+    prm.off_qd = off;  off += round_up(prm.GP * dirs * 2, 4);
+    smem = (size_t)off * sizeof(float);
+    const DeviceLimits lim = device_limits();
+    if (smem > (size_t)lim.max_smem) return MTB_ERR_TOO_LARGE;
+    block = prm.GP;
+    int per_sm = (int)((size_t)lim.smem_per_sm / (smem + 1024));
+    const int by_threads = (prm.GP <= 256 ? 1024 : 1024) / block;      // ~100 registers per thread
+    if (per_sm > by_threads) per_sm = by_threads;
+    if (per_sm > 32) per_sm = 32;
+    if (per_sm < 1) per_sm = 1;
+    long long gl = (long long)lim.sms * per_sm;
+    if (gl > prm.num_items) gl = prm.num_items;
+    grid = (int)gl;
+    return 0;
+}
+
+template <int ENV, int D, int MAXT>
+static int launch_jacobian_t(const JParams& prm, int grid, int block, size_t smem, cudaStream_t stream) {
+#ifndef MTB_HOST_EMUL
+    cudaError_t err = cudaFuncSetAttribute(jacobian_kernel<ENV, D, MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return (int)err;
+#endif
+    MTB_LAUNCH((jacobian_kernel<ENV, D, MAXT>), grid, block, smem, stream, prm);
+#ifndef MTB_HOST_EMUL
+    return (int)cudaGetLastError();
+#else
+    return 0;
+#endif
+}
+
+template <int ENV>
+static int launch_jacobian(const JParams& prm, int grid, int block, size_t smem, int dirs, cudaStream_t stream) {
+    if (dirs == 8) return launch_jacobian_t<ENV, 8, 256>(prm, grid, block, smem, stream);
+    return launch_jacobian_t<ENV, 4, kMaxThreads>(prm, grid, block, smem, stream);
+}
+
+}  // namespace mtb
+
+extern "C" {
+
+size_t mtb_jacobian_workspace_bytes(const mtb_problem*) { return 0; }   // everything lives in shared memory
+
+int mtb_constraint_jacobian(const mtb_problem* problem, const mtb_modules* modules, float* cons, float* jac,
+                            void* /*workspace*/, size_t /*workspace_bytes*/, void* stream) {
+    if (jac == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    mtb::JParams prm;
+    int grid = 0, block = 0, dirs = 0;
+    size_t smem = 0;
+    const int err = mtb::plan_jacobian(problem, modules, prm, grid, block, smem, dirs);
+    if (err != 0) return err;
+    prm.cons = cons;
+    prm.jac = jac;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    switch (problem->env_kind) {
+        case MTB_ENV_SOCIAL_FORCES: return mtb::launch_jacobian<MTB_ENV_SOCIAL_FORCES>(prm, grid, block, smem, dirs, st);
+        case MTB_ENV_POTENTIAL_FIELD: return mtb::launch_jacobian<MTB_ENV_POTENTIAL_FIELD>(prm, grid, block, smem, dirs, st);
+        default: return mtb::launch_jacobian<MTB_ENV_KALMAN>(prm, grid, block, smem, dirs, st);
+    }
+}
+
+}  // extern "C"

@@ -12,31 +12,11 @@
 //                          folded through the integrator dynamics into the control gradient; no autograd graph.
 //
 // The same source compiles for the host emulation used by the CPU tests (tests/host_emul, -DMTB_HOST_EMUL).
-#ifdef MTB_HOST_EMUL
-#include "cuda_shim.h"
-#else
-#include <cuda_runtime.h>
-#include <math_constants.h>
-#define MTB_SHARED_FLOAT4(name) extern __shared__ float4 name[]
-#define MTB_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
-// named barrier over `count` threads (a multiple of 32): synchronises one evaluation group, not the whole block
-static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
-}
-#endif
-
-#include <cfloat>
-#include <cmath>
-#include <cstdint>
-#include <cstdlib>
-#include <cstring>
-
-#include "mantrap_b200.h"
+#include "mtb_common.cuh"
 #include "mtb_math.cuh"
 
 namespace mtb {
 
-constexpr int kMaxThreads = 1024;
 constexpr int kDefaultBlock = 256;
 
 struct KParams {
@@ -709,66 +689,10 @@ __global__ void argmin_kernel(const float* __restrict__ total, const float* __re
 // ---------------------------------------------------------------------------------------------------------
 // host side: launch geometry
 // ---------------------------------------------------------------------------------------------------------
-static int round_up(int x, int m) { return (x + m - 1) / m * m; }
-
 // development knobs (read once per call; unset in production)
 static int env_flag(const char* name) {
     const char* v = std::getenv(name);
     return (v != nullptr && v[0] != '\0') ? std::atoi(v) : 0;
-}
-
-struct DeviceLimits {
-    int sms;
-    int max_smem;      // opt-in dynamic shared memory per block
-    int smem_per_sm;
-};
-
-static DeviceLimits device_limits() {
-    DeviceLimits lim;
-#ifdef MTB_HOST_EMUL
-    lim.sms = 2;
-    lim.max_smem = 227 * 1024;
-    lim.smem_per_sm = 228 * 1024;
-#else
-    int dev = 0;
-    lim.sms = 148; lim.max_smem = 227 * 1024; lim.smem_per_sm = 228 * 1024;   // B200 defaults (no device present)
-    if (cudaGetDevice(&dev) == cudaSuccess) {
-        int v = 0;
-        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) lim.sms = v;
-        if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) == cudaSuccess && v > 0) lim.max_smem = v;
-        if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev) == cudaSuccess && v > 0) lim.smem_per_sm = v;
-    } else {
-        (void)cudaGetLastError();
-    }
-#endif
-    return lim;
-}
-
-static int validate(const mtb_problem* pb) {
-    if (pb == nullptr) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->num_scenes < 1 || pb->num_candidates < 1 || pb->t_horizon < 1 || pb->num_ados < 1) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->num_ados > MTB_MAX_ADOS || pb->t_horizon > MTB_MAX_HORIZON) return MTB_ERR_TOO_LARGE;
-    if (pb->env_kind < 0 || pb->env_kind > MTB_ENV_KALMAN || pb->ego_kind < 0 || pb->ego_kind > MTB_EGO_NONE) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->env_kind != MTB_ENV_KALMAN && pb->num_particles < 1) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->ego_kind == MTB_EGO_NONE && pb->num_candidates != 1) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->ado0 == nullptr) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->ego_kind != MTB_EGO_NONE && (pb->ego0 == nullptr || pb->controls == nullptr)) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->env_kind != MTB_ENV_KALMAN && (pb->v0 == nullptr || pb->weight == nullptr)) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->env_kind == MTB_ENV_SOCIAL_FORCES && (pb->sigma == nullptr || pb->ado_goal == nullptr)) return MTB_ERR_BAD_ARGUMENT;
-    const int particles = pb->num_ados * (pb->env_kind == MTB_ENV_KALMAN ? 1 : pb->num_particles);
-    if (particles > kMaxThreads) return MTB_ERR_TOO_LARGE;
-    return 0;
-}
-
-static float pair_cut_squared(float radius) {
-    // largest float d2 with sqrtf(d2) <= radius, so that `d2 <= cut` decides exactly like `norm <= radius`
-    float cut = radius * radius;
-    while (sqrtf(cut) > radius) cut = nextafterf(cut, 0.f);
-    for (;;) {
-        const float nxt = nextafterf(cut, INFINITY);
-        if (sqrtf(nxt) <= radius) cut = nxt; else break;
-    }
-    return cut;
 }
 
 static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs* out, bool want_grad, KParams& prm,
@@ -796,13 +720,10 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         prm.GP = round_up(prm.G, 32);
     }
     // constraint rows
-    prm.rows_control = prm.rows_speed = prm.rows_mind = 0;
-    if (md != nullptr && prm.has_ego) {
-        if (md->con_control) prm.rows_control = (pb->ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) ? 2 * prm.T : prm.T;
-        if (md->con_speed) prm.rows_speed = 2 * (prm.T + 1);
-        if (md->con_min_distance) prm.rows_mind = prm.N * prm.T;
+    {
+        const ConstraintRows rows = constraint_rows(pb, md);
+        prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.R = rows.total;
     }
-    prm.R = prm.rows_control + prm.rows_speed + prm.rows_mind;
 
     const DeviceLimits lim = device_limits();
     const bool need_tape = want_grad && !kalman && prm.has_ego && prm.T > 1;
@@ -1007,12 +928,6 @@ int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, i
 #else
     return 0;
 #endif
-}
-
-size_t mtb_jacobian_workspace_bytes(const mtb_problem*) { return 0; }
-
-int mtb_constraint_jacobian(const mtb_problem*, const mtb_modules*, float*, float*, void*, size_t, void*) {
-    return MTB_ERR_BAD_ARGUMENT;   // implemented in mtb_jacobian.cu (forward-mode tangent kernel)
 }
 
 #ifdef MTB_HOST_EMUL

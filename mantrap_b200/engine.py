@@ -177,6 +177,26 @@ def launch_evaluate(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Option
     return res
 
 
+def launch_jacobian(lib: ctypes.CDLL, scene: SceneBatch, controls: torch.Tensor, spec: ModuleSpec, stream: int = 0,
+                    want_values: bool = False):
+    """One `mtb_constraint_jacobian` launch: dense UN-normalised Jacobian [S,C,R,2T] of every constraint row enabled
+    in `spec` (control | speed | min-distance, the row order of `cons`) w.r.t. the flattened controls; optionally the
+    un-normalised min-distance values [S,C,N,T]."""
+    t_horizon = controls.shape[2]
+    pb = _problem_struct(scene, controls, t_horizon)
+    md = _module_struct(scene, spec)
+    rows = lib.mtb_num_constraint_rows(ctypes.byref(pb), ctypes.byref(md))
+    if rows <= 0:
+        _cabi.check(lib, rows if rows < 0 else -1, "mtb_num_constraint_rows")
+    s, c, n = pb.num_scenes, pb.num_candidates, pb.num_ados
+    jac = torch.empty((s, c, rows, 2 * t_horizon), dtype=torch.float32, device=scene.device)
+    values = torch.empty((s, c, n, t_horizon), dtype=torch.float32, device=scene.device) \
+        if (want_values and spec.min_distance) else None
+    code = lib.mtb_constraint_jacobian(ctypes.byref(pb), ctypes.byref(md), _cabi.ptr(values), _cabi.ptr(jac), None, 0, stream)
+    _cabi.check(lib, code, "mtb_constraint_jacobian")
+    return (jac, values) if want_values else jac
+
+
 def query_launch(lib: ctypes.CDLL, scene: SceneBatch, controls: torch.Tensor, want_grad: bool) -> typing.Dict[str, int]:
     pb = _problem_struct(scene, controls, controls.shape[2])
     info = _cabi.MtbLaunchInfo()
@@ -235,6 +255,14 @@ class Engine:
             res = launch_evaluate(self.lib, scene.without_ego(), None, None, want, t_horizon=t_horizon, stream=self._stream())
         self.launches += 1
         return {k: v[:, 0] for k, v in res.items() if not k.startswith("_")}
+
+    def constraint_jacobian(self, scene: SceneBatch, controls: torch.Tensor, spec: ModuleSpec, want_values: bool = False):
+        """Dense constraint Jacobian [S,C,R,2T] (forward-mode tangent kernel)."""
+        self._check(scene.ado0, controls)
+        with torch.cuda.device(self.device):
+            out = launch_jacobian(self.lib, scene, controls, spec, stream=self._stream(), want_values=want_values)
+        self.launches += 1
+        return out
 
     def argmin(self, total, violation, controls, feas_tol: float = constants.SOLVER_CONSTRAINT_LIMIT):
         self._check(total, violation, controls)

@@ -98,6 +98,70 @@ def check_constraints(lib, device, name):
     gio.assert_parity(np_(res["violation"][0, 0]), expect_vio, 1e-4, "violation", atol=1e-6)
 
 
+def check_jacobian_golden(lib, device, name):
+    """Constraint Jacobian kernel against the reference's `module.jacobian` vectors (control / speed limits: analytic,
+    min-distance: row-by-row autograd through the reference rollout)."""
+    g = gio.load(name)
+    scene = scene_from_golden(g, device)
+    t_hor, n = int(g["T"]), g["ado0"].shape[0]
+    controls = gio.t(g["controls"])[None, None].to(device).contiguous()
+    has_mind = "jac_min_distance" in g
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=has_mind)
+    jac, values = engine.launch_jacobian(lib, scene, controls, spec, want_values=True)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    jac = np_(jac[0, 0])
+    n_ctl = 2 * t_hor if str(g["ego_kind"]) == "double" else t_hor
+    n_spd = 2 * (t_hor + 1)
+    assert jac.shape == (n_ctl + n_spd + (n * t_hor if has_mind else 0), 2 * t_hor)
+    if str(g["ego_kind"]) == "double":       # single integrator: the reference returns a 2T x 2T identity for T rows
+        gio.assert_parity(jac[:n_ctl], g["jac_control_limits"].reshape(n_ctl, 2 * t_hor), gio.RTOL_GRAD, "jac control")
+    gio.assert_parity(jac[n_ctl:n_ctl + n_spd], g["jac_speed_limits"].reshape(n_spd, 2 * t_hor), gio.RTOL_GRAD, "jac speed")
+    # the speed rows are the velocity rows of dx_du (linear.py:169-196)
+    dx_du = g["dx_du"].reshape(t_hor + 1, 5, 2 * t_hor)
+    gio.assert_parity(jac[n_ctl:n_ctl + n_spd].reshape(t_hor + 1, 2, -1), dx_du[:, 2:4], gio.RTOL_GRAD, "dx_du velocity rows")
+    if has_mind:
+        gio.assert_parity(np_(values[0, 0]).flatten(), g["con_min_distance"], gio.RTOL_ROLLOUT, "min-distance values")
+        gio.assert_parity(jac[n_ctl + n_spd:], g["jac_min_distance"].reshape(n * t_hor, 2 * t_hor), gio.RTOL_GRAD, "jac min-distance")
+
+
+def check_jacobian_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, seed=0):
+    """Random batch through the tangent kernel vs. row-by-row autograd of the CPU oracle (optimization_module.py:428-434)."""
+    from oracle import torch_oracle as to
+    from mantrap_b200 import scenarios
+    scene_cpu = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=400 + seed,
+                                           param_seed=500 + seed, regular_sigma=True)
+    controls_cpu = scenarios.candidate_controls(num_scenes, num_candidates, t_hor, seed=600 + seed, u_max=1.0)
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True)
+    jac, values = engine.launch_jacobian(lib, scene_cpu.to(device), controls_cpu.to(device).contiguous(), spec, want_values=True)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    jac, values = np_(jac), np_(values)
+    n_ctl = 2 * t_hor if ego_kind == "double" else t_hor
+    n_spd = 2 * (t_hor + 1)
+    osc = oracle_scene(scene_cpu, num_candidates)
+    worst = 0.0
+    for b in range(num_scenes * num_candidates):
+        one = to.Scene(*[(x[b:b + 1] if isinstance(x, torch.Tensor) else x) for x in osc])
+        u = controls_cpu.reshape(-1, t_hor, 2)[b:b + 1]
+        g_ref, j_ref = to.min_distance_jacobian(one, u)
+        g64, j64 = to.min_distance_jacobian(to.scene_to(one, torch.float64), u.double())
+        floor = float((j_ref.double() - j64).abs().max())
+        sc, c = divmod(b, num_candidates)
+        gio.assert_parity(values[sc, c].flatten(), g_ref.numpy(), gio.RTOL_ROLLOUT, "min-distance values", atol=gio.ATOL + 1e-6)
+        worst = max(worst, gio.assert_parity(jac[sc, c, n_ctl + n_spd:], j_ref.numpy(), gio.RTOL_GRAD, "jac min-distance",
+                                             atol=gio.ATOL + 2 * floor))
+        # control / speed rows against autograd of the oracle's constraint functions
+        uu = u.clone().requires_grad_(True)
+        et = to.ego_unroll(one.ego0, uu, one.dt, ego_kind)
+        rows = torch.cat((to.control_limit_raw(et, one.dt, ego_kind)[0], to.speed_limit_raw(et)[0]))
+        j_cs = torch.stack([torch.autograd.grad(r, uu, retain_graph=True)[0].flatten() for r in rows]).numpy()
+        if ego_kind == "double":                 # reference quirk: identity even for negative controls
+            j_cs[:n_ctl] = np.eye(n_ctl)
+        gio.assert_parity(jac[sc, c, :n_ctl + n_spd], j_cs, gio.RTOL_GRAD, "jac control+speed", atol=1e-6)
+    return worst
+
+
 def oracle_scene(scene, num_candidates):
     """Expand a SceneBatch (CPU copy) to the oracle's per-evaluation batch layout [S*C, ...]."""
     from oracle import torch_oracle as to

@@ -50,6 +50,24 @@ def test_batched_vs_oracle(eng, env_kind, ego_kind, s, c, n, p, t_hor, weights):
     kc.check_batched_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)
 
 
+@pytest.mark.parametrize("name", gio.case_names())
+def test_jacobian_golden(eng, name):
+    kc.check_jacobian_golden(eng.lib, DEV, name)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 2, 3, 4, 3, 10),
+    ("sf", "single", 2, 2, 12, 3, 8),
+    ("sf", "double", 1, 2, 10, 4, 20),          # config-3 shape
+    ("sf", "double", 1, 1, 40, 8, 6),           # 320 particles: D = 4 instantiation
+    ("pf", "double", 1, 3, 5, 5, 15),
+    ("pf", "single", 2, 2, 7, 2, 9),
+    ("kalman", "double", 1, 2, 5, 1, 15),
+])
+def test_jacobian_vs_oracle(eng, env_kind, ego_kind, s, c, n, p, t_hor):
+    kc.check_jacobian_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor)
+
+
 def test_argmin(eng):
     total = torch.tensor([[3.0, 1.0, 2.0, 0.5], [4.0, -1.0, 5.0, 6.0], [1.0, 2.0, 3.0, 4.0]], device=DEV)
     vio = torch.tensor([[0.0, 0.0, 0.0, 1.0], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]], device=DEV)

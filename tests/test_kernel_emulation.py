@@ -51,6 +51,21 @@ def test_batched_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor, weig
     kc.check_batched_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights)
 
 
+@pytest.mark.parametrize("name", gio.case_names())
+def test_jacobian_golden(emul_lib, name):
+    kc.check_jacobian_golden(emul_lib, "cpu", name)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 2, 2, 4, 3, 6),
+    ("sf", "single", 1, 2, 5, 2, 5),
+    ("pf", "double", 1, 2, 5, 3, 7),
+    ("kalman", "double", 1, 1, 3, 1, 5),
+])
+def test_jacobian_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor):
+    kc.check_jacobian_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor)
+
+
 def test_argmin(emul_lib):
     total = torch.tensor([[3.0, 1.0, 2.0, 0.5], [4.0, -1.0, 5.0, 6.0], [1.0, 2.0, 3.0, 4.0]])
     vio = torch.tensor([[0.0, 0.0, 0.0, 1.0], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]])
