@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define MTB_ABI_VERSION 1
+#define MTB_ABI_VERSION 2
 
 /* environment kinds: mantrap/environment/social_forces.py, simplified/potential_field.py, simplified/kalman.py */
 #define MTB_ENV_SOCIAL_FORCES 0
@@ -74,6 +74,10 @@ typedef struct mtb_problem {
     const float* weight;    /* [S,N,P] cdf weights, already normalised over the ado axis (particle.py:62,79,141) */
     const float* noise;     /* [S,T-1,N,P,2] U(0,1) velocity noise (particle.py:165) or NULL = no noise */
     const float* controls;  /* [S,C,T,2] (unused for MTB_EGO_NONE) */
+    const float* ego_traj;  /* optional [S,C,T+1,4]: ego trajectory GIVEN instead of unrolled from the controls -- the
+                             * module interface objective(ego_trajectory) / gradient(ego_trajectory, grad_wrt=controls)
+                             * (optimization_module.py:75-179); `controls` may then be NULL. ego_kind still says how the
+                             * trajectory depends on the controls (gradient fold, control rows). */
 } mtb_problem;
 
 /* Objective / constraint modules (mantrap/modules). A weight of 0 switches a module off. */
@@ -95,6 +99,11 @@ typedef struct mtb_modules {
     float v_max;            /* normaliser + symmetric bound of speed rows */
     float min_distance;     /* lower bound of min-distance rows (not normalised) */
     float violation_eps;    /* constants.py:108 */
+    /* Optional external adjoint seeds: d(loss)/d(mus) [S,C,N,T,4] and d(loss)/d(sigmas) [S,C,N,T,2] of a loss the
+     * CALLER computed from the rollout outputs (torch.autograd.Function backward of compute_distributions,
+     * graph_based.py:362-381); added to the seeds of the fused objectives. Level 0 is the current state (no gradient). */
+    const float* seed_mus;
+    const float* seed_sigmas;
 } mtb_modules;
 
 /* Outputs; every pointer may be NULL (= not wanted). */
@@ -102,7 +111,9 @@ typedef struct mtb_outputs {
     float* obj;        /* [S,C,4] weighted+normalised goal, acc, vel, pos objectives (what module.objective returns) */
     float* obj_raw;    /* [S,C,4] raw, un-clamped costs */
     float* total;      /* [S,C] sum of obj */
-    float* grad;       /* [S,C,T,2] gradient of total w.r.t. controls; NULL = forward only */
+    float* grad;       /* [S,C,T,2] gradient of total (+ seeded loss) w.r.t. controls */
+    float* grad_traj;  /* [S,C,T+1,4] the same gradient w.r.t. the ego trajectory rows (px,py,vx,vy), before it is
+                        * folded through the ego dynamics. grad == NULL && grad_traj == NULL = forward only */
     float* cons;       /* [S,C,R] normalised constraint rows: control (2T or T) | speed 2(T+1) | min-distance N*T */
     float* violation;  /* [S,C] summed constraint violation (optimization_module.py:512-533) */
     float* ego_traj;   /* [S,C,T+1,4] */
@@ -148,6 +159,19 @@ size_t mtb_jacobian_workspace_bytes(const mtb_problem* problem);
 int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, int32_t num_candidates,
                float feas_tol, const float* controls, int32_t t_horizon, int32_t* best_idx, float* best_val,
                float* best_controls, void* stream);
+
+/* Batched ego (robot) dynamics, state rows (px, py, vx, vy, time); device pointers.
+ *   mtb_ego_unroll          LinearDTAgent.unroll_trajectory  agents/base/linear.py:68-105   x0[B,5], controls[B,T,2] -> [B,T+1,5]
+ *   mtb_ego_roll            LinearDTAgent.roll_trajectory    agents/base/linear.py:107-130  trajectory[B,T+1,5] -> controls[B,T,2]
+ *   mtb_ego_unroll_adjoint  autograd through unroll_trajectory: grad_trajectory[B,T+1,5] -> grad_controls[B,T,2]
+ *   mtb_ego_dx_du           LinearDTAgent.dx_du              agents/base/linear.py:169-196  -> out[5(T+1), 2T] */
+int mtb_ego_unroll(int ego_kind, float dt, const float* x0, const float* controls, int32_t batch, int32_t t_horizon,
+                   float* trajectory, void* stream);
+int mtb_ego_roll(int ego_kind, float dt, const float* trajectory, int32_t batch, int32_t t_horizon, float* controls,
+                 void* stream);
+int mtb_ego_unroll_adjoint(int ego_kind, float dt, const float* grad_trajectory, int32_t batch, int32_t t_horizon,
+                           float* grad_controls, void* stream);
+int mtb_ego_dx_du(int ego_kind, float dt, int32_t t_horizon, float* out, void* stream);
 
 /* benchmark support: launches `grid` blocks of 256 threads running 8 dependent chains of `iters` FP32 FMAs
  * (kind 0, 16*iters flop per thread) or MUFU rsqrt (kind 1, 8*iters ops per thread); out[grid*256] floats. */

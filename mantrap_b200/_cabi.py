@@ -12,6 +12,7 @@ import torch
 ENV_SOCIAL_FORCES, ENV_POTENTIAL_FIELD, ENV_KALMAN = 0, 1, 2
 EGO_DOUBLE_INTEGRATOR, EGO_SINGLE_INTEGRATOR, EGO_NONE = 0, 1, 2
 MAX_ADOS, MAX_HORIZON = 64, 64
+ABI_VERSION = 2
 
 _f, _i, _p = ctypes.c_float, ctypes.c_int32, ctypes.c_void_p
 
@@ -23,7 +24,7 @@ class MtbProblem(ctypes.Structure):
                 ("sf_interaction_radius", _f), ("pf_theta_max", _f), ("particle_noise", _f), ("var_initial", _f),
                 ("kalman_noise", _f),
                 ("ego0", _p), ("ado0", _p), ("ado_goal", _p), ("v0", _p), ("sigma", _p), ("weight", _p),
-                ("noise", _p), ("controls", _p)]
+                ("noise", _p), ("controls", _p), ("ego_traj", _p)]
 
 
 class MtbModules(ctypes.Structure):
@@ -31,11 +32,12 @@ class MtbModules(ctypes.Structure):
                 ("max_acc", _f), ("max_vel", _f), ("max_pos", _f),
                 ("ego_goal", _p), ("mus_wo", _p), ("ado_mask", _p),
                 ("con_control", _i), ("con_speed", _i), ("con_min_distance", _i),
-                ("u_max", _f), ("v_max", _f), ("min_distance", _f), ("violation_eps", _f)]
+                ("u_max", _f), ("v_max", _f), ("min_distance", _f), ("violation_eps", _f),
+                ("seed_mus", _p), ("seed_sigmas", _p)]
 
 
 class MtbOutputs(ctypes.Structure):
-    _fields_ = [("obj", _p), ("obj_raw", _p), ("total", _p), ("grad", _p), ("cons", _p), ("violation", _p),
+    _fields_ = [("obj", _p), ("obj_raw", _p), ("total", _p), ("grad", _p), ("grad_traj", _p), ("cons", _p), ("violation", _p),
                 ("ego_traj", _p), ("mus", _p), ("sigmas", _p), ("stats", _p)]
 
 
@@ -46,7 +48,8 @@ class MtbLaunchInfo(ctypes.Structure):
 
 EXPORTED_SYMBOLS = ("mtb_abi_version", "mtb_error_string", "mtb_num_constraint_rows", "mtb_workspace_bytes",
                     "mtb_evaluate", "mtb_query_launch", "mtb_constraint_jacobian", "mtb_jacobian_workspace_bytes",
-                    "mtb_argmin", "mtb_probe_launch")
+                    "mtb_argmin", "mtb_probe_launch", "mtb_ego_unroll", "mtb_ego_roll", "mtb_ego_unroll_adjoint",
+                    "mtb_ego_dx_du")
 
 
 def bind(lib: ctypes.CDLL) -> ctypes.CDLL:
@@ -68,6 +71,11 @@ def bind(lib: ctypes.CDLL) -> ctypes.CDLL:
     lib.mtb_jacobian_workspace_bytes.restype, lib.mtb_jacobian_workspace_bytes.argtypes = ctypes.c_size_t, [pp]
     lib.mtb_probe_launch.restype = ctypes.c_int
     lib.mtb_probe_launch.argtypes = [ctypes.c_int, _p, ctypes.c_int, ctypes.c_int, _p]
+    lib.mtb_ego_unroll.restype, lib.mtb_ego_unroll.argtypes = ctypes.c_int, [ctypes.c_int, _f, _p, _p, _i, _i, _p, _p]
+    lib.mtb_ego_roll.restype, lib.mtb_ego_roll.argtypes = ctypes.c_int, [ctypes.c_int, _f, _p, _i, _i, _p, _p]
+    lib.mtb_ego_unroll_adjoint.restype = ctypes.c_int
+    lib.mtb_ego_unroll_adjoint.argtypes = [ctypes.c_int, _f, _p, _i, _i, _p, _p]
+    lib.mtb_ego_dx_du.restype, lib.mtb_ego_dx_du.argtypes = ctypes.c_int, [ctypes.c_int, _f, _i, _p, _p]
     lib.mtb_argmin.restype = ctypes.c_int
     lib.mtb_argmin.argtypes = [_p, _p, _i, _i, _f, _p, _i, _p, _p, _p, _p]
     return lib

@@ -16,7 +16,7 @@ def load() -> ctypes.CDLL:
             raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -m mantrap_b200.build` "
                                "(mantrap_b200 has no CPU fallback)")
         lib = _cabi.bind(ctypes.CDLL(LIB_PATH))
-        if lib.mtb_abi_version() != 1:
+        if lib.mtb_abi_version() != _cabi.ABI_VERSION:
             raise RuntimeError("mantrap_b200: ABI version mismatch between the Python package and the library")
         _LIB = lib
     return _LIB

@@ -3,6 +3,7 @@
 ID_EGO = "ego"                                   # :4
 
 PED_SPEED_MAX = 2.5                              # :28 [m/s]
+PED_ACC_MAX = 20.0                               # :30 (not used by the reference either)
 ROBOT_SPEED_MAX = 2.0                            # :30 [m/s]
 ROBOT_ACC_MAX = 2.0                              # :31 [m/s^2]
 

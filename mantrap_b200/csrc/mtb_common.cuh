@@ -64,7 +64,7 @@ static inline int validate(const mtb_problem* pb) {
     if (pb->env_kind != MTB_ENV_KALMAN && pb->num_particles < 1) return MTB_ERR_BAD_ARGUMENT;
     if (pb->ego_kind == MTB_EGO_NONE && pb->num_candidates != 1) return MTB_ERR_BAD_ARGUMENT;
     if (pb->ado0 == nullptr) return MTB_ERR_BAD_ARGUMENT;
-    if (pb->ego_kind != MTB_EGO_NONE && (pb->ego0 == nullptr || pb->controls == nullptr)) return MTB_ERR_BAD_ARGUMENT;
+    if (pb->ego_kind != MTB_EGO_NONE && pb->ego_traj == nullptr && (pb->ego0 == nullptr || pb->controls == nullptr)) return MTB_ERR_BAD_ARGUMENT;
     if (pb->env_kind != MTB_ENV_KALMAN && (pb->v0 == nullptr || pb->weight == nullptr)) return MTB_ERR_BAD_ARGUMENT;
     if (pb->env_kind == MTB_ENV_SOCIAL_FORCES && (pb->sigma == nullptr || pb->ado_goal == nullptr)) return MTB_ERR_BAD_ARGUMENT;
     const int particles = pb->num_ados * (pb->env_kind == MTB_ENV_KALMAN ? 1 : pb->num_particles);

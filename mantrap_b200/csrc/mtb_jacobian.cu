@@ -67,13 +67,26 @@ __global__ void __launch_bounds__(MAXT) jacobian_kernel(const JParams prm) {
         const int s = (int)(ev / (size_t)prm.pb.num_candidates);
         float* jac = prm.jac + ev * (size_t)R * two_t;
 
-        const float* u_g = prm.pb.controls + ev * (size_t)two_t;
-        for (int idx = g; idx < two_t; idx += nthreads) ctl[idx] = __ldg(u_g + idx);
+        const bool traj_given = prm.pb.ego_traj != nullptr;
+        if (!traj_given) {
+            const float* u_g = prm.pb.controls + ev * (size_t)two_t;
+            for (int idx = g; idx < two_t; idx += nthreads) ctl[idx] = __ldg(u_g + idx);
+        } else {                                                    // module interface: jacobian(ego_trajectory, ...)
+            const float* x_g = prm.pb.ego_traj + ev * (size_t)(T + 1) * 4;
+            for (int t = g; t <= T; t += nthreads) ego[t] = *reinterpret_cast<const float4*>(x_g + t * 4);
+        }
         const float* ado0_s = prm.pb.ado0 + (size_t)s * N * 4;
         for (int k = g; k < N; k += nthreads) mus[k] = *reinterpret_cast<const float4*>(ado0_s + k * 4);
         for (int idx = g; idx < 2 * N * D; idx += nthreads) mud[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncthreads();
-        if (g == 0) {
+        if (traj_given) {                                           // controls by inverse dynamics (roll_trajectory)
+            for (int t = g; t < T; t += nthreads) {
+                const float4 a = ego[t], b = ego[t + 1];
+                const bool dbl = ego_kind == MTB_EGO_DOUBLE_INTEGRATOR;
+                ctl[2 * t] = dbl ? (b.z - a.z) / dt : (b.x - a.x) / dt;
+                ctl[2 * t + 1] = dbl ? (b.w - a.w) / dt : (b.y - a.y) / dt;
+            }
+        } else if (g == 0) {
             const float4 x0 = *reinterpret_cast<const float4*>(prm.pb.ego0 + (size_t)s * 4);
             float px = x0.x, py = x0.y, vx = x0.z, vy = x0.w;
             ego[0] = x0;

@@ -108,9 +108,10 @@ MTB_DEV float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p);
 
 // Adjoint seed of the interaction objectives on mus[k, level] (level >= 1): (d/d mu_p, d/d mu_v).
 MTB_DEV float4 objective_seed(const KParams& prm, const float* misc, const float4* mus, const float* wo_scene,
-                              int k, int level, bool in_cost) {
+                              const float* seed_mus_ev, int k, int level, bool in_cost) {
     float4 sd = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (!in_cost) return sd;
+    if (seed_mus_ev != nullptr) sd = ld4(seed_mus_ev + (k * prm.T + level) * 4);   // caller's d(loss)/d(mus[k, level])
+    if (!in_cost || wo_scene == nullptr) return sd;
     const int T = prm.T, N = prm.N;
     const float cacc = misc[kCoefAcc], cvel = misc[kCoefVel], cpos = misc[kCoefPos];
     const float4 cur = mus[level * N + k];
@@ -205,9 +206,14 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
         const int s = (int)(ev / (size_t)prm.pb.num_candidates);
 
         // ------------------------------------------------------------------ controls -> ego trajectory
-        if (has_ego) {
+        const bool traj_given = prm.pb.ego_traj != nullptr;
+        if (has_ego && !traj_given) {
             const float* u_g = prm.pb.controls + ev * (size_t)(2 * T);
             for (int idx = g; idx < 2 * T; idx += GP) ctl[idx] = __ldg(u_g + idx);
+        }
+        if (has_ego && traj_given) {
+            const float* x_g = prm.pb.ego_traj + ev * (size_t)(T + 1) * 4;
+            for (int t = g; t <= T; t += GP) ego[t] = ld4(x_g + t * 4);
         }
         const float* ado0_s = prm.pb.ado0 + (size_t)s * N * 4;
         for (int k = g; k < N; k += GP) mus[k] = ld4(ado0_s + k * 4);
@@ -216,7 +222,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             for (int idx = g; idx <= T; idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         group_sync(GP, e);
-        if (has_ego && g == 0) {
+        if (has_ego && !traj_given && g == 0) {
             const float4 x0 = ld4(prm.pb.ego0 + (size_t)s * 4);
             float px = x0.x, py = x0.y, vx = x0.z, vy = x0.w;
             ego[0] = x0;
@@ -502,7 +508,10 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             // per group: anything to back-propagate through the environment? (saturated objectives have zero
             // gradient). For sub-warp groups the other groups of the warp may differ, so no early exit: the
             // shuffles below are executed by every lane.
-            const bool env_adjoint = prm.want_env_adjoint != 0 && misc[kNeedAdjoint] != 0.f;
+            const float* seed_mus_ev = (prm.md.seed_mus != nullptr) ? prm.md.seed_mus + ev * (size_t)N * T * 4 : nullptr;
+            const float* seed_sig_ev = (prm.md.seed_sigmas != nullptr) ? prm.md.seed_sigmas + ev * (size_t)N * T * 2 : nullptr;
+            const bool env_adjoint = prm.want_env_adjoint != 0 &&
+                                     (misc[kNeedAdjoint] != 0.f || seed_mus_ev != nullptr || seed_sig_ev != nullptr);
             bool any_adjoint = env_adjoint;
             if (GP <= 32) any_adjoint = __ballot_sync(0xffffffffu, env_adjoint) != 0u;
             V2 pbar = v2(0.f, 0.f), vbar = v2(0.f, 0.f);
@@ -516,15 +525,13 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 V2 eb_p = v2(0.f, 0.f), eb_v = v2(0.f, 0.f);      // this particle's share of the ego adjoint at t
                 if (active && env_adjoint) {
                     float4 tot = abar[b_next * N + m];            // pair terms of step t+1 ...
-                    const float4 sd = objective_seed(prm, misc, mus, wo_scene, m, t + 1, in_cost);
+                    const float4 sd = objective_seed(prm, misc, mus, wo_scene, seed_mus_ev, m, t + 1, in_cost);
                     tot.x += sd.x + rec.x; tot.y += sd.y + rec.y; // ... + objective seed + mean-position recurrence
                     tot.z += sd.z + rec.z; tot.w += sd.w + rec.w;
                     rec = make_float4(tot.x, tot.y, dt * tot.x, dt * tot.y);   // (identical in the P threads of ado m)
                     // mu_v[t+1] = (1/P) sum_i w_i (v'_i + noise)
                     vbar.x = fmaf(tot.z, w_over_p, vbar.x);
                     vbar.y = fmaf(tot.w, w_over_p, vbar.y);
-                    // v' = u', p' = p + dt u'
-                    const V2 upbar = v2(fmaf(dt, pbar.x, vbar.x), fmaf(dt, pbar.y, vbar.y));
                     const float4 tp = tape[(size_t)t * tape_stride + tape_idx];
                     const V2 pt = v2(tp.x, tp.y), ut = v2(tp.z, tp.w);
                     V2 vt = v_init;
@@ -532,6 +539,23 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                         const float4 tq = tape[(size_t)(t - 1) * tape_stride + tape_idx];
                         vt = feasible(v2(tq.z, tq.w), u_ped);
                     }
+                    if (seed_sig_ev != nullptr) {
+                        // var[m,t+1] = sum_i (q_i - mean q)^2 / (P-1), q_i = w_i (v'_i + noise): d var / d v'_i =
+                        // 2 w_i (q_i - mean) / (P-1)   (particle.py:175; the mean term cancels)
+                        V2 vel = feasible(ut, u_ped);
+                        if (prm.pb.noise != nullptr) {
+                            const float* nz = prm.pb.noise + ((((size_t)s * (T - 1) + t) * N + m) * P + i) * 2;
+                            vel.x = fmaf(__ldg(nz), prm.pb.particle_noise, vel.x);
+                            vel.y = fmaf(__ldg(nz + 1), prm.pb.particle_noise, vel.y);
+                        }
+                        const float4 mean = mus[(t + 1) * N + m];
+                        const float c2 = 2.0f * pw / (float)(P - 1);
+                        const float sbx = __ldg(seed_sig_ev + (m * T + t + 1) * 2), sby = __ldg(seed_sig_ev + (m * T + t + 1) * 2 + 1);
+                        vbar.x = fmaf(c2 * (vel.x * pw - mean.z), sbx, vbar.x);
+                        vbar.y = fmaf(c2 * (vel.y * pw - mean.w), sby, vbar.y);
+                    }
+                    // v' = u', p' = p + dt u'
+                    const V2 upbar = v2(fmaf(dt, pbar.x, vbar.x), fmaf(dt, pbar.y, vbar.y));
                     const V2 ubar = feasible_adjoint(ut, u_ped, upbar);
                     V2 pb = pbar;                                 // p carries through p' = p + dt u'
                     V2 vb = v2(0.f, 0.f);
@@ -631,9 +655,20 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 }
             }
             group_sync(GP, e);
-            if (has_ego && eval_valid) {
+            if (has_ego && eval_valid && prm.out.grad != nullptr) {
                 float* go = prm.out.grad + ev * (size_t)(2 * T);
                 for (int idx = g; idx < 2 * T; idx += GP) go[idx] = ctl[idx];
+            }
+            if (has_ego && eval_valid && prm.out.grad_traj != nullptr) {   // gradient w.r.t. the ego trajectory rows
+                float4* gt = reinterpret_cast<float4*>(prm.out.grad_traj + ev * (size_t)(T + 1) * 4);
+                const float cg = prm.md.w_goal / (float)(T + 1);
+                float gx = 0.f, gy = 0.f;
+                if (prm.md.w_goal != 0.f) { gx = __ldg(prm.md.ego_goal + (size_t)s * 2); gy = __ldg(prm.md.ego_goal + (size_t)s * 2 + 1); }
+                for (int t = g; t <= T; t += GP) {
+                    const float4 eb = egobar[t];
+                    const float4 x = ego[t];
+                    gt[t] = make_float4(sanitize(eb.x) + cg * (x.x - gx), sanitize(eb.y) + cg * (x.y - gy), sanitize(eb.z), sanitize(eb.w));
+                }
             }
         }
         group_sync(GP, e);
@@ -783,8 +818,9 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const int evals_per_unit = (prm.GP <= 32) ? 32 / prm.GP : 1;          // unit = warp of sub-warp groups, or one group
     prm.num_items = (int)((prm.num_evals + evals_per_unit - 1) / evals_per_unit);
     prm.use_tape = need_tape ? 1 : 0;
-    prm.want_env_adjoint = (need_tape && md != nullptr && md->mus_wo != nullptr &&
-                            (md->w_acc != 0.f || md->w_vel != 0.f || md->w_pos != 0.f)) ? 1 : 0;
+    prm.want_env_adjoint = (need_tape && md != nullptr &&
+                            ((md->mus_wo != nullptr && (md->w_acc != 0.f || md->w_vel != 0.f || md->w_pos != 0.f)) ||
+                             md->seed_mus != nullptr || md->seed_sigmas != nullptr)) ? 1 : 0;
     const int block = E * prm.GP;
     int blocks_per_sm = (int)((size_t)lim.smem_per_sm / (smem + 1024));
     if (blocks_per_sm < 1) blocks_per_sm = 1;
@@ -884,7 +920,7 @@ int mtb_query_launch(const mtb_problem* problem, int want_grad, mtb_launch_info*
 int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const mtb_outputs* out, void* workspace,
                  size_t workspace_bytes, void* stream) {
     if (out == nullptr) return MTB_ERR_BAD_ARGUMENT;
-    const bool want_grad = out->grad != nullptr;
+    const bool want_grad = out->grad != nullptr || out->grad_traj != nullptr;
     mtb::KParams prm;
     mtb_launch_info info;
     size_t ws = 0;

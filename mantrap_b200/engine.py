@@ -5,6 +5,7 @@ the C-ABI structs of `include/mantrap_b200.h` from it and launches `mtb_evaluate
 pointer plumbing only. `Engine` is what the product uses: it binds the CUDA library and refuses anything that is
 not a CUDA tensor (there is no CPU path).
 """
+import contextlib
 import ctypes
 import dataclasses
 import math
@@ -81,17 +82,22 @@ class ModuleSpec:
     u_max: float = constants.ROBOT_ACC_MAX
     v_max: float = constants.ROBOT_SPEED_MAX
     d_min: float = constants.CONSTRAINT_MIN_L2_DISTANCE
+    seed_mus: typing.Optional[torch.Tensor] = None        # [S,C,N,T,4] external adjoint seeds (autograd backward)
+    seed_sigmas: typing.Optional[torch.Tensor] = None     # [S,C,N,T,2]
 
 
-def _problem_struct(scene: SceneBatch, controls: typing.Optional[torch.Tensor], t_horizon: int) -> _cabi.MtbProblem:
+def _problem_struct(scene: SceneBatch, controls: typing.Optional[torch.Tensor], t_horizon: int,
+                    ego_traj: typing.Optional[torch.Tensor] = None) -> _cabi.MtbProblem:
     pb = _cabi.MtbProblem()
     pb.num_scenes = scene.num_scenes
-    pb.num_candidates = 1 if controls is None else controls.shape[1]
+    with_ego = controls is not None or ego_traj is not None
+    pb.num_candidates = controls.shape[1] if controls is not None else (ego_traj.shape[1] if ego_traj is not None else 1)
     pb.t_horizon = t_horizon
     pb.num_ados = scene.num_ados
     pb.num_particles = scene.num_particles
     pb.env_kind = ENV_KINDS[scene.env_kind]
-    pb.ego_kind = EGO_KINDS[scene.ego_kind if controls is not None else None]
+    pb.ego_kind = EGO_KINDS[scene.ego_kind if with_ego else None]
+    pb.ego_traj = _cabi.ptr(ego_traj)
     pb.dt = scene.dt
     pb.sf_tau = constants.SOCIAL_FORCES_DEFAULT_TAU
     pb.ped_speed_max = constants.PED_SPEED_MAX
@@ -130,12 +136,15 @@ def _module_struct(scene: SceneBatch, spec: ModuleSpec) -> _cabi.MtbModules:
     md.con_min_distance = int(spec.min_distance)
     md.u_max, md.v_max, md.min_distance = spec.u_max, spec.v_max, spec.d_min
     md.violation_eps = constants.CONSTRAINT_VIOLATION_PRECISION
+    md.seed_mus = _cabi.ptr(spec.seed_mus)
+    md.seed_sigmas = _cabi.ptr(spec.seed_sigmas)
     return md
 
 
 OUTPUT_SHAPES = {
     "obj": lambda s, c, t, n, r: (s, c, 4), "obj_raw": lambda s, c, t, n, r: (s, c, 4),
     "total": lambda s, c, t, n, r: (s, c), "grad": lambda s, c, t, n, r: (s, c, t, 2),
+    "grad_traj": lambda s, c, t, n, r: (s, c, t + 1, 4),
     "cons": lambda s, c, t, n, r: (s, c, r), "violation": lambda s, c, t, n, r: (s, c),
     "ego_traj": lambda s, c, t, n, r: (s, c, t + 1, 4), "mus": lambda s, c, t, n, r: (s, c, n, t, 4),
     "sigmas": lambda s, c, t, n, r: (s, c, n, t, 2),
@@ -145,13 +154,16 @@ OUTPUT_SHAPES = {
 def launch_evaluate(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Optional[torch.Tensor],
                     spec: typing.Optional[ModuleSpec], want: typing.Sequence[str], t_horizon: int = None,
                     stream: int = 0, out: typing.Dict[str, torch.Tensor] = None, stats: torch.Tensor = None,
-                    workspace: torch.Tensor = None) -> typing.Dict[str, torch.Tensor]:
-    """One `mtb_evaluate` launch. controls [S,C,T,2] (None = rollout without ego, needs `t_horizon`).
-    `want` names the output arrays to produce (keys of OUTPUT_SHAPES); `out` may supply pre-allocated tensors."""
+                    workspace: torch.Tensor = None, ego_traj: torch.Tensor = None) -> typing.Dict[str, torch.Tensor]:
+    """One `mtb_evaluate` launch. controls [S,C,T,2] (None = rollout without ego, needs `t_horizon`), or a given ego
+    trajectory `ego_traj` [S,C,T+1,4] (module interface). `want` names the output arrays to produce (keys of
+    OUTPUT_SHAPES); `out` may supply pre-allocated tensors."""
     spec = spec if spec is not None else ModuleSpec()
     if controls is not None:
         t_horizon = controls.shape[2]
-    pb = _problem_struct(scene, controls, t_horizon)
+    elif ego_traj is not None:
+        t_horizon = ego_traj.shape[2] - 1
+    pb = _problem_struct(scene, controls, t_horizon, ego_traj)
     md = _module_struct(scene, spec)
     rows = lib.mtb_num_constraint_rows(ctypes.byref(pb), ctypes.byref(md))
     if rows < 0:
@@ -165,7 +177,7 @@ def launch_evaluate(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Option
         setattr(outs, key, _cabi.ptr(res[key]))
     if stats is not None:
         outs.stats = _cabi.ptr(stats, dtype=torch.int64)
-    need = lib.mtb_workspace_bytes(ctypes.byref(pb), int("grad" in want))
+    need = lib.mtb_workspace_bytes(ctypes.byref(pb), int("grad" in want or "grad_traj" in want))
     ws_ptr, ws_bytes = None, 0
     if need > 0:
         if workspace is None or workspace.numel() * workspace.element_size() < need:
@@ -177,13 +189,13 @@ def launch_evaluate(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Option
     return res
 
 
-def launch_jacobian(lib: ctypes.CDLL, scene: SceneBatch, controls: torch.Tensor, spec: ModuleSpec, stream: int = 0,
-                    want_values: bool = False):
+def launch_jacobian(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Optional[torch.Tensor], spec: ModuleSpec,
+                    stream: int = 0, want_values: bool = False, ego_traj: torch.Tensor = None):
     """One `mtb_constraint_jacobian` launch: dense UN-normalised Jacobian [S,C,R,2T] of every constraint row enabled
     in `spec` (control | speed | min-distance, the row order of `cons`) w.r.t. the flattened controls; optionally the
     un-normalised min-distance values [S,C,N,T]."""
-    t_horizon = controls.shape[2]
-    pb = _problem_struct(scene, controls, t_horizon)
+    t_horizon = controls.shape[2] if controls is not None else ego_traj.shape[2] - 1
+    pb = _problem_struct(scene, controls, t_horizon, ego_traj)
     md = _module_struct(scene, spec)
     rows = lib.mtb_num_constraint_rows(ctypes.byref(pb), ctypes.byref(md))
     if rows <= 0:
@@ -230,20 +242,78 @@ class Engine:
         self.launches = 0
         self._workspace = None
 
+    @classmethod
+    def from_library(cls, lib: ctypes.CDLL, device: typing.Union[str, torch.device]) -> "Engine":
+        """TEST HOOK: an engine over an explicitly given, already bound C-ABI library. The CPU test-suite uses it with
+        the host emulation of the kernel source (tests/host_emul) to exercise the host classes without a GPU; nothing
+        in the package calls it."""
+        self = cls.__new__(cls)
+        self.lib, self.device, self.launches, self._workspace = lib, torch.device(device), 0, None
+        return self
+
     def _check(self, *tensors):
         for t in tensors:
-            if t is not None and not t.is_cuda:
-                raise RuntimeError("mantrap_b200.Engine only accepts CUDA tensors")
+            if t is not None and t.device != self.device and not (t.is_cuda and self.device.type == "cuda" and
+                                                                  self.device.index in (None, t.device.index)):
+                raise RuntimeError(f"mantrap_b200.Engine only accepts tensors on {self.device} (got {t.device})")
 
     def _stream(self) -> int:
-        return torch.cuda.current_stream(self.device).cuda_stream
+        return torch.cuda.current_stream(self.device).cuda_stream if self.device.type == "cuda" else 0
 
-    def evaluate(self, scene: SceneBatch, controls: torch.Tensor, spec: ModuleSpec = None,
-                 want: typing.Sequence[str] = ("obj", "total", "grad"), out=None, stats=None):
-        self._check(scene.ado0, controls)
-        with torch.cuda.device(self.device):
+    def _guard(self):
+        return torch.cuda.device(self.device) if self.device.type == "cuda" else contextlib.nullcontext()
+
+    # ---- ego dynamics (agents interface) ---------------------------------------------------------------------
+    def ego_unroll(self, ego_kind: str, dt: float, x0: torch.Tensor, controls: torch.Tensor) -> torch.Tensor:
+        """x0 [B,5] (px,py,vx,vy,time), controls [B,T,2] -> trajectory [B,T+1,5] (linear.py:68-105)."""
+        self._check(x0, controls)
+        b, t_horizon = controls.shape[0], controls.shape[1]
+        out = torch.empty((b, t_horizon + 1, 5), dtype=torch.float32, device=self.device)
+        with self._guard():
+            code = self.lib.mtb_ego_unroll(EGO_KINDS[ego_kind], dt, _cabi.ptr(x0), _cabi.ptr(controls), b, t_horizon,
+                                           _cabi.ptr(out), self._stream())
+        _cabi.check(self.lib, code, "mtb_ego_unroll")
+        self.launches += 1
+        return out
+
+    def ego_roll(self, ego_kind: str, dt: float, trajectory: torch.Tensor) -> torch.Tensor:
+        """trajectory [B,T+1,5] -> controls [B,T,2] (linear.py:107-130)."""
+        self._check(trajectory)
+        b, t_horizon = trajectory.shape[0], trajectory.shape[1] - 1
+        out = torch.empty((b, t_horizon, 2), dtype=torch.float32, device=self.device)
+        with self._guard():
+            code = self.lib.mtb_ego_roll(EGO_KINDS[ego_kind], dt, _cabi.ptr(trajectory), b, t_horizon, _cabi.ptr(out), self._stream())
+        _cabi.check(self.lib, code, "mtb_ego_roll")
+        self.launches += 1
+        return out
+
+    def ego_unroll_adjoint(self, ego_kind: str, dt: float, grad_trajectory: torch.Tensor) -> torch.Tensor:
+        """grad_trajectory [B,T+1,5] -> grad_controls [B,T,2] (reverse mode of unroll_trajectory)."""
+        self._check(grad_trajectory)
+        b, t_horizon = grad_trajectory.shape[0], grad_trajectory.shape[1] - 1
+        out = torch.empty((b, t_horizon, 2), dtype=torch.float32, device=self.device)
+        with self._guard():
+            code = self.lib.mtb_ego_unroll_adjoint(EGO_KINDS[ego_kind], dt, _cabi.ptr(grad_trajectory), b, t_horizon,
+                                                   _cabi.ptr(out), self._stream())
+        _cabi.check(self.lib, code, "mtb_ego_unroll_adjoint")
+        self.launches += 1
+        return out
+
+    def ego_dx_du(self, ego_kind: str, dt: float, t_horizon: int) -> torch.Tensor:
+        """[5(T+1), 2T] Jacobian of the trajectory w.r.t. the controls (linear.py:169-196)."""
+        out = torch.empty((5 * (t_horizon + 1), 2 * t_horizon), dtype=torch.float32, device=self.device)
+        with self._guard():
+            code = self.lib.mtb_ego_dx_du(EGO_KINDS[ego_kind], dt, t_horizon, _cabi.ptr(out), self._stream())
+        _cabi.check(self.lib, code, "mtb_ego_dx_du")
+        self.launches += 1
+        return out
+
+    def evaluate(self, scene: SceneBatch, controls: typing.Optional[torch.Tensor], spec: ModuleSpec = None,
+                 want: typing.Sequence[str] = ("obj", "total", "grad"), out=None, stats=None, ego_traj=None):
+        self._check(scene.ado0, controls, ego_traj)
+        with self._guard():
             res = launch_evaluate(self.lib, scene, controls, spec, want, stream=self._stream(), out=out, stats=stats,
-                                  workspace=self._workspace)
+                                  workspace=self._workspace, ego_traj=ego_traj)
         self._workspace = res.pop("_workspace", self._workspace)
         self.launches += 1
         return res
@@ -251,22 +321,24 @@ class Engine:
     def rollout_wo_ego(self, scene: SceneBatch, t_horizon: int, want=("mus", "sigmas")):
         """Ego-free prediction (`compute_distributions_wo_ego`): mus [S,N,T,4], sigmas [S,N,T,2]."""
         self._check(scene.ado0)
-        with torch.cuda.device(self.device):
+        with self._guard():
             res = launch_evaluate(self.lib, scene.without_ego(), None, None, want, t_horizon=t_horizon, stream=self._stream())
         self.launches += 1
         return {k: v[:, 0] for k, v in res.items() if not k.startswith("_")}
 
-    def constraint_jacobian(self, scene: SceneBatch, controls: torch.Tensor, spec: ModuleSpec, want_values: bool = False):
+    def constraint_jacobian(self, scene: SceneBatch, controls: typing.Optional[torch.Tensor], spec: ModuleSpec,
+                            want_values: bool = False, ego_traj=None):
         """Dense constraint Jacobian [S,C,R,2T] (forward-mode tangent kernel)."""
-        self._check(scene.ado0, controls)
-        with torch.cuda.device(self.device):
-            out = launch_jacobian(self.lib, scene, controls, spec, stream=self._stream(), want_values=want_values)
+        self._check(scene.ado0, controls, ego_traj)
+        with self._guard():
+            out = launch_jacobian(self.lib, scene, controls, spec, stream=self._stream(), want_values=want_values,
+                                  ego_traj=ego_traj)
         self.launches += 1
         return out
 
     def argmin(self, total, violation, controls, feas_tol: float = constants.SOLVER_CONSTRAINT_LIMIT):
         self._check(total, violation, controls)
-        with torch.cuda.device(self.device):
+        with self._guard():
             out = launch_argmin(self.lib, total, violation, controls, feas_tol, stream=self._stream())
         self.launches += 1
         return out

@@ -1,0 +1,501 @@
+"""Solvers of the hot path with the reference's interface (`mantrap/solver`).
+
+The optimisation variable is z = the ego's controls, flattened (t, xy) (solver/base/trajopt.py:356-357, :439-444).
+`TrajOptSolver` keeps the reference's frame -- module construction, `objective / constraints / gradient / jacobian (z)`,
+warm start, the closed-loop `solve()` -- and answers the four callbacks from the CUDA kernels:
+
+* `fused=True` (default): ONE `mtb_evaluate` launch per distinct z produces every module's objective, the summed
+  gradient, all constraint rows and the violation (one particle draw shared by all modules); the four callbacks
+  of an IPOPT iteration share it through a per-z cache (callbacks may be invoked in any order with the same z,
+  SURVEY §8b). The dense Jacobian is one `mtb_constraint_jacobian` launch.
+* `fused=False`: module by module, in the reference's call order, each drawing its own particles -- with
+  `torch.manual_seed` pinned this reproduces the reference's numbers call for call (parity tests).
+
+Mirrors: TrajOptSolver solver/base/trajopt.py:18-666; IPOPTSolver solver/ipopt.py:12-229 (cyipopt is third-party and not
+shipped: `optimize_core` binds `ipopt` / `cyipopt` when importable and raises otherwise); SearchIntermediate
+solver/base/search.py:11-108; RandomSearch solver/baselines/random_search.py:9-39 (here: thousands of candidates per
+launch + device argmin instead of one candidate per Python iteration). `SLSQPSolver` drives the same four callbacks
+with scipy and is NOT IPOPT; it exists for end-to-end checks of the callbacks.
+"""
+import time
+import typing
+
+import numpy as np
+import torch
+
+from . import constants, modules as mods, runtime
+from .engine import ModuleSpec
+
+
+class TrajOptSolver:
+    def __init__(self, env, goal: torch.Tensor, t_planning: int = constants.SOLVER_HORIZON_DEFAULT,
+                 modules: typing.Union[typing.List[typing.Tuple], typing.List] = None, attention_module=None,
+                 eval_env=None, config_name: str = "unknown", is_logging: bool = False, is_debug: bool = False,
+                 fused: bool = True, num_particles: int = constants.ENV_NUM_PARTICLES, **solver_params):
+        goal = torch.as_tensor(goal).detach().float().cpu()
+        assert goal.shape == (2,)
+        self._solver_params = dict(solver_params, t_planning=t_planning, config_name=config_name, goal=goal)
+        self._env = env.copy()
+        self._eval_env = env.copy(env_type=eval_env) if eval_env is not None else env.copy()
+        assert self._env.ego is not None and self._env.same_initial_conditions(self._eval_env)
+        self._fused, self._num_particles = fused, num_particles
+        module_list = self.module_defaults() if modules is None else modules
+        self._module_dict = {}
+        for entry in module_list:
+            cls, kwargs = (entry[0], (entry[1] if len(entry) > 1 and entry[1] is not None else {})) \
+                if isinstance(entry, tuple) else (entry, {})
+            module = cls(t_horizon=self.planning_horizon, goal=self.goal, env=self.env, num_particles=num_particles, **kwargs)
+            self._module_dict[module.name] = module
+        self._attention_module = attention_module(env=self.env, t_horizon=self.planning_horizon) \
+            if attention_module is not None else None
+        self._log, self._cache = {}, {}
+        self._is_logging = is_logging
+        assert self.num_optimization_variables() > 0
+
+    # ---- closed loop -------------------------------------------------------------------------------------------
+    def solve(self, time_steps: int, warm_start_method: str = constants.WARM_START_HARD, **kwargs
+              ) -> typing.Tuple[torch.Tensor, torch.Tensor]:
+        """MPC loop: optimise, execute the first control in the evaluation environment, shift the warm start, repeat
+        until `time_steps` or the goal is reached (trajopt.py:109-193). The solver's environments are restored at the end."""
+        ego_trajectory_opt = torch.zeros((time_steps + 1, 5))
+        ado_trajectories = torch.zeros((self.env.num_ados, time_steps + 1, 1, 5))
+        env_copy, eval_env_copy = self.env.copy(), self.eval_env.copy()
+        ego_trajectory_opt[0] = self._env.ego.state_with_time
+        for m, ado in enumerate(self.env.ados):
+            ado_trajectories[m, 0, 0] = ado.state_with_time
+        z_warm_start = self.warm_start(method=warm_start_method)
+        for k in range(time_steps):
+            z_k = self.optimize(z_warm_start, tag=constants.TAG_OPTIMIZATION, **kwargs)
+            ego_controls_k = z_k.detach().float().view(-1, 2)
+            z_warm_start = torch.cat((ego_controls_k[1:], torch.zeros((1, 2)))).flatten()
+            ado_states, ego_state = self._eval_env.step(ego_action=ego_controls_k[0])
+            self._env.step_reset(ego_next=ego_state, ado_next=ado_states)
+            self._refresh_modules()
+            ego_trajectory_opt[k + 1] = ego_state
+            ado_trajectories[:, k + 1, 0] = ado_states
+            if torch.norm(ego_state[0:2] - self.goal) < constants.SOLVER_GOAL_END_DISTANCE:
+                ego_trajectory_opt = ego_trajectory_opt[:k + 2].detach()
+                ado_trajectories = ado_trajectories[:, :k + 2].detach()
+                break
+        self._env, self._eval_env = env_copy, eval_env_copy
+        self._refresh_modules()
+        return ego_trajectory_opt, ado_trajectories
+
+    def _refresh_modules(self):
+        self._cache.clear()
+        for module in self.modules:
+            module.reset_env(env=self.env)
+
+    def optimize(self, z0: torch.Tensor, tag: str, **kwargs) -> torch.Tensor:
+        ado_ids = self._attention_module.compute() if self._attention_module is not None else self.env.ado_ids
+        z_opt, self._log = self.optimize_core(z0, ado_ids=ado_ids, tag=tag, **kwargs)
+        return z_opt
+
+    def optimize_core(self, z0: torch.Tensor, tag: str, ado_ids: typing.List[str], **kwargs):
+        raise NotImplementedError
+
+    # ---- warm start --------------------------------------------------------------------------------------------
+    def warm_start(self, method: str = constants.WARM_START_HARD) -> torch.Tensor:
+        """"hard": the same problem with the hard modules only, started from full throttle towards the goal
+        (trajopt.py:248-306); "zeros": zero controls. (Encoding / soft / potential need data or modules out of scope.)"""
+        if method == constants.WARM_START_HARD:
+            part = self.__class__(env=self.env, goal=self.goal, modules=self.module_hard(), t_planning=self.planning_horizon,
+                                  config_name=self.config_name, fused=self._fused, num_particles=self._num_particles)
+            _, u_max = self.env.ego.control_limits()
+            dx_goal = self.goal - self.env.ego.position
+            init = torch.stack([dx_goal / torch.norm(dx_goal).clamp(min=1e-6) * u_max] * self.planning_horizon)
+            return part.optimize(z0=init.flatten(), tag=constants.TAG_WARM_START)
+        if method == constants.WARM_START_ZEROS:
+            return torch.zeros(2 * self.planning_horizon)
+        raise ValueError(f"Invalid warm starting-method {method} !")
+
+    @staticmethod
+    def module_defaults():
+        """The reference's defaults are goal, interaction-probability, speed limits and HJ reachability
+        (trajopt.py:336-343); the probability module is a "next" row and the HJ value grid is not shipped, so
+        the default interaction objective here is the acceleration module of BASELINE config 1."""
+        return [mods.GoalNormModule, mods.InteractionAccelerationModule, mods.SpeedLimitModule]
+
+    @staticmethod
+    def module_hard():
+        return [mods.GoalNormModule, mods.ControlLimitModule, mods.SpeedLimitModule]
+
+    # ---- problem formulation -------------------------------------------------------------------------------------
+    def num_optimization_variables(self) -> int:
+        return 2 * self.planning_horizon
+
+    def optimization_variable_bounds(self) -> typing.Tuple[typing.List, typing.List]:
+        lower, upper = self._env.ego.control_limits()
+        n = self.num_optimization_variables()
+        return (np.ones(n) * lower).tolist(), (np.ones(n) * upper).tolist()
+
+    def constraint_bounds(self, ado_ids) -> typing.Tuple[typing.List, typing.List]:
+        cl, cu = [], []
+        for module in self.modules:
+            lower, upper = module.constraint_boundaries(ado_ids=ado_ids)
+            cl += list(lower)
+            cu += list(upper)
+        return cl, cu
+
+    def _fusable(self) -> bool:
+        return self._fused and all(getattr(m, "fused_key", None) is not None or getattr(m, "spec_flag", None) is not None
+                                   for m in self.modules)
+
+    def _fused_spec(self, ado_ids) -> ModuleSpec:
+        spec = ModuleSpec(weights={}, ado_mask=None)
+        for m in self.modules:
+            one = m._spec(ado_ids)
+            spec.weights.update(one.weights)
+            spec.mus_wo = one.mus_wo if one.mus_wo is not None else spec.mus_wo
+            spec.ado_mask = one.ado_mask if one.ado_mask is not None else spec.ado_mask
+            spec.control_limits |= one.control_limits
+            spec.speed_limits |= one.speed_limits
+            spec.min_distance |= one.min_distance
+            if one.control_limits:
+                spec.u_max = one.u_max
+            if one.speed_limits:
+                spec.v_max = one.v_max
+        if len(ado_ids) == 0:                       # interaction objectives are undefined without ados (-> 0)
+            for key in ("acc", "vel", "pos"):
+                spec.weights.pop(key, None)
+        return spec
+
+    def evaluate_fused(self, z: np.ndarray, ado_ids: typing.List[str], want_jacobian: bool = False) -> typing.Dict:
+        """One launch for everything the callbacks need at this z (cached). Keys: obj {module: value}, total, grad [2T],
+        cons {module: rows}, violation, optionally jac {module: [rows, 2T]}."""
+        key = (np.asarray(z, dtype=np.float64).tobytes(), tuple(ado_ids))
+        hit = self._cache.get(key)
+        if hit is not None and (not want_jacobian or "jac" in hit):
+            return hit
+        engine = runtime.default_engine()
+        controls = torch.from_numpy(np.asarray(z, dtype=np.float32)).view(1, 1, -1, 2).to(engine.device).contiguous()
+        rollout = any(m.needs_rollout for m in self.modules)
+        env = self.env
+        if rollout:
+            num_p = self._num_particles if env.env_kind != "kalman" else 1
+            scene = env.scene_batch(num_p, self.planning_horizon, with_noise=env.env_kind != "kalman")
+        else:
+            scene = self.modules[0]._scene().to("cpu")
+        scene.ego_goal = self.goal.view(1, 2).clone()
+        scene = scene.to(engine.device)
+        spec = self._fused_spec(ado_ids)
+        out = hit if hit is not None else {}
+        if hit is None:
+            res = engine.evaluate(scene, controls, spec, want=("obj", "total", "grad", "cons", "violation"))
+            obj = res["obj"][0, 0].cpu().numpy()
+            cons = res["cons"][0, 0].cpu().numpy()
+            out.update(obj={m.name: float(obj[("goal", "acc", "vel", "pos").index(m.fused_key)]) for m in self.modules
+                            if getattr(m, "fused_key", None) is not None},
+                       total=float(res["total"][0, 0]), grad=res["grad"][0, 0].cpu().numpy().flatten().astype(np.float64),
+                       violation=float(res["violation"][0, 0]), cons=self._split_rows(cons, ado_ids, spec))
+        if want_jacobian:
+            jac = engine.constraint_jacobian(scene, controls, spec)[0, 0].cpu().numpy().astype(np.float64)
+            out["jac"] = self._split_rows(jac, ado_ids, spec)
+        if len(self._cache) > 64:
+            self._cache.clear()
+        self._cache[key] = out
+        return out
+
+    def _split_rows(self, rows: np.ndarray, ado_ids, spec: ModuleSpec) -> typing.Dict[str, np.ndarray]:
+        """Kernel row order (control | speed | min-distance) -> per module, min-distance restricted to `ado_ids`."""
+        t_hor, n = self.planning_horizon, self.env.num_ados
+        out, base = {}, 0
+        for flag, count, name in (("control_limits", 2 * t_hor if self.env.ego.ego_kind == "double" else t_hor, "control_limits"),
+                                  ("speed_limits", 2 * (t_hor + 1), "speed_limits"), ("min_distance", n * t_hor, "min_distance")):
+            if not getattr(spec, flag):
+                continue
+            block = rows[base:base + count]
+            if name == "min_distance" and list(ado_ids) != list(self.env.ado_ids):
+                idx = [self.env.index_ado_id(i) for i in ado_ids]
+                block = block.reshape(n, t_hor, *block.shape[1:])[idx].reshape(len(idx) * t_hor, *block.shape[1:])
+            out[name] = block
+            base += count
+        return out
+
+    # ---- the four callbacks --------------------------------------------------------------------------------------
+    def objective(self, z: np.ndarray, ado_ids: typing.List[str] = None, tag: str = constants.TAG_OPTIMIZATION) -> float:
+        ado_ids = ado_ids if ado_ids is not None else self.env.ado_ids
+        if self._fusable():
+            return self.evaluate_fused(z, ado_ids)["total"]
+        ego_trajectory = self.z_to_ego_trajectory(z)
+        return float(np.sum([m.objective(ego_trajectory, ado_ids=ado_ids, tag=tag) for m in self.modules]))
+
+    def constraints(self, z: np.ndarray, ado_ids: typing.List[str] = None, tag: str = constants.TAG_OPTIMIZATION,
+                    return_violation: bool = False):
+        ado_ids = ado_ids if ado_ids is not None else self.env.ado_ids
+        if self._fusable():
+            res = self.evaluate_fused(z, ado_ids)
+            rows = [res["cons"][m.name] for m in self.modules if m.name in res["cons"]]
+            constraints = np.concatenate(rows) if rows else np.array([])
+            violation = res["violation"]
+            if "min_distance" in res["cons"] and list(ado_ids) != list(self.env.ado_ids):   # violation over ado_ids only
+                violation = float(sum(self.module_dict[k]._violation(v, ado_ids) for k, v in res["cons"].items()))
+        else:
+            ego_trajectory = self.z_to_ego_trajectory(z)
+            constraints = np.concatenate([m.constraint(ego_trajectory, tag=tag, ado_ids=ado_ids) for m in self.modules])
+            violation = float(np.sum([m.compute_violation_internal(tag=tag) for m in self.modules]))
+        return constraints if not return_violation else (constraints, violation)
+
+    def gradient(self, z: np.ndarray, ado_ids: typing.List[str] = None, tag: str = constants.TAG_OPTIMIZATION) -> np.ndarray:
+        ado_ids = ado_ids if ado_ids is not None else self.env.ado_ids
+        if self._fusable():
+            return self.evaluate_fused(z, ado_ids)["grad"]
+        ego_trajectory, grad_wrt = self.z_to_ego_trajectory(z, return_leaf=True)
+        gradient = [m.gradient(ego_trajectory, grad_wrt=grad_wrt, tag=tag, ado_ids=ado_ids) for m in self.modules]
+        return np.sum(gradient, axis=0)
+
+    def jacobian(self, z: np.ndarray, ado_ids: typing.List[str] = None, tag: str = constants.TAG_OPTIMIZATION) -> np.ndarray:
+        """Concatenated, flattened, un-normalised module Jacobians (solver/ipopt.py:140-154)."""
+        ado_ids = ado_ids if ado_ids is not None else self.env.ado_ids
+        if self._fusable():
+            res = self.evaluate_fused(z, ado_ids, want_jacobian=True)
+            blocks = []
+            for m in self.modules:
+                if m.name == "control_limits" and self.env.ego.ego_kind == "double":     # reference quirk: identity
+                    blocks.append(np.eye(2 * self.planning_horizon).flatten())
+                elif m.name in res["jac"]:
+                    blocks.append(res["jac"][m.name].flatten())
+            return np.concatenate(blocks) if blocks else np.array([])
+        ego_trajectory, grad_wrt = self.z_to_ego_trajectory(z, return_leaf=True)
+        jacobian = [m.jacobian(ego_trajectory, grad_wrt=grad_wrt, tag=tag, ado_ids=ado_ids) for m in self.modules]
+        jacobian = [x.flatten() for x in jacobian if x.size > 0]
+        return np.concatenate(jacobian) if jacobian else np.array([])
+
+    def evaluate(self, z: np.ndarray, ado_ids: typing.List[str], tag: str) -> typing.Tuple[float, float]:
+        """objective + summed constraint violation (solver/base/search.py:98-103)."""
+        objective = self.objective(z, tag=tag, ado_ids=ado_ids)
+        _, violation = self.constraints(z, ado_ids=ado_ids, return_violation=True, tag=tag)
+        return objective, violation
+
+    # ---- z <-> controls <-> trajectory -----------------------------------------------------------------------------
+    def z_to_ego_trajectory(self, z: np.ndarray, return_leaf: bool = False):
+        ego_controls = torch.from_numpy(np.asarray(z)).view(-1, 2).float()
+        ego_controls.requires_grad = True
+        ego_trajectory = self.env.ego.unroll_trajectory(controls=ego_controls, dt=self.env.dt)
+        return ego_trajectory if not return_leaf else (ego_trajectory, ego_controls)
+
+    @staticmethod
+    def z_to_ego_controls(z: np.ndarray, return_leaf: bool = False):
+        ego_controls = torch.from_numpy(np.asarray(z)).view(-1, 2).float()
+        ego_controls.requires_grad = True
+        return ego_controls if not return_leaf else (ego_controls, ego_controls)
+
+    def ego_trajectory_to_z(self, ego_trajectory: torch.Tensor) -> np.ndarray:
+        return self.env.ego.roll_trajectory(ego_trajectory, dt=self.env.dt).flatten().detach().numpy()
+
+    @staticmethod
+    def ego_controls_to_z(ego_controls: torch.Tensor) -> np.ndarray:
+        return ego_controls.flatten().detach().numpy()
+
+    # ---- properties ------------------------------------------------------------------------------------------------
+    @property
+    def env(self):
+        return self._env
+
+    @property
+    def eval_env(self):
+        return self._eval_env
+
+    @property
+    def goal(self) -> torch.Tensor:
+        return self._solver_params["goal"]
+
+    @property
+    def planning_horizon(self) -> int:
+        return self._solver_params["t_planning"]
+
+    @property
+    def module_dict(self):
+        return self._module_dict
+
+    @property
+    def modules(self):
+        return list(self._module_dict.values())
+
+    @property
+    def module_names(self) -> typing.List[str]:
+        return list(self._module_dict.keys())
+
+    @property
+    def config_name(self) -> str:
+        return self._solver_params["config_name"]
+
+    @property
+    def log(self):
+        return self._log
+
+    @property
+    def name(self) -> str:
+        raise NotImplementedError
+
+
+class IPOPTProblem:
+    """The object cyipopt calls back into (solver/ipopt.py:201-229)."""
+
+    def __init__(self, problem: "IPOPTSolver", ado_ids: typing.List[str], tag: str = constants.TAG_OPTIMIZATION):
+        self.problem, self.tag, self.ado_ids = problem, tag, ado_ids
+
+    def objective(self, z: np.ndarray) -> float:
+        return self.problem.objective(z, tag=self.tag, ado_ids=self.ado_ids)
+
+    def gradient(self, z: np.ndarray) -> np.ndarray:
+        return self.problem.gradient(z, tag=self.tag, ado_ids=self.ado_ids)
+
+    def constraints(self, z: np.ndarray) -> np.ndarray:
+        return self.problem.constraints(z, tag=self.tag, ado_ids=self.ado_ids)
+
+    def jacobian(self, z: np.ndarray) -> np.ndarray:
+        return self.problem.jacobian(z, tag=self.tag, ado_ids=self.ado_ids)
+
+    def intermediate(self, *args):
+        pass
+
+
+class IPOPTSolver(TrajOptSolver):
+    def optimize_core(self, z0: torch.Tensor, ado_ids: typing.List[str], tag: str = constants.TAG_OPTIMIZATION,
+                      max_cpu_time: float = constants.IPOPT_MAX_CPU_TIME_DEFAULT, approx_jacobian: bool = False, **solver_kwargs):
+        """NLP assembly + IPOPT call with the reference's options (solver/ipopt.py:15-99)."""
+        lb, ub = self.optimization_variable_bounds()
+        cl, cu = self.constraint_bounds(ado_ids)
+        z0_flat = z0.detach().flatten().double().numpy().tolist()
+        problem = IPOPTProblem(self, ado_ids=ado_ids, tag=tag)
+        options = {"max_cpu_time": max_cpu_time, "tol": constants.IPOPT_OPTIMALITY_TOLERANCE, "mu_strategy": "adaptive",
+                   "mehrotra_algorithm": "yes", "hessian_approximation": "limited-memory", "print_level": 0}
+        if approx_jacobian:
+            options["jacobian_approximation"] = "finite-difference-values"
+        big = 2.0e19
+        cl = [(-big if x is None else x) for x in cl]
+        cu = [(big if x is None else x) for x in cu]
+        try:
+            import ipopt                                            # cyipopt 0.1.9, the version the reference pins
+            nlp = ipopt.problem(n=len(z0_flat), m=len(cl), problem_obj=problem, lb=lb, ub=ub, cl=cl, cu=cu)
+            add = nlp.addOption
+        except ImportError:
+            try:
+                import cyipopt                                      # cyipopt >= 1.0: same callbacks, renamed entry points
+            except ImportError as err:
+                raise ImportError("IPOPTSolver.optimize_core needs cyipopt (`ipopt` or `cyipopt` module), which is a "
+                                  "third-party dependency of the reference and is not installed. The four callbacks "
+                                  "(objective / gradient / constraints / jacobian) work without it; SLSQPSolver drives "
+                                  "them with scipy instead (not IPOPT).") from err
+            nlp = cyipopt.Problem(n=len(z0_flat), m=len(cl), problem_obj=problem, lb=lb, ub=ub, cl=cl, cu=cu)
+            add = nlp.add_option
+        for key, value in options.items():
+            add(key, value)
+        z_opt, _ = nlp.solve(z0_flat)
+        nlp.close()
+        return torch.from_numpy(np.asarray(z_opt)).view(-1, 2), self._log
+
+    @staticmethod
+    def module_hard():
+        """Variable bounds already are the control limits (solver/ipopt.py:105-113)."""
+        return [mods.GoalNormModule, mods.SpeedLimitModule]
+
+    @property
+    def name(self) -> str:
+        return "ipopt"
+
+
+class SLSQPSolver(TrajOptSolver):
+    """NOT IPOPT: scipy's SLSQP over the same four callbacks and bounds. For end-to-end checks where cyipopt is absent."""
+
+    def optimize_core(self, z0: torch.Tensor, ado_ids: typing.List[str], tag: str = constants.TAG_OPTIMIZATION,
+                      max_iter: int = 30, **solver_kwargs):
+        import scipy.optimize
+        lb, ub = self.optimization_variable_bounds()
+        cl, cu = self.constraint_bounds(ado_ids)
+        n = self.num_optimization_variables()
+        cons = []
+        if len(cl) > 0:
+            lo = np.array([-np.inf if x is None else x for x in cl])
+            hi = np.array([np.inf if x is None else x for x in cu])
+
+            def g(z):
+                c = self.constraints(z, ado_ids=ado_ids, tag=tag)
+                return np.concatenate((c[np.isfinite(lo)] - lo[np.isfinite(lo)], hi[np.isfinite(hi)] - c[np.isfinite(hi)]))
+
+            def g_jac(z):
+                j = self.jacobian(z, ado_ids=ado_ids, tag=tag).reshape(len(cl), n)
+                j = j / self._row_normalisers(ado_ids)[:, None]           # constraints are normalised, Jacobians are not
+                return np.concatenate((j[np.isfinite(lo)], -j[np.isfinite(hi)]))
+
+            cons = [{"type": "ineq", "fun": g, "jac": g_jac}]
+        res = scipy.optimize.minimize(lambda z: self.objective(z, ado_ids=ado_ids, tag=tag), z0.detach().flatten().double().numpy(),
+                                      jac=lambda z: self.gradient(z, ado_ids=ado_ids, tag=tag), bounds=list(zip(lb, ub)),
+                                      constraints=cons, method="SLSQP", options={"maxiter": max_iter, "ftol": 1e-4})
+        return torch.from_numpy(res.x).view(-1, 2), self._log
+
+    def _row_normalisers(self, ado_ids) -> np.ndarray:
+        factors = []
+        for m in self.modules:
+            k = m.num_constraints(ado_ids=ado_ids)
+            if k > 0:
+                factors.append(np.ones(k) * float(1.0 / m.normalize(1.0)))
+        return np.concatenate(factors)
+
+    @property
+    def name(self) -> str:
+        return "slsqp"
+
+
+class SearchIntermediate(TrajOptSolver):
+    """Sampling solvers: the reference evaluates ONE candidate per Python iteration until the time budget is spent
+    (solver/base/search.py:19-81); here every iteration evaluates `num_candidates` candidates in one launch and picks the
+    best feasible one with the device argmin."""
+
+    def optimize_core(self, z0: torch.Tensor, ado_ids: typing.List[str], tag: str = constants.TAG_OPTIMIZATION,
+                      max_cpu_time: float = constants.SEARCH_MAX_CPU_TIME, num_candidates: int = 4096, max_rounds: int = None,
+                      **solver_kwargs):
+        start = time.time()
+        z_fallback = np.random.uniform(*self.z_bounds)
+        z_best, obj_best, rounds = None, np.inf, 0
+        while True:
+            z_cand, obj_cand = self._optimize_inner(z_best, obj_best, num_candidates, tag, ado_ids)
+            if obj_cand <= obj_best and z_cand is not None:
+                z_best, obj_best = z_cand, obj_cand
+            rounds += 1
+            if (max_rounds is not None and rounds >= max_rounds) or time.time() - start > max_cpu_time:
+                break
+        z_best = z_fallback if z_best is None else z_best
+        self._log = {"rounds": rounds, "candidates": rounds * num_candidates, "objective": obj_best}
+        return torch.from_numpy(np.asarray(z_best, dtype=np.float32)).view(-1, 2), self._log
+
+    def _optimize_inner(self, z_best, obj_best, num_candidates, tag, ado_ids):
+        raise NotImplementedError
+
+    def evaluate_batch(self, z: np.ndarray, ado_ids: typing.List[str]):
+        """z [C, 2T] -> device tensors total [1,C], violation [1,C] and the controls [1,C,T,2] (one launch)."""
+        assert self._fusable(), "batched search needs the built-in (fused) modules"
+        engine = runtime.default_engine()
+        controls = torch.from_numpy(np.asarray(z, dtype=np.float32)).view(1, z.shape[0], -1, 2).to(engine.device).contiguous()
+        env = self.env
+        if any(m.needs_rollout for m in self.modules):
+            num_p = self._num_particles if env.env_kind != "kalman" else 1
+            scene = env.scene_batch(num_p, self.planning_horizon, with_noise=False)
+        else:
+            scene = self.modules[0]._scene().to("cpu")
+        scene.ego_goal = self.goal.view(1, 2).clone()
+        res = engine.evaluate(scene.to(engine.device), controls, self._fused_spec(ado_ids), want=("total", "violation"))
+        return res["total"], res["violation"], controls
+
+    @property
+    def z_bounds(self) -> typing.Tuple[np.ndarray, np.ndarray]:
+        lb, ub = self.optimization_variable_bounds()
+        return np.asarray(lb), np.asarray(ub)
+
+
+class RandomSearch(SearchIntermediate):
+    """Uniform candidates within the control bounds, keep the best feasible (baselines/random_search.py:12-35)."""
+
+    def _optimize_inner(self, z_best, obj_best, num_candidates, tag, ado_ids):
+        lb, ub = self.z_bounds
+        z = np.random.uniform(lb, ub, size=(num_candidates, lb.size))
+        total, violation, controls = self.evaluate_batch(z, ado_ids)
+        idx, val, best = runtime.default_engine().argmin(total, violation, controls, constants.SOLVER_CONSTRAINT_LIMIT)
+        if int(idx[0]) < 0:
+            return None, np.inf
+        return best[0].flatten().cpu().numpy().astype(np.float64), float(val[0])
+
+    @property
+    def name(self) -> str:
+        return "random_search"

@@ -98,6 +98,58 @@ def check_constraints(lib, device, name):
     gio.assert_parity(np_(res["violation"][0, 0]), expect_vio, 1e-4, "violation", atol=1e-6)
 
 
+def check_seeded_adjoint(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, seed=0):
+    """Module interface of the kernel: the ego TRAJECTORY is given (not the controls) and the caller supplies adjoint
+    seeds d(loss)/d(mus), d(loss)/d(sigmas) (what torch.autograd hands to the backward of compute_distributions).
+    Checked against autograd of the CPU oracle for loss = <a, mus> + <b, sigmas>: gradient w.r.t. the trajectory rows
+    (grad_traj) and folded through the ego dynamics w.r.t. the controls (grad)."""
+    from oracle import torch_oracle as to
+    from mantrap_b200 import scenarios
+    scene_cpu = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=700 + seed,
+                                           param_seed=800 + seed, regular_sigma=True)
+    controls_cpu = scenarios.candidate_controls(num_scenes, num_candidates, t_hor, seed=900 + seed, u_max=1.0)
+    gen = torch.Generator().manual_seed(1000 + seed)
+    b = num_scenes * num_candidates
+    a_mus = torch.randn((b, n, t_hor, 4), generator=gen) * 0.1
+    a_sig = torch.randn((b, n, t_hor, 2), generator=gen)
+    osc = oracle_scene(scene_cpu, num_candidates)
+
+    def oracle(dtype):
+        sc = to.scene_to(osc, dtype)
+        u = controls_cpu.reshape(b, t_hor, 2).to(dtype).requires_grad_(True)
+        traj = to.ego_unroll(sc.ego0, u, sc.dt, ego_kind)
+        traj.retain_grad()
+        mus, sigmas = to.rollout(env_kind, sc.ado0, sc.goal, sc.v0, sc.sigma, sc.weights, sc.noise, traj, sc.dt)
+        loss = (mus * a_mus.to(dtype)).sum() + (sigmas * a_sig.to(dtype)).sum()
+        if not loss.requires_grad:                 # Kalman: the prediction does not depend on the ego (kalman.py:63)
+            return traj.detach(), torch.zeros_like(u), torch.zeros_like(traj), mus.detach(), sigmas.detach()
+        loss.backward()
+        return traj.detach(), torch.nan_to_num(u.grad), torch.nan_to_num(traj.grad), mus.detach(), sigmas.detach()
+
+    traj, g_u, g_traj, mus_ref, sig_ref = oracle(torch.float32)
+    _, g_u64, g_traj64, _, _ = oracle(torch.float64)
+    floor = max(float((g_u.double() - g_u64).abs().max()), float((g_traj.double() - g_traj64).abs().max()))
+    shape5 = (num_scenes, num_candidates)
+    spec = engine.ModuleSpec(seed_mus=a_mus.reshape(*shape5, n, t_hor, 4).to(device).contiguous(),
+                             seed_sigmas=a_sig.reshape(*shape5, n, t_hor, 2).to(device).contiguous())
+    ego_traj = traj.reshape(*shape5, t_hor + 1, 4).to(device).contiguous()
+    res = engine.launch_evaluate(lib, scene_cpu.to(device), None, spec, want=("grad", "grad_traj", "mus", "sigmas"),
+                                 ego_traj=ego_traj)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    gio.assert_parity(np_(res["mus"]).reshape(b, n, t_hor, 4), mus_ref.numpy(), gio.RTOL_ROLLOUT, "mus (trajectory given)",
+                      atol=gio.ATOL + 1e-6)
+    if env_kind != "kalman":
+        gio.assert_parity(np_(res["sigmas"]).reshape(b, n, t_hor, 2), sig_ref.numpy(), gio.RTOL_ROLLOUT, "sigmas", atol=gio.ATOL + 1e-6)
+    e1 = gio.assert_parity(np_(res["grad_traj"]).reshape(b, t_hor + 1, 4), g_traj.numpy(), gio.RTOL_GRAD, "seeded grad_traj",
+                           atol=gio.ATOL + 2 * floor)
+    e2 = gio.assert_parity(np_(res["grad"]).reshape(b, t_hor, 2), g_u.numpy(), gio.RTOL_GRAD, "seeded grad (controls)",
+                           atol=gio.ATOL + 2 * floor)
+    if env_kind == "sf":                       # (potential field: the ego may be outside every field of view)
+        assert float(g_u.abs().max()) > 0
+    return e1, e2
+
+
 def check_jacobian_golden(lib, device, name):
     """Constraint Jacobian kernel against the reference's `module.jacobian` vectors (control / speed limits: analytic,
     min-distance: row-by-row autograd through the reference rollout)."""

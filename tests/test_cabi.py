@@ -22,7 +22,7 @@ def test_header_symbols_exported(lib_path):
     declared = set(re.findall(r"\b(mtb_[a-z_]+)\s*\(", header))
     assert declared == set(_cabi.EXPORTED_SYMBOLS), declared ^ set(_cabi.EXPORTED_SYMBOLS)
     lib = _cabi.bind(ctypes.CDLL(lib_path))
-    assert lib.mtb_abi_version() == 1
+    assert lib.mtb_abi_version() == _cabi.ABI_VERSION
     assert b"bad argument" in lib.mtb_error_string(-1)
 
 

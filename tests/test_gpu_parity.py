@@ -68,6 +68,17 @@ def test_jacobian_vs_oracle(eng, env_kind, ego_kind, s, c, n, p, t_hor):
     kc.check_jacobian_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor)
 
 
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 3, 5, 4, 3, 10),
+    ("sf", "single", 2, 3, 12, 3, 8),
+    ("sf", "double", 2, 4, 20, 3, 12),
+    ("pf", "double", 2, 9, 5, 5, 15),
+    ("kalman", "double", 1, 2, 5, 1, 9),
+])
+def test_seeded_adjoint(eng, env_kind, ego_kind, s, c, n, p, t_hor):
+    kc.check_seeded_adjoint(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, seed=3)
+
+
 def test_argmin(eng):
     total = torch.tensor([[3.0, 1.0, 2.0, 0.5], [4.0, -1.0, 5.0, 6.0], [1.0, 2.0, 3.0, 4.0]], device=DEV)
     vio = torch.tensor([[0.0, 0.0, 0.0, 1.0], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]], device=DEV)

@@ -23,7 +23,7 @@ def emul_lib():
 
 
 def test_exports(emul_lib):
-    assert emul_lib.mtb_abi_version() == 1
+    assert emul_lib.mtb_abi_version() == _cabi.ABI_VERSION
 
 
 @pytest.mark.parametrize("name", gio.case_names())
@@ -64,6 +64,16 @@ def test_jacobian_golden(emul_lib, name):
 ])
 def test_jacobian_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor):
     kc.check_jacobian_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 2, 2, 4, 3, 6),
+    ("sf", "single", 1, 2, 12, 3, 5),
+    ("pf", "double", 1, 3, 5, 5, 7),
+    ("kalman", "single", 1, 1, 3, 1, 5),
+])
+def test_seeded_adjoint(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor):
+    kc.check_seeded_adjoint(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, seed=3)
 
 
 def test_argmin(emul_lib):
