@@ -283,11 +283,11 @@ def check_random_search(num_candidates):
 def check_closed_loop(solver_cls, env_kind, steps=3, **kwargs):
     """`solve()`: warm start, optimise, step the evaluation environment, repeat (trajopt.py:109-193; test_solver.py:111-153)."""
     env, goal = small_scene(env_kind)
+    torch.manual_seed(0)
+    np.random.seed(0)
     sol = solver_cls(env, goal=goal, t_planning=3,
                      modules=[modules.GoalNormModule, modules.InteractionAccelerationModule, modules.SpeedLimitModule])
     start = float(torch.norm(env.ego.position - goal))
-    torch.manual_seed(0)
-    np.random.seed(0)
     ego_traj, ado_trajs = sol.solve(time_steps=steps, warm_start_method="zeros", **kwargs)
     assert ego_traj.shape[1] == 5 and 2 <= ego_traj.shape[0] <= steps + 1
     assert ado_trajs.shape == (env.num_ados, ego_traj.shape[0], 1, 5)
