@@ -113,7 +113,8 @@ typedef struct mtb_outputs {
     float* total;      /* [S,C] sum of obj */
     float* grad;       /* [S,C,T,2] gradient of total (+ seeded loss) w.r.t. controls */
     float* grad_traj;  /* [S,C,T+1,4] the same gradient w.r.t. the ego trajectory rows (px,py,vx,vy), before it is
-                        * folded through the ego dynamics. grad == NULL && grad_traj == NULL = forward only */
+                        * folded through the ego dynamics; raw: NaN is NOT replaced (grad applies np.nan_to_num as the reference does).
+                        * grad == NULL && grad_traj == NULL = forward only */
     float* cons;       /* [S,C,R] normalised constraint rows: control (2T or T) | speed 2(T+1) | min-distance N*T */
     float* violation;  /* [S,C] summed constraint violation (optimization_module.py:512-533) */
     float* ego_traj;   /* [S,C,T+1,4] */

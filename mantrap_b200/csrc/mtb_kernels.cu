@@ -667,7 +667,9 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 for (int t = g; t <= T; t += GP) {
                     const float4 eb = egobar[t];
                     const float4 x = ego[t];
-                    gt[t] = make_float4(sanitize(eb.x) + cg * (x.x - gx), sanitize(eb.y) + cg * (x.y - gy), sanitize(eb.z), sanitize(eb.w));
+                    // raw (NaN propagates like in autograd; nan_to_num is applied by the caller AFTER the fold through the
+                    // ego dynamics, optimization_module.py:446, so one NaN zeroes the whole gradient as in the reference)
+                    gt[t] = make_float4(eb.x + cg * (x.x - gx), eb.y + cg * (x.y - gy), eb.z, eb.w);
                 }
             }
         }

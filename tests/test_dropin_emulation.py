@@ -14,7 +14,8 @@ from mantrap_b200 import _cabi, engine, runtime
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "host_emul"))
 import build_emul  # noqa: E402
 
-SMALL = ["c1_sf_n3_t10", "c2_pf_n5_t15", "kalman_n5_t15", "sf_single_n6_t12", "pf_single_n4_t8", "sf_dense_n5_t6"]
+SMALL = ["c1_sf_n3_t10", "c2_pf_n5_t15", "kalman_n5_t15", "sf_single_n6_t12", "pf_single_n4_t8", "sf_dense_n5_t6",
+         "c4_sf_n20_p3_t12"]
 
 
 @pytest.fixture(scope="module", autouse=True)
