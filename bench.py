@@ -46,7 +46,9 @@ def bytes_per_eval(t_hor, n_mod):
 # CPU arm: the oracle port of the reference algorithm on the host cores (cpu_baseline and --impl reference)
 # ---------------------------------------------------------------------------------------------------------------
 def _cpu_worker(args):
-    worker, n_batches, batch, seed = args
+    """One process = one core: evaluates batches of the bench workload with the CPU oracle until `budget` seconds of
+    timed work are spent (after one untimed warm-up batch). Returns (evaluations, seconds)."""
+    worker, budget, batch, seed = args
     import torch
     torch.set_num_threads(1)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -57,29 +59,33 @@ def _cpu_worker(args):
     controls = scenarios.candidate_controls(batch, 1, T_HORIZON, seed=seed + 2000 + worker)[:, 0]
     osc = kc.oracle_scene(scene, 1)
     mus_wo, _ = to.rollout("sf", osc.ado0, osc.goal, osc.v0, osc.sigma, osc.weights, None, T_HORIZON, scene.dt)
-    t0 = time.perf_counter()
-    for _ in range(n_batches):
+    to.evaluate(osc, controls, mus_wo, WEIGHTS)                                    # warm-up (allocator, autograd)
+    done, t0 = 0, time.perf_counter()
+    while True:
         to.evaluate(osc, controls, mus_wo, WEIGHTS)
-    return time.perf_counter() - t0
+        done += batch
+        elapsed = time.perf_counter() - t0
+        if elapsed >= budget:
+            return done, elapsed
 
 
 def cpu_arm(seconds_target=12.0, batch=32, workers=None):
-    """Times the CPU oracle (vectorised float32 torch port of the reference algorithm, one process per core, one
-    thread each) on a bounded sample of the bench workload. Returns (evals/s, cores, description)."""
+    """Times the CPU oracle (vectorised float32 torch port of the reference algorithm: forward rollout + objectives +
+    torch.autograd gradient; one process per core, one thread each) on a bounded sample of the bench workload.
+    Returns (evals/s, cores, description)."""
     import multiprocessing as mp
     workers = workers or os.cpu_count() or 1
     ctx = mp.get_context("fork")
     with ctx.Pool(workers) as pool:
-        warm = pool.map(_cpu_worker, [(w, 1, batch, 7) for w in range(workers)])
-        per_batch = max(warm)
-        n_batches = max(1, int(seconds_target / per_batch))
         t0 = time.perf_counter()
-        pool.map(_cpu_worker, [(w, n_batches, batch, 7) for w in range(workers)])
+        results = pool.map(_cpu_worker, [(w, seconds_target, batch, 7) for w in range(workers)])
         wall = time.perf_counter() - t0
-    evals = workers * n_batches * batch
+    evals = sum(r[0] for r in results)
+    timed = max(r[1] for r in results)
     sample = (f"{evals} evaluations of the bench workload (SF N={N_ADOS} P={N_PARTICLES} T={T_HORIZON}, goal+acc objective "
-              f"+ autograd gradient) = {workers} processes x {n_batches} batches x {batch}, wall {wall:.1f} s")
-    return evals / wall, workers, sample
+              f"+ autograd gradient) in {timed:.1f} s of timed work on {workers} single-threaded processes (batches of {batch}; "
+              f"wall incl. start-up {wall:.1f} s)")
+    return evals / timed, workers, sample
 
 
 def reference_arm(args):
@@ -89,11 +95,10 @@ def reference_arm(args):
     values = []
     sample = ""
     cores = os.cpu_count() or 1
-    for _ in range(args.warmup if args.warmup < 2 else 1):
-        cpu_arm(seconds_target=2.0)
     t0 = time.perf_counter()
+    budget = max(3.0, min(30.0, 60.0 / max(1, args.steps)))        # each "step" = one bounded sample of the workload
     for _ in range(max(1, args.steps)):
-        v, cores, sample = cpu_arm(seconds_target=max(2.0, 40.0 / max(1, args.steps)))
+        v, cores, sample = cpu_arm(seconds_target=budget)
         values.append(v)
     value = sum(values) / len(values)
     line = {
@@ -231,7 +236,7 @@ def main():
     bufs = eng.evaluate(scene, controls, spec, want=want, stats=stats)          # allocates outputs; counts pairs once
     torch.cuda.synchronize(dev)
     pair_stats = stats.tolist()
-    gathered = torch.empty((world, s_g, 2 + 2 * t_hor), dtype=torch.float32, device=dev) if world > 1 else None
+    from mantrap_b200 import parallel
     launches_per_step = 2
 
     def step(kernel_events=None):
@@ -241,9 +246,8 @@ def main():
         if kernel_events is not None:
             kernel_events[1].record()
         idx, val, best = eng.argmin(bufs["total"], bufs["violation"], controls)
-        if world > 1:   # the only exchange on the path: every rank learns every scene's best candidate
-            packed = torch.cat((val[:, None], idx.float()[:, None], best.reshape(s_g, -1)), dim=1)
-            dist.all_gather_into_tensor(gathered, packed)
+        if world > 1:   # the only exchange on the path: every rank learns every scene's best candidate (one all-gather)
+            val, idx, best = parallel.gather_best_scene_partitioned(val, idx, best, s_g * world)
         return idx, val, best
 
     def barrier():
@@ -283,7 +287,9 @@ def main():
     for _ in range(args.steps):
         api.evaluate_candidates_host(eng, scene, controls_host, spec, host_out, device_buffers=bufs, device_controls=controls)
         if world > 1:
-            dist.all_gather_into_tensor(gathered, host_out.last_packed_device)
+            rows = host_out.last_packed_device
+            parallel.gather_best_scene_partitioned(rows[:, 0].contiguous(), rows[:, 1].to(torch.int32),
+                                                   rows[:, 2:].reshape(s_g, t_hor, 2), s_g * world)
     e_stop.record()
     barrier()
     e_ms = torch.tensor([e_start.elapsed_time(e_stop)], dtype=torch.float64, device=dev)
@@ -303,12 +309,24 @@ def main():
         spec_fp32 = 2 * 148 * 128 * (sm_clock or 1965.0) * 1e6 / 1e12
         fp32_peak = min(spec_fp32, peaks["fp32_tflops"])
         evals_per_launch = s_g * c
-        f_eval = flops_per_eval(t_hor, N_ADOS, N_PARTICLES)
-        achieved = evals_per_launch * f_eval / (kernel_ms * 1e-3) / 1e12
-        # work actually executed: pairs inside the 2 m interaction radius + ego pairs (the reference skips the rest too)
+        # Algorithmic work: 150 FLOP per EXECUTED pair term (forward 50 incl. 7 MUFU + reverse 100; pairs
+        # outside the 2 m interaction radius are skipped by the reference as well, social_forces.py:152, and are NOT
+        # counted), 150 FLOP per particle-step (goal force, clamp, integration, mean/variance collapse, fwd + reverse)
+        # and 5 FLOP per (particle, ado, step) for the interaction-radius test (forward only).
+        steps_pp = (t_hor - 1) * N_ADOS * N_PARTICLES
         exec_pairs = (pair_stats[0] + pair_stats[1]) / evals_per_launch
-        executed = evals_per_launch * exec_pairs * 150.0 / (kernel_ms * 1e-3) / 1e12
+        f_eval = 150.0 * exec_pairs + 150.0 * steps_pp + 5.0 * steps_pp * N_ADOS
+        sfu_eval = 3.0 * (7.0 * exec_pairs + 5.0 * steps_pp)
+        achieved = evals_per_launch * f_eval / (kernel_ms * 1e-3) / 1e12
+        model_tflops = evals_per_launch * flops_per_eval(t_hor, N_ADOS, N_PARTICLES) / (kernel_ms * 1e-3) / 1e12
         hbm_achieved = evals_per_launch * bytes_per_eval(t_hor, 3) / (kernel_ms * 1e-3) / 1e9
+        traffic, traffic_src = None, None
+        try:        # DRAM bytes per evaluation from the committed ncu --set full capture of this kernel, scaled to this launch
+            prof = json.load(open(os.path.join(ROOT, "profiles", "evaluate_kernel_ncu.json")))
+            traffic = prof["dram_bytes_per_eval"] * evals_per_launch
+            traffic_src = prof["source"]
+        except Exception:
+            pass
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -318,15 +336,21 @@ def main():
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks.summary(),
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": achieved / fp32_peak, "traffic": None,
+                         "frac": achieved / fp32_peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "note": "compute-bound path (FP32 CUDA cores + MUFU; no contraction, HBM ~1e-3 of peak): the bound is "
+                                 "the FP32 pipe, not hbm/tensor",
                          "kernel": "mtb::evaluate_kernel<SF, GRAD>", "kernel_ms": kernel_ms,
                          "kernel_share_of_step": kernel_ms / ms_per_step,
-                         "work_model": "SURVEY 8(d): 150 (T-1) N P (N+1) FLOP per eval, all N+1 pair terms counted",
-                         "executed_tflops": executed, "executed_frac": executed / fp32_peak,
-                         "executed_pairs_per_eval": exec_pairs, "model_pairs_per_eval": (t_hor - 1) * N_ADOS * N_PARTICLES * (N_ADOS + 1),
+                         "work_model": "executed work: 150 FLOP x executed pair terms + 150 FLOP x particle-steps + 5 FLOP x "
+                                       "radius tests (DESIGN.md §6)",
+                         "flop_per_eval": f_eval, "executed_pairs_per_eval": exec_pairs,
                          "peak_source": f"min(2*148*128*f_max = {spec_fp32:.1f}, measured FMA probe = {peaks['fp32_tflops']:.1f}) TFLOP/s",
-                         "mufu_frac": evals_per_launch * sfu_per_eval(t_hor, N_ADOS, N_PARTICLES) / (kernel_ms * 1e-3) / 1e12 / peaks["mufu_tops"],
+                         "mufu_frac": evals_per_launch * sfu_eval / (kernel_ms * 1e-3) / 1e12 / peaks["mufu_tops"],
                          "mufu_peak_tops": peaks["mufu_tops"],
+                         "survey_model": {"flop_per_eval": flops_per_eval(t_hor, N_ADOS, N_PARTICLES), "tflops": model_tflops,
+                                          "frac": model_tflops / fp32_peak,
+                                          "note": "SURVEY 8(d) upper-bound model counting all N+1 pair terms per particle-step, "
+                                                  "including the out-of-radius pairs nobody evaluates; reported for reference only"},
                          "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
                                  "peak_source": peak_src}},
             "saturated_fraction": pair_stats[2] / evals_per_launch,

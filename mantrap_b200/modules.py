@@ -504,3 +504,13 @@ class MinDistanceModule(_FusedConstraintModule):
     @property
     def name(self) -> str:
         return "min_distance"
+
+
+# `mantrap.modules.baselines.*` of the reference (modules/baselines/__init__.py:1-5)
+import types as _types  # noqa: E402
+
+baselines = _types.SimpleNamespace(InteractionAccelerationModule=InteractionAccelerationModule,
+                                   InteractionVelocityModule=InteractionVelocityModule,
+                                   InteractionPositionModule=InteractionPositionModule)
+base = _types.SimpleNamespace(OptimizationModule=OptimizationModule, PureObjectiveModule=PureObjectiveModule,
+                              PureConstraintModule=PureConstraintModule)

@@ -499,3 +499,10 @@ class RandomSearch(SearchIntermediate):
     @property
     def name(self) -> str:
         return "random_search"
+
+
+# `mantrap.solver.baselines.*` of the reference (solver/baselines/__init__.py:1-4)
+import types as _types  # noqa: E402
+
+baselines = _types.SimpleNamespace(RandomSearch=RandomSearch)
+base = _types.SimpleNamespace(TrajOptSolver=TrajOptSolver, SearchIntermediate=SearchIntermediate)

@@ -127,8 +127,10 @@ def check_seeded_adjoint(lib, device, env_kind, ego_kind, num_scenes, num_candid
         return traj.detach(), torch.nan_to_num(u.grad), torch.nan_to_num(traj.grad), mus.detach(), sigmas.detach()
 
     traj, g_u, g_traj, mus_ref, sig_ref = oracle(torch.float32)
-    _, g_u64, g_traj64, _, _ = oracle(torch.float64)
+    _, g_u64, g_traj64, mus64, sig64 = oracle(torch.float64)
     floor = max(float((g_u.double() - g_u64).abs().max()), float((g_traj.double() - g_traj64).abs().max()))
+    # float32 conditioning of the rollout itself on random (dense) scenes, as in check_batched_vs_oracle
+    floor_roll = max(float((mus_ref.double() - mus64).abs().max()), float((sig_ref.double() - sig64).abs().max()))
     shape5 = (num_scenes, num_candidates)
     spec = engine.ModuleSpec(seed_mus=a_mus.reshape(*shape5, n, t_hor, 4).to(device).contiguous(),
                              seed_sigmas=a_sig.reshape(*shape5, n, t_hor, 2).to(device).contiguous())
@@ -138,9 +140,10 @@ def check_seeded_adjoint(lib, device, env_kind, ego_kind, num_scenes, num_candid
     if device != "cpu":
         torch.cuda.synchronize()
     gio.assert_parity(np_(res["mus"]).reshape(b, n, t_hor, 4), mus_ref.numpy(), gio.RTOL_ROLLOUT, "mus (trajectory given)",
-                      atol=gio.ATOL + 1e-6)
+                      atol=gio.ATOL + 1e-6 + 2 * floor_roll)
     if env_kind != "kalman":
-        gio.assert_parity(np_(res["sigmas"]).reshape(b, n, t_hor, 2), sig_ref.numpy(), gio.RTOL_ROLLOUT, "sigmas", atol=gio.ATOL + 1e-6)
+        gio.assert_parity(np_(res["sigmas"]).reshape(b, n, t_hor, 2), sig_ref.numpy(), gio.RTOL_ROLLOUT, "sigmas",
+                          atol=gio.ATOL + 1e-6 + 2 * floor_roll)
     e1 = gio.assert_parity(np_(res["grad_traj"]).reshape(b, t_hor + 1, 4), g_traj.numpy(), gio.RTOL_GRAD, "seeded grad_traj",
                            atol=gio.ATOL + 2 * floor)
     e2 = gio.assert_parity(np_(res["grad"]).reshape(b, t_hor, 2), g_u.numpy(), gio.RTOL_GRAD, "seeded grad (controls)",
