@@ -13,6 +13,14 @@
 static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
+// Fire-and-forget 16-byte float accumulation in L2 (REDG.E.ADD.F32x4, sm_90+): one instruction per pair adjoint instead
+// of four shared-memory compare-and-swap loops. The target lives in an L2-resident global scratch; loads / stores of it
+// bypass L1 (ld/st.global.cg) and are ordered against the reductions by the group barriers.
+static __device__ __forceinline__ void mtb_red_add_f4(float4* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+static __device__ __forceinline__ float4 mtb_ldcg_f4(const float4* addr) { return __ldcg(addr); }
+static __device__ __forceinline__ void mtb_stcg_f4(float4* addr, float4 v) { __stcg(addr, v); }
 #endif
 
 #include <cfloat>

@@ -32,9 +32,11 @@ struct KParams {
     int off_ctl, off_ego, off_egobar, off_mus, off_abar, off_q, off_misc, off_tape, off_mask;
     int per_eval_f, red_f;
     int tape_in_smem;
+    float4* abar_global;             // [grid][E][3][N] mean adjoints accumulated with L2 vector reductions (SF + GRAD)
     float4* tape_global;             // [grid][T-1][block]   when the tape does not fit in shared memory
     unsigned* mask_global;           // [grid][T-1][block][MW]
     int rows_control, rows_speed, rows_mind, R;
+    size_t ws_abar_bytes, ws_tape_bytes, ws_mask_bytes;   // workspace layout: mean adjoints | tape | interaction masks
 };
 
 // misc slots (per evaluation)
@@ -169,7 +171,10 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     float4* ego = reinterpret_cast<float4*>(sm + prm.off_ego);    // [T+1]
     float4* egobar = reinterpret_cast<float4*>(sm + prm.off_egobar);  // [T+1] adjoint from the environment
     float4* mus = reinterpret_cast<float4*>(sm + prm.off_mus);    // [T][N]
-    float4* abar = reinterpret_cast<float4*>(sm + prm.off_abar);  // [3][N] adjoint of the means (rotating)
+    // [3][N] adjoint of the means (rotating levels): shared memory, or the L2 scratch when pair terms scatter into it
+    const bool abar_l2 = prm.abar_global != nullptr;
+    float4* abar = abar_l2 ? prm.abar_global + ((size_t)blockIdx.x * prm.E + e) * 3 * N
+                           : reinterpret_cast<float4*>(sm + prm.off_abar);
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);     // [GP]
     float* misc = sm + prm.off_misc;
 
@@ -218,7 +223,10 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
         const float* ado0_s = prm.pb.ado0 + (size_t)s * N * 4;
         for (int k = g; k < N; k += GP) mus[k] = ld4(ado0_s + k * 4);
         if (GRAD) {
-            for (int idx = g; idx < 3 * N; idx += GP) abar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int idx = g; idx < 3 * N; idx += GP) {
+                if (abar_l2) mtb_stcg_f4(abar + idx, make_float4(0.f, 0.f, 0.f, 0.f));
+                else abar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
             for (int idx = g; idx <= T; idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         group_sync(GP, e);
@@ -521,10 +529,13 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             for (int t = T - 2; t >= 0 && any_adjoint; --t) {
                 group_sync(GP, e);                                // level t+1 adjoints complete
                 const int b_next = (t + 1) % 3, b_cur = t % 3, b_free = (t + 2) % 3;
-                for (int k = g; k < N; k += GP) abar[b_free * N + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int k = g; k < N; k += GP) {
+                    if (abar_l2) mtb_stcg_f4(abar + b_free * N + k, make_float4(0.f, 0.f, 0.f, 0.f));
+                    else abar[b_free * N + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
                 V2 eb_p = v2(0.f, 0.f), eb_v = v2(0.f, 0.f);      // this particle's share of the ego adjoint at t
                 if (active && env_adjoint) {
-                    float4 tot = abar[b_next * N + m];            // pair terms of step t+1 ...
+                    float4 tot = abar_l2 ? mtb_ldcg_f4(abar + b_next * N + m) : abar[b_next * N + m];   // pair terms of step t+1 ...
                     const float4 sd = objective_seed(prm, misc, mus, wo_scene, seed_mus_ev, m, t + 1, in_cost);
                     tot.x += sd.x + rec.x; tot.y += sd.y + rec.y; // ... + objective seed + mean-position recurrence
                     tot.z += sd.z + rec.z; tot.w += sd.w + rec.w;
@@ -584,9 +595,13 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                                 repulsion_adjoint(o, r, w, dt, fbar, rb, wb);
                                 pb = pb + rb; vb = vb + wb;
                                 if (t >= 1) {                     // mus[:, 0] are constants; adjoint of ado k's mean at level t
-                                    float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
-                                    atomic_add_f2(ac, -rb.x, -rb.y);
-                                    atomic_add_f2(ac + 2, -wb.x, -wb.y);
+                                    if (abar_l2) {
+                                        mtb_red_add_f4(abar + b_cur * N + k, -rb.x, -rb.y, -wb.x, -wb.y);
+                                    } else {
+                                        float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
+                                        atomic_add_f2(ac, -rb.x, -rb.y);
+                                        atomic_add_f2(ac + 2, -wb.x, -wb.y);
+                                    }
                                 }
                             }
                         }
@@ -766,13 +781,15 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const bool need_tape = want_grad && !kalman && prm.has_ego && prm.T > 1;
     const bool need_mask = need_tape && pb->env_kind == MTB_ENV_SOCIAL_FORCES;
 
+    // mean adjoints: pair terms scatter into them -> L2 scratch + vector reductions (social forces with an ego only)
+    const bool abar_l2 = need_mask && env_flag("MTB_ABAR_SMEM") == 0;
     auto layout = [&](int E, bool tape_in_smem) -> size_t {
         int off = 0;
         prm.off_ctl = off;    off += round_up(2 * prm.T, 4);
         prm.off_ego = off;    off += (prm.T + 1) * 4;
         prm.off_egobar = off; off += want_grad ? (prm.T + 1) * 4 : 0;
         prm.off_mus = off;    off += prm.T * prm.N * 4;
-        prm.off_abar = off;   off += want_grad ? 3 * prm.N * 4 : 0;
+        prm.off_abar = off;   off += (want_grad && !abar_l2) ? 3 * prm.N * 4 : 0;
         prm.off_q = off;      off += round_up(prm.GP * 2, 4);
         prm.off_misc = off;   off += kMiscFloats;
         prm.off_tape = off;   off += (need_tape && tape_in_smem) ? (prm.T - 1) * prm.GP * 4 : 0;
@@ -833,12 +850,13 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const int units_per_block = (prm.GP <= 32) ? block / 32 : E;
     const int max_grid = (prm.num_items + units_per_block - 1) / units_per_block;
     if (grid > max_grid) grid = max_grid;
-    workspace_bytes = 0;
+    prm.ws_abar_bytes = abar_l2 ? (size_t)grid * E * 3 * prm.N * sizeof(float4) : 0;
+    prm.ws_tape_bytes = prm.ws_mask_bytes = 0;
     if (need_tape && !tape_in_smem) {
-        const size_t tape_b = (size_t)grid * (prm.T - 1) * block * sizeof(float4);
-        const size_t mask_b = need_mask ? (size_t)grid * (prm.T - 1) * block * prm.MW * sizeof(unsigned) : 0;
-        workspace_bytes = tape_b + mask_b;
+        prm.ws_tape_bytes = (size_t)grid * (prm.T - 1) * block * sizeof(float4);
+        prm.ws_mask_bytes = need_mask ? (size_t)grid * (prm.T - 1) * block * prm.MW * sizeof(unsigned) : 0;
     }
+    workspace_bytes = prm.ws_abar_bytes + prm.ws_tape_bytes + prm.ws_mask_bytes;
     info.grid = grid;
     info.block = block;
     info.evals_per_block = E;
@@ -935,9 +953,12 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
     if (modules != nullptr && modules->w_goal != 0.f && modules->ego_goal == nullptr) return MTB_ERR_BAD_ARGUMENT;
     if (ws > 0) {
         if (workspace == nullptr || workspace_bytes < ws) return MTB_ERR_WORKSPACE;
-        const size_t tape_b = (size_t)info.grid * (prm.T - 1) * info.block * sizeof(float4);
-        prm.tape_global = reinterpret_cast<float4*>(workspace);
-        prm.mask_global = reinterpret_cast<unsigned*>(reinterpret_cast<char*>(workspace) + tape_b);
+        char* base = reinterpret_cast<char*>(workspace);
+        if (prm.ws_abar_bytes > 0) prm.abar_global = reinterpret_cast<float4*>(base);
+        if (prm.ws_tape_bytes > 0) {
+            prm.tape_global = reinterpret_cast<float4*>(base + prm.ws_abar_bytes);
+            prm.mask_global = reinterpret_cast<unsigned*>(base + prm.ws_abar_bytes + prm.ws_tape_bytes);
+        }
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (problem->env_kind) {

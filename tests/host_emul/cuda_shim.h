@@ -125,6 +125,12 @@ static inline unsigned long long atomicMin(unsigned long long* addr, unsigned lo
 }
 template <class T>
 static inline T __ldg(const T* p) { return *p; }
+static inline void mtb_red_add_f4(float4* addr, float a, float b, float c, float d) {
+    float* f = reinterpret_cast<float*>(addr);
+    atomicAdd(f, a); atomicAdd(f + 1, b); atomicAdd(f + 2, c); atomicAdd(f + 3, d);
+}
+static inline float4 mtb_ldcg_f4(const float4* addr) { return *addr; }
+static inline void mtb_stcg_f4(float4* addr, float4 v) { *addr = v; }
 static inline int __ffs(int x) { return __builtin_ffs(x); }
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
 static inline float rsqrtf(float x) { return 1.0f / sqrtf(x); }
