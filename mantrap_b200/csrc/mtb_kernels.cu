@@ -23,7 +23,7 @@ struct KParams {
     mtb_problem pb;
     mtb_modules md;
     mtb_outputs out;
-    int T, N, P, G, GP, E, MW;
+    int T, N, P, G, GP, E, MW, NW;   // NW = warps per evaluation group (1 for sub-warp groups)
     int num_items;
     long long num_evals;
     int has_ego, want_grad, want_env_adjoint, use_tape;
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 if (abar_l2) mtb_stcg_f4(abar + idx, make_float4(0.f, 0.f, 0.f, 0.f));
                 else abar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
-            for (int idx = g; idx <= T; idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int idx = g; idx < prm.NW * (T + 1); idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         group_sync(GP, e);
         if (has_ego && !traj_given && g == 0) {
@@ -619,8 +619,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                     vbar = vb;
                 }
                 // ego adjoint of step t: sum over the particles of the group (all lanes take part)
-                float* ebt = reinterpret_cast<float*>(egobar + t);
                 if (GP <= 32) {
+                    float* ebt = reinterpret_cast<float*>(egobar + t);
                     for (int off = GP >> 1; off > 0; off >>= 1) {
                         eb_p.x += __shfl_xor_sync(0xffffffffu, eb_p.x, off);
                         eb_p.y += __shfl_xor_sync(0xffffffffu, eb_p.y, off);
@@ -635,10 +635,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                         eb_v.x += __shfl_xor_sync(0xffffffffu, eb_v.x, off);
                         eb_v.y += __shfl_xor_sync(0xffffffffu, eb_v.y, off);
                     }
-                    if ((tid & 31) == 0) {
-                        atomic_add_f2(ebt, eb_p.x, eb_p.y);
-                        atomic_add_f2(ebt + 2, eb_v.x, eb_v.y);
-                    }
+                    // one slot per warp of the group, summed when the adjoint is folded (no shared-memory atomics)
+                    if ((tid & 31) == 0) egobar[(g >> 5) * (T + 1) + t] = make_float4(eb_p.x, eb_p.y, eb_v.x, eb_v.y);
                 }
             }
             group_sync(GP, e);
@@ -652,7 +650,11 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 float gpx = 0.f, gpy = 0.f, gvx = 0.f, gvy = 0.f;     // goal part (kept apart: separate nan_to_num)
                 const bool dbl = prm.pb.ego_kind == MTB_EGO_DOUBLE_INTEGRATOR;
                 for (int t = T; t >= 1; --t) {
-                    const float4 eb = egobar[t];
+                    float4 eb = egobar[t];
+                    for (int w = 1; w < prm.NW; ++w) {
+                        const float4 o = egobar[w * (T + 1) + t];
+                        eb.x += o.x; eb.y += o.y; eb.z += o.z; eb.w += o.w;
+                    }
                     const float4 x = ego[t];
                     const float bpx = cg * (x.x - gx), bpy = cg * (x.y - gy);
                     float outx, outy, goutx, gouty;
@@ -680,7 +682,11 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 float gx = 0.f, gy = 0.f;
                 if (prm.md.w_goal != 0.f) { gx = __ldg(prm.md.ego_goal + (size_t)s * 2); gy = __ldg(prm.md.ego_goal + (size_t)s * 2 + 1); }
                 for (int t = g; t <= T; t += GP) {
-                    const float4 eb = egobar[t];
+                    float4 eb = egobar[t];
+                    for (int w = 1; w < prm.NW; ++w) {
+                        const float4 o = egobar[w * (T + 1) + t];
+                        eb.x += o.x; eb.y += o.y; eb.z += o.z; eb.w += o.w;
+                    }
                     const float4 x = ego[t];
                     // raw (NaN propagates like in autograd; nan_to_num is applied by the caller AFTER the fold through the
                     // ego dynamics, optimization_module.py:446, so one NaN zeroes the whole gradient as in the reference)
@@ -771,6 +777,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     } else {
         prm.GP = round_up(prm.G, 32);
     }
+    prm.NW = prm.GP <= 32 ? 1 : prm.GP / 32;
     // constraint rows
     {
         const ConstraintRows rows = constraint_rows(pb, md);
@@ -787,7 +794,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         int off = 0;
         prm.off_ctl = off;    off += round_up(2 * prm.T, 4);
         prm.off_ego = off;    off += (prm.T + 1) * 4;
-        prm.off_egobar = off; off += want_grad ? (prm.T + 1) * 4 : 0;
+        prm.off_egobar = off; off += want_grad ? prm.NW * (prm.T + 1) * 4 : 0;
         prm.off_mus = off;    off += prm.T * prm.N * 4;
         prm.off_abar = off;   off += (want_grad && !abar_l2) ? 3 * prm.N * 4 : 0;
         prm.off_q = off;      off += round_up(prm.GP * 2, 4);
@@ -812,7 +819,9 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     if (need_tape) {
         const size_t with_tape = layout(E, true);
         const int resident = (int)((size_t)lim.smem_per_sm / (with_tape + 1024));
-        tape_in_smem = resident >= 3 && with_tape <= (size_t)lim.max_smem;
+        // (measured on the config-4 shape with 3 resident blocks either way: L2 tape 11.6 ms, shared tape 12.3 ms -- a
+        // 76 KB block leaves no L1 for the scene / baseline loads)
+        tape_in_smem = resident >= 3 && with_tape <= (size_t)32 * 1024;
         const int knob = env_flag("MTB_TAPE_GLOBAL");       // development knob: 1 = global, 2 = shared
         if (knob == 1) tape_in_smem = false;
         if (knob == 2) tape_in_smem = true;
