@@ -27,12 +27,13 @@ struct KParams {
     int num_items;
     long long num_evals;
     int has_ego, want_grad, want_env_adjoint, use_tape;
-    float pair_cut2;                 // largest d^2 with sqrtf(d^2) <= interaction radius
+    float pair_cut2;                 // the float after the largest d^2 with sqrtf(d^2) <= interaction radius (strict <)
     // shared-memory layout (float units, per evaluation) -------------------------------------------------
-    int off_ctl, off_ego, off_egobar, off_mus, off_abar, off_q, off_misc, off_tape, off_mask;
+    int off_ctl, off_ego, off_egobar, off_mus, off_pos, off_q, off_misc, off_tape, off_mask;
+    int NP4;                         // N rounded up to 4: length of the SoA position rows used by the radius test
     int per_eval_f, red_f;
     int tape_in_smem;
-    float4* abar_global;             // [grid][E][3][N] mean adjoints accumulated with L2 vector reductions (SF + GRAD)
+    float4* abar_global;             // [grid][E][T][N] adjoints of the means: objective seeds + pair terms (L2 vector reductions)
     float4* tape_global;             // [grid][T-1][block]   when the tape does not fit in shared memory
     unsigned* mask_global;           // [grid][T-1][block][MW]
     int rows_control, rows_speed, rows_mind, R;
@@ -91,12 +92,48 @@ MTB_DEV Red4 group_reduce4(Red4 v, int GP, int e, float* red) {
     return r;
 }
 
-// Shared-memory float accumulation. sm_100a has no native FP32 shared atomic add: this compiles to an
-// ATOMS.CAST.SPIN compare-and-swap loop. Measured alternatives (one 64-bit CAS per float2; staging the pair adjoints
-// in consumed tape rows and gathering them per target ado) were slower on the config-4 shape, see DESIGN.md.
-MTB_DEV void atomic_add_f2(float* addr, float a, float b) {
-    atomicAdd(addr, a);
-    atomicAdd(addr + 1, b);
+// Sum of four values over the W = 2^n lanes of a lane group (W <= 32, aligned), 6 shuffles instead of 4 log2(W): the first two
+// butterfly levels halve the number of live values (lanes keep the components selected by their own lane bits), the rest
+// reduce one value per lane. Afterwards lane l of the group holds the total of component ((l & W/2) ? 2 : 0) + ((l & W/4) ? 1 : 0).
+// All 32 lanes of the warp must call it. W >= 4.
+MTB_DEV float transpose_reduce4(float a, float b, float c, float d, int W) {
+    const int lane = threadIdx.x & 31;
+    const int h1 = W >> 1, h2 = W >> 2;
+    const bool up1 = (lane & h1) != 0, up2 = (lane & h2) != 0;
+    const float k0 = up1 ? c : a, k1 = up1 ? d : b;               // kept
+    const float s0 = up1 ? a : c, s1 = up1 ? b : d;               // sent to the partner half
+    const float r0 = k0 + __shfl_xor_sync(0xffffffffu, s0, h1);
+    const float r1 = k1 + __shfl_xor_sync(0xffffffffu, s1, h1);
+    float r = (up2 ? r1 : r0) + __shfl_xor_sync(0xffffffffu, up2 ? r0 : r1, h2);
+    for (int off = h2 >> 1; off > 0; off >>= 1) r += __shfl_xor_sync(0xffffffffu, r, off);
+    return r;
+}
+
+// Radius test of one particle against four ado means (SoA rows X, Y), appended to a running bit mask: the mask is shifted
+// left by four and the new low bits 3..0 are the tests of X.w .. X.x (callers walk the ados from high to low, so that bit k of
+// the finished word is ado k). A test is  fmaf(dx, dx, dy * dy) < cut_above  with (dx, dy) = p - mean, cut_above = the float
+// after the largest d^2 whose sqrtf is <= radius, i.e. exactly `norm <= radius`. Device: packed FP32 (two tests per
+// instruction); the sign bit of d^2 - cut_above is funnel-shifted into the mask (no predicates, no selects).
+MTB_DEV unsigned radius_bits4(unsigned acc, float4 X, float4 Y, float px, float py, float cut_above) {
+#if !defined(MTB_HOST_EMUL) && !defined(MTB_NO_F32X2)
+    const float2 m1 = make_float2(-1.f, -1.f), pxx = make_float2(px, px), pyy = make_float2(py, py);
+    const float2 nc = make_float2(-cut_above, -cut_above);
+    const float2 dx01 = __ffma2_rn(make_float2(X.x, X.y), m1, pxx), dx23 = __ffma2_rn(make_float2(X.z, X.w), m1, pxx);
+    const float2 dy01 = __ffma2_rn(make_float2(Y.x, Y.y), m1, pyy), dy23 = __ffma2_rn(make_float2(Y.z, Y.w), m1, pyy);
+    const float2 s01 = __fadd2_rn(__ffma2_rn(dx01, dx01, __fmul2_rn(dy01, dy01)), nc);
+    const float2 s23 = __fadd2_rn(__ffma2_rn(dx23, dx23, __fmul2_rn(dy23, dy23)), nc);
+    acc = __funnelshift_l(__float_as_uint(s23.y), acc, 1);
+    acc = __funnelshift_l(__float_as_uint(s23.x), acc, 1);
+    acc = __funnelshift_l(__float_as_uint(s01.y), acc, 1);
+    acc = __funnelshift_l(__float_as_uint(s01.x), acc, 1);
+    return acc;
+#else
+    const float d0 = fmaf(px - X.x, px - X.x, (py - Y.x) * (py - Y.x));
+    const float d1 = fmaf(px - X.y, px - X.y, (py - Y.y) * (py - Y.y));
+    const float d2 = fmaf(px - X.z, px - X.z, (py - Y.z) * (py - Y.z));
+    const float d3 = fmaf(px - X.w, px - X.w, (py - Y.w) * (py - Y.w));
+    return (acc << 4) | (d0 < cut_above ? 1u : 0u) | (d1 < cut_above ? 2u : 0u) | (d2 < cut_above ? 4u : 0u) | (d3 < cut_above ? 8u : 0u);
+#endif
 }
 
 MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py:446)
@@ -171,27 +208,28 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     float4* ego = reinterpret_cast<float4*>(sm + prm.off_ego);    // [T+1]
     float4* egobar = reinterpret_cast<float4*>(sm + prm.off_egobar);  // [T+1] adjoint from the environment
     float4* mus = reinterpret_cast<float4*>(sm + prm.off_mus);    // [T][N]
-    // [3][N] adjoint of the means (rotating levels): shared memory, or the L2 scratch when pair terms scatter into it
-    const bool abar_l2 = prm.abar_global != nullptr;
-    float4* abar = abar_l2 ? prm.abar_global + ((size_t)blockIdx.x * prm.E + e) * 3 * N
-                           : reinterpret_cast<float4*>(sm + prm.off_abar);
+    float* posx = sm + prm.off_pos;                               // [NP4] mean positions of the current level, SoA, padded
+    float* posy = posx + prm.NP4;                                 //       with +inf (radius test, four ados per load)
+    // [T][N] adjoints of the means in an L2-resident scratch: seeded by the objectives, pair terms add with red.global
+    float4* abar = prm.abar_global + ((size_t)blockIdx.x * prm.E + e) * (size_t)(T * N);
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);     // [GP]
     float* misc = sm + prm.off_misc;
 
-    float4* tape;            // [(T-1)][stride] (p.x, p.y, u.x, u.y) of every particle before its step
-    unsigned* maskbuf;       // [(T-1)][stride][MW] interaction bit masks
-    int tape_stride, tape_idx;
+    // Backward tape, addressed per thread: row t of this particle is tape[t * tape_stride] = (p.x, p.y, u.x, u.y) before its
+    // step and maskbuf[t * mask_stride + wd] = its interaction bit masks. Shared memory, or a per-block L2-resident scratch.
+    float4* tape;
+    unsigned* maskbuf;
+    int tape_stride;
     if (prm.tape_in_smem) {
-        tape = reinterpret_cast<float4*>(sm + prm.off_tape);
-        maskbuf = reinterpret_cast<unsigned*>(sm + prm.off_mask);
+        tape = reinterpret_cast<float4*>(sm + prm.off_tape) + g;
+        maskbuf = reinterpret_cast<unsigned*>(sm + prm.off_mask) + g * MW;
         tape_stride = GP;
-        tape_idx = g;
     } else {
-        tape = prm.tape_global + (size_t)blockIdx.x * (size_t)(T - 1) * blockDim.x;
-        maskbuf = prm.mask_global + (size_t)blockIdx.x * (size_t)(T - 1) * blockDim.x * MW;
+        tape = prm.tape_global + (size_t)blockIdx.x * (size_t)(T - 1) * blockDim.x + tid;
+        maskbuf = prm.mask_global + ((size_t)blockIdx.x * (size_t)(T - 1) * blockDim.x + tid) * MW;
         tape_stride = blockDim.x;
-        tape_idx = tid;
     }
+    const int mask_stride = tape_stride * MW;
 
     unsigned long long n_pairs = 0, n_ego = 0;
 
@@ -221,12 +259,13 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             for (int t = g; t <= T; t += GP) ego[t] = ld4(x_g + t * 4);
         }
         const float* ado0_s = prm.pb.ado0 + (size_t)s * N * 4;
-        for (int k = g; k < N; k += GP) mus[k] = ld4(ado0_s + k * 4);
+        for (int k = g; k < prm.NP4; k += GP) {
+            float4 a0 = make_float4(INFINITY, INFINITY, 0.f, 0.f);
+            if (k < N) { a0 = ld4(ado0_s + k * 4); mus[k] = a0; }
+            posx[k] = a0.x;
+            posy[k] = a0.y;
+        }
         if (GRAD) {
-            for (int idx = g; idx < 3 * N; idx += GP) {
-                if (abar_l2) mtb_stcg_f4(abar + idx, make_float4(0.f, 0.f, 0.f, 0.f));
-                else abar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
             for (int idx = g; idx < prm.NW * (T + 1); idx += GP) egobar[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         group_sync(GP, e);
@@ -288,29 +327,19 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 V2 u;
                 if (ENV == MTB_ENV_SOCIAL_FORCES) {
                     const V2 fgoal = goal_force(p, v, goal, inv_tau, prm.pb.sf_goal_radius);
-                    // which ado means are inside the interaction radius (social_forces.py:148-153)
-                    unsigned mk0 = 0u, mk1 = 0u;
-                    {
-                        const int n0 = N < 32 ? N : 32;
-#pragma unroll 4
-                        for (int k = 0; k < n0; ++k) {
-                            const float4 mu = mus_t[k];
-                            const float dx = p.x - mu.x, dy = p.y - mu.y;
-                            if (fmaf(dx, dx, dy * dy) <= prm.pair_cut2) mk0 |= (1u << k);
-                        }
-                        for (int k = 32; k < N; ++k) {
-                            const float4 mu = mus_t[k];
-                            const float dx = p.x - mu.x, dy = p.y - mu.y;
-                            if (fmaf(dx, dx, dy * dy) <= prm.pair_cut2) mk1 |= (1u << (k - 32));
-                        }
-                        if (m < 32) mk0 &= ~(1u << m); else mk1 &= ~(1u << (m - 32));   // never the own ado
-                    }
+                    // which ado means are inside the interaction radius (social_forces.py:148-153): four per iteration
                     V2 frep = v2(0.f, 0.f);
                     for (int wd = 0; wd < MW; ++wd) {
-                        unsigned bits = wd == 0 ? mk0 : mk1;
-                        if (GRAD && prm.use_tape) maskbuf[((size_t)t * tape_stride + tape_idx) * MW + wd] = bits;
+                        unsigned bits = 0u;
+                        const int kbase = wd << 5;
+                        const int kend = (prm.NP4 - kbase) < 32 ? (prm.NP4 - kbase) : 32;
+#pragma unroll 2
+                        for (int k0 = kend - 4; k0 >= 0; k0 -= 4)
+                            bits = radius_bits4(bits, ld4(posx + kbase + k0), ld4(posy + kbase + k0), p.x, p.y, prm.pair_cut2);
+                        if ((m >> 5) == wd) bits &= ~(1u << (m & 31));          // never the own ado
+                        if (GRAD && prm.use_tape) maskbuf[t * mask_stride + wd] = bits;
                         while (bits) {
-                            const int k = (wd << 5) + __ffs((int)bits) - 1;
+                            const int k = kbase + __ffs((int)bits) - 1;
                             bits &= bits - 1;
                             const float4 mu = mus_t[k];
                             const RepulsionFwd o = repulsion_forward(p - v2(mu.x, mu.y), v - v2(mu.z, mu.w), pv0, psig, dt, u_ped);
@@ -336,7 +365,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 } else {
                     u = v;                                        // Kalman: constant velocity (kalman.py:80)
                 }
-                if (GRAD && prm.use_tape) tape[(size_t)t * tape_stride + tape_idx] = make_float4(p.x, p.y, u.x, u.y);
+                if (GRAD && prm.use_tape) tape[t * tape_stride] = make_float4(p.x, p.y, u.x, u.y);
                 const V2 up = (ENV == MTB_ENV_KALMAN) ? u : feasible(u, u_ped);
                 v = up;
                 p = v2(fmaf(dt, up.x, p.x), fmaf(dt, up.y, p.y));
@@ -354,7 +383,10 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 for (int j = 0; j < P; ++j) { sx += qbuf[g + j].x; sy += qbuf[g + j].y; }
                 const float mx = sx / (float)P, my = sy / (float)P;
                 const float4 cur = mus_t[m];
-                mus[(t + 1) * N + m] = make_float4(fmaf(cur.z, dt, cur.x), fmaf(cur.w, dt, cur.y), mx, my);
+                const float npx = fmaf(cur.z, dt, cur.x), npy = fmaf(cur.w, dt, cur.y);
+                mus[(t + 1) * N + m] = make_float4(npx, npy, mx, my);
+                posx[m] = npx;
+                posy[m] = npy;
                 if (sig_out != nullptr) {
                     float vx = prm.pb.kalman_noise, vy = prm.pb.kalman_noise;
                     if (ENV != MTB_ENV_KALMAN) {
@@ -524,31 +556,35 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             if (GP <= 32) any_adjoint = __ballot_sync(0xffffffffu, env_adjoint) != 0u;
             V2 pbar = v2(0.f, 0.f), vbar = v2(0.f, 0.f);
             float4 rec = make_float4(0.f, 0.f, 0.f, 0.f);         // adjoint flowing along mu_p[t+1] = mu_p[t] + dt mu_v[t]
-            const bool in_cost = active && (amask == nullptr || amask[m] != 0);
             const float w_over_p = pw / (float)P;
+            // Seed the adjoints of the means with the objective derivatives (and the caller's seeds), once per (ado, level):
+            // abar[level][k] = d(objectives)/d(mus[k, level]); the pair terms of the sweep below accumulate on top.
+            if (env_adjoint) {
+                for (int idx = g; idx < (T - 1) * N; idx += GP) {
+                    const int lv = idx / N, k = idx - lv * N;
+                    const bool k_in_cost = amask == nullptr || amask[k] != 0;
+                    mtb_stcg_f4(abar + (lv + 1) * N + k, objective_seed(prm, misc, mus, wo_scene, seed_mus_ev, k, lv + 1, k_in_cost));
+                }
+            }
+            float4 tape_next = make_float4(0.f, 0.f, 0.f, 0.f);   // tape row t, carried from the previous iteration's look-back
+            if (active && env_adjoint && T >= 2) tape_next = tape[(T - 2) * tape_stride];
             for (int t = T - 2; t >= 0 && any_adjoint; --t) {
                 group_sync(GP, e);                                // level t+1 adjoints complete
-                const int b_next = (t + 1) % 3, b_cur = t % 3, b_free = (t + 2) % 3;
-                for (int k = g; k < N; k += GP) {
-                    if (abar_l2) mtb_stcg_f4(abar + b_free * N + k, make_float4(0.f, 0.f, 0.f, 0.f));
-                    else abar[b_free * N + k] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
                 V2 eb_p = v2(0.f, 0.f), eb_v = v2(0.f, 0.f);      // this particle's share of the ego adjoint at t
                 if (active && env_adjoint) {
-                    float4 tot = abar_l2 ? mtb_ldcg_f4(abar + b_next * N + m) : abar[b_next * N + m];   // pair terms of step t+1 ...
-                    const float4 sd = objective_seed(prm, misc, mus, wo_scene, seed_mus_ev, m, t + 1, in_cost);
-                    tot.x += sd.x + rec.x; tot.y += sd.y + rec.y; // ... + objective seed + mean-position recurrence
-                    tot.z += sd.z + rec.z; tot.w += sd.w + rec.w;
+                    float4 tot = mtb_ldcg_f4(abar + (t + 1) * N + m);   // objective seed + pair terms of step t+1 ...
+                    tot.x += rec.x; tot.y += rec.y;               // ... + mean-position recurrence
+                    tot.z += rec.z; tot.w += rec.w;
                     rec = make_float4(tot.x, tot.y, dt * tot.x, dt * tot.y);   // (identical in the P threads of ado m)
                     // mu_v[t+1] = (1/P) sum_i w_i (v'_i + noise)
                     vbar.x = fmaf(tot.z, w_over_p, vbar.x);
                     vbar.y = fmaf(tot.w, w_over_p, vbar.y);
-                    const float4 tp = tape[(size_t)t * tape_stride + tape_idx];
+                    const float4 tp = tape_next;
                     const V2 pt = v2(tp.x, tp.y), ut = v2(tp.z, tp.w);
                     V2 vt = v_init;
                     if (t > 0) {
-                        const float4 tq = tape[(size_t)(t - 1) * tape_stride + tape_idx];
-                        vt = feasible(v2(tq.z, tq.w), u_ped);
+                        tape_next = tape[(t - 1) * tape_stride];
+                        vt = feasible(v2(tape_next.z, tape_next.w), u_ped);
                     }
                     if (seed_sig_ev != nullptr) {
                         // var[m,t+1] = sum_i (q_i - mean q)^2 / (P-1), q_i = w_i (v'_i + noise): d var / d v'_i =
@@ -584,7 +620,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                             eb_p = eb_p - rb; eb_v = eb_v - wb;
                         }
                         for (int wd = 0; wd < MW; ++wd) {
-                            unsigned bits = maskbuf[((size_t)t * tape_stride + tape_idx) * MW + wd];
+                            unsigned bits = maskbuf[t * mask_stride + wd];
                             while (bits) {
                                 const int k = (wd << 5) + __ffs((int)bits) - 1;
                                 bits &= bits - 1;
@@ -594,15 +630,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                                 V2 rb, wb;
                                 repulsion_adjoint(o, r, w, dt, fbar, rb, wb);
                                 pb = pb + rb; vb = vb + wb;
-                                if (t >= 1) {                     // mus[:, 0] are constants; adjoint of ado k's mean at level t
-                                    if (abar_l2) {
-                                        mtb_red_add_f4(abar + b_cur * N + k, -rb.x, -rb.y, -wb.x, -wb.y);
-                                    } else {
-                                        float* ac = reinterpret_cast<float*>(abar + b_cur * N + k);
-                                        atomic_add_f2(ac, -rb.x, -rb.y);
-                                        atomic_add_f2(ac + 2, -wb.x, -wb.y);
-                                    }
-                                }
+                                // mus[:, 0] are constants; adjoint of ado k's mean at level t
+                                if (t >= 1) mtb_red_add_f4(abar + t * N + k, -rb.x, -rb.y, -wb.x, -wb.y);
                             }
                         }
                     } else if (ENV == MTB_ENV_POTENTIAL_FIELD) {  // u = v + gate * impact(ego_p - p)
@@ -618,25 +647,24 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                     pbar = pb;
                     vbar = vb;
                 }
-                // ego adjoint of step t: sum over the particles of the group (all lanes take part)
-                if (GP <= 32) {
-                    float* ebt = reinterpret_cast<float*>(egobar + t);
-                    for (int off = GP >> 1; off > 0; off >>= 1) {
-                        eb_p.x += __shfl_xor_sync(0xffffffffu, eb_p.x, off);
-                        eb_p.y += __shfl_xor_sync(0xffffffffu, eb_p.y, off);
-                        eb_v.x += __shfl_xor_sync(0xffffffffu, eb_v.x, off);
-                        eb_v.y += __shfl_xor_sync(0xffffffffu, eb_v.y, off);
+                // ego adjoint of step t: sum over the particles of the group (all lanes take part); one slot per warp of the
+                // group, summed when the adjoint is folded (no shared-memory atomics)
+                {
+                    const int W = GP < 32 ? GP : 32;
+                    const int l = g & (W - 1);
+                    float* ebt = reinterpret_cast<float*>(egobar + (GP <= 32 ? 0 : (g >> 5) * (T + 1)) + t);
+                    if (W >= 4) {
+                        const float r = transpose_reduce4(eb_p.x, eb_p.y, eb_v.x, eb_v.y, W);
+                        if ((l & ((W >> 2) - 1)) == 0) ebt[l / (W >> 2)] = r;
+                    } else {
+                        for (int off = W >> 1; off > 0; off >>= 1) {
+                            eb_p.x += __shfl_xor_sync(0xffffffffu, eb_p.x, off);
+                            eb_p.y += __shfl_xor_sync(0xffffffffu, eb_p.y, off);
+                            eb_v.x += __shfl_xor_sync(0xffffffffu, eb_v.x, off);
+                            eb_v.y += __shfl_xor_sync(0xffffffffu, eb_v.y, off);
+                        }
+                        if (l == 0) { ebt[0] = eb_p.x; ebt[1] = eb_p.y; ebt[2] = eb_v.x; ebt[3] = eb_v.y; }
                     }
-                    if (g == 0) { ebt[0] = eb_p.x; ebt[1] = eb_p.y; ebt[2] = eb_v.x; ebt[3] = eb_v.y; }
-                } else {
-                    for (int off = 16; off > 0; off >>= 1) {
-                        eb_p.x += __shfl_xor_sync(0xffffffffu, eb_p.x, off);
-                        eb_p.y += __shfl_xor_sync(0xffffffffu, eb_p.y, off);
-                        eb_v.x += __shfl_xor_sync(0xffffffffu, eb_v.x, off);
-                        eb_v.y += __shfl_xor_sync(0xffffffffu, eb_v.y, off);
-                    }
-                    // one slot per warp of the group, summed when the adjoint is folded (no shared-memory atomics)
-                    if ((tid & 31) == 0) egobar[(g >> 5) * (T + 1) + t] = make_float4(eb_p.x, eb_p.y, eb_v.x, eb_v.y);
                 }
             }
             group_sync(GP, e);
@@ -767,9 +795,10 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     prm.P = kalman ? 1 : pb->num_particles;
     prm.G = prm.N * prm.P;
     prm.MW = (prm.N + 31) / 32;
+    prm.NP4 = round_up(prm.N, 4);
     prm.has_ego = pb->ego_kind != MTB_EGO_NONE;
     prm.want_grad = want_grad ? 1 : 0;
-    prm.pair_cut2 = pair_cut_squared(pb->sf_interaction_radius);
+    prm.pair_cut2 = nextafterf(pair_cut_squared(pb->sf_interaction_radius), INFINITY);   // d^2 < pair_cut2  <=>  norm <= radius
     if (prm.G <= 32) {
         int gp = 1;
         while (gp < prm.G) gp <<= 1;
@@ -788,15 +817,15 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const bool need_tape = want_grad && !kalman && prm.has_ego && prm.T > 1;
     const bool need_mask = need_tape && pb->env_kind == MTB_ENV_SOCIAL_FORCES;
 
-    // mean adjoints: pair terms scatter into them -> L2 scratch + vector reductions (social forces with an ego only)
-    const bool abar_l2 = need_mask && env_flag("MTB_ABAR_SMEM") == 0;
+    // adjoints of the means [T][N] per evaluation: L2-resident scratch (objective seeds + vector reductions of the pair terms)
+    const bool abar_l2 = need_tape;
     auto layout = [&](int E, bool tape_in_smem) -> size_t {
         int off = 0;
         prm.off_ctl = off;    off += round_up(2 * prm.T, 4);
         prm.off_ego = off;    off += (prm.T + 1) * 4;
         prm.off_egobar = off; off += want_grad ? prm.NW * (prm.T + 1) * 4 : 0;
         prm.off_mus = off;    off += prm.T * prm.N * 4;
-        prm.off_abar = off;   off += (want_grad && !abar_l2) ? 3 * prm.N * 4 : 0;
+        prm.off_pos = off;    off += 2 * prm.NP4;
         prm.off_q = off;      off += round_up(prm.GP * 2, 4);
         prm.off_misc = off;   off += kMiscFloats;
         prm.off_tape = off;   off += (need_tape && tape_in_smem) ? (prm.T - 1) * prm.GP * 4 : 0;
@@ -859,7 +888,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const int units_per_block = (prm.GP <= 32) ? block / 32 : E;
     const int max_grid = (prm.num_items + units_per_block - 1) / units_per_block;
     if (grid > max_grid) grid = max_grid;
-    prm.ws_abar_bytes = abar_l2 ? (size_t)grid * E * 3 * prm.N * sizeof(float4) : 0;
+    prm.ws_abar_bytes = abar_l2 ? (size_t)grid * E * prm.T * prm.N * sizeof(float4) : 0;
     prm.ws_tape_bytes = prm.ws_mask_bytes = 0;
     if (need_tape && !tape_in_smem) {
         prm.ws_tape_bytes = (size_t)grid * (prm.T - 1) * block * sizeof(float4);

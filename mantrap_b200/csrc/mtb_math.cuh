@@ -19,15 +19,25 @@
 
 namespace mtb {
 
-struct V2 {
+struct alignas(8) V2 {
     float x, y;
 };
 MTB_DEV V2 v2(float x, float y) { V2 r; r.x = x; r.y = y; return r; }
+#if !defined(MTB_HOST_EMUL) && !defined(MTB_NO_F32X2)
+// sm_100 packed FP32 (FADD2 / FMUL2 / FFMA2): one issue slot per 2-vector operation. The kernels are bound by
+// instruction issue, not by the FMA pipe, and every quantity of the step models is a 2-vector.
+MTB_DEV float2 f2(V2 a) { return make_float2(a.x, a.y); }
+MTB_DEV V2 operator+(V2 a, V2 b) { const float2 r = __fadd2_rn(f2(a), f2(b)); return v2(r.x, r.y); }
+MTB_DEV V2 operator-(V2 a, V2 b) { const float2 r = __ffma2_rn(f2(b), make_float2(-1.f, -1.f), f2(a)); return v2(r.x, r.y); }
+MTB_DEV V2 operator*(float s, V2 a) { const float2 r = __fmul2_rn(make_float2(s, s), f2(a)); return v2(r.x, r.y); }
+MTB_DEV void axpy(V2& y, float a, V2 x) { const float2 r = __ffma2_rn(make_float2(a, a), f2(x), f2(y)); y = v2(r.x, r.y); }
+#else
 MTB_DEV V2 operator+(V2 a, V2 b) { return v2(a.x + b.x, a.y + b.y); }
 MTB_DEV V2 operator-(V2 a, V2 b) { return v2(a.x - b.x, a.y - b.y); }
 MTB_DEV V2 operator*(float s, V2 a) { return v2(s * a.x, s * a.y); }
-MTB_DEV float dot(V2 a, V2 b) { return a.x * b.x + a.y * b.y; }
 MTB_DEV void axpy(V2& y, float a, V2 x) { y.x = fmaf(a, x.x, y.x); y.y = fmaf(a, x.y, y.y); }
+#endif
+MTB_DEV float dot(V2 a, V2 b) { return a.x * b.x + a.y * b.y; }
 MTB_DEV bool is_nan(float x) { return x != x; }
 
 // ---------------------------------------------------------------------------------------------------------
