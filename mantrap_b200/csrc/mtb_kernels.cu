@@ -29,7 +29,7 @@ struct KParams {
     int has_ego, want_grad, want_env_adjoint, use_tape;
     float pair_cut2;                 // the float after the largest d^2 with sqrtf(d^2) <= interaction radius (strict <)
     // shared-memory layout (float units, per evaluation) -------------------------------------------------
-    int off_ctl, off_ego, off_egobar, off_mus, off_pos, off_q, off_misc, off_tape, off_mask;
+    int off_ctl, off_ego, off_egobar, off_mus, off_pos, off_dir, off_q, off_misc, off_tape, off_mask;
     int NP4;                         // N rounded up to 4: length of the SoA position rows used by the radius test
     int per_eval_f, red_f;
     int tape_in_smem;
@@ -213,6 +213,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     // [T][N] adjoints of the means in an L2-resident scratch: seeded by the objectives, pair terms add with red.global
     float4* abar = prm.abar_global + ((size_t)blockIdx.x * prm.E + e) * (size_t)(T * N);
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);     // [GP]
+    float2* accdir = reinterpret_cast<float2*>(sm + prm.off_dir); // [T-1][N] unit directions of the acceleration differences (GRAD)
     float* misc = sm + prm.off_misc;
 
     // Backward tape, addressed per thread: row t of this particle is tape[t * tape_stride] = (p.x, p.y, u.x, u.y) before its
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     }
     const int mask_stride = tape_stride * MW;
 
-    unsigned long long n_pairs = 0, n_ego = 0;
+    unsigned n_pairs = 0, n_ego = 0;   // per thread (a thread executes < 2^32 pair terms per launch)
 
     // Work distribution: a "unit" is the set of threads that must run in lock step -- one warp holding 32/GP
     // sub-warp groups, or one group of GP >= 32 threads. Units loop over work items independently of each other;
@@ -421,7 +422,10 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
         if (want_interact) {
             for (int idx = g; idx < N * T; idx += GP) {
                 const int k = idx / T, t = idx - k * T;
-                if (amask != nullptr && amask[k] == 0) continue;
+                if (amask != nullptr && amask[k] == 0) {
+                    if (GRAD && t < T - 1) accdir[t * N + k] = make_float2(0.f, 0.f);
+                    continue;
+                }
                 const float4 cur = mus[t * N + k];
                 const float4 wcur = ld4(wo_scene + (k * T + t) * 4);
                 if (prm.md.w_acc != 0.f && t < T - 1) {
@@ -429,7 +433,9 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                     const float4 wnxt = ld4(wo_scene + (k * T + t + 1) * 4);
                     const float ax = (nxt.z - cur.z) / dt - (wnxt.z - wcur.z) / dt;
                     const float ay = (nxt.w - cur.w) / dt - (wnxt.w - wcur.w) / dt;
-                    part.b += sqrtf(ax * ax + ay * ay);
+                    const float nn = sqrtf(ax * ax + ay * ay);
+                    part.b += nn;
+                    if (GRAD) accdir[t * N + k] = (nn > 0.f) ? make_float2(ax / nn, ay / nn) : make_float2(0.f, 0.f);   // norm'(0) = 0
                 }
                 if (prm.md.w_vel != 0.f) {
                     const float dx = cur.z - wcur.z, dy = cur.w - wcur.w;
@@ -488,8 +494,11 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
         }
 
         if (g == 0) {
-            int K = 0;
-            for (int k = 0; k < N; ++k) K += (amask == nullptr || amask[k] != 0) ? 1 : 0;
+            int K = N;
+            if (amask != nullptr) {
+                K = 0;
+                for (int k = 0; k < N; ++k) K += (amask[k] != 0) ? 1 : 0;
+            }
             const float invK = (K > 0) ? 1.0f / (float)K : 0.f;
             const float raw_goal = part.a / (float)(2 * (T + 1));
             const float raw_acc = (T > 1) ? part.b * invK / (float)(T - 1) : 0.f;
@@ -560,10 +569,22 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             // Seed the adjoints of the means with the objective derivatives (and the caller's seeds), once per (ado, level):
             // abar[level][k] = d(objectives)/d(mus[k, level]); the pair terms of the sweep below accumulate on top.
             if (env_adjoint) {
-                for (int idx = g; idx < (T - 1) * N; idx += GP) {
-                    const int lv = idx / N, k = idx - lv * N;
-                    const bool k_in_cost = amask == nullptr || amask[k] != 0;
-                    mtb_stcg_f4(abar + (lv + 1) * N + k, objective_seed(prm, misc, mus, wo_scene, seed_mus_ev, k, lv + 1, k_in_cost));
+                const bool acc_only = seed_mus_ev == nullptr && misc[kCoefVel] == 0.f && misc[kCoefPos] == 0.f &&
+                                      wo_scene != nullptr && prm.md.w_acc != 0.f;
+                if (acc_only) {       // d/d mu_v[k, lv] of c * sum_t |a_t - a_t^wo|: c (dir[lv-1] - dir[lv]), directions kept by the epilogue
+                    const float cacc = misc[kCoefAcc];            // includes the 1/dt of a = diff(mu_v) / dt
+                    for (int idx = g; idx < (T - 1) * N; idx += GP) {
+                        const float2 dp = accdir[idx];
+                        float2 dn = make_float2(0.f, 0.f);
+                        if (idx + N < (T - 1) * N) dn = accdir[idx + N];
+                        mtb_stcg_f4(abar + N + idx, make_float4(0.f, 0.f, cacc * (dp.x - dn.x), cacc * (dp.y - dn.y)));
+                    }
+                } else {
+                    for (int idx = g; idx < (T - 1) * N; idx += GP) {
+                        const int lv = idx / N, k = idx - lv * N;
+                        const bool k_in_cost = amask == nullptr || amask[k] != 0;
+                        mtb_stcg_f4(abar + (lv + 1) * N + k, objective_seed(prm, misc, mus, wo_scene, seed_mus_ev, k, lv + 1, k_in_cost));
+                    }
                 }
             }
             float4 tape_next = make_float4(0.f, 0.f, 0.f, 0.f);   // tape row t, carried from the previous iteration's look-back
@@ -655,7 +676,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                     float* ebt = reinterpret_cast<float*>(egobar + (GP <= 32 ? 0 : (g >> 5) * (T + 1)) + t);
                     if (W >= 4) {
                         const float r = transpose_reduce4(eb_p.x, eb_p.y, eb_v.x, eb_v.y, W);
-                        if ((l & ((W >> 2) - 1)) == 0) ebt[l / (W >> 2)] = r;
+                        if ((l & ((W >> 2) - 1)) == 0) ebt[((l & (W >> 1)) ? 2 : 0) + ((l & (W >> 2)) ? 1 : 0)] = r;
                     } else {
                         for (int off = W >> 1; off > 0; off >>= 1) {
                             eb_p.x += __shfl_xor_sync(0xffffffffu, eb_p.x, off);
@@ -670,8 +691,51 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             group_sync(GP, e);
 
             // ------------------------------------------------ fold ego adjoints through the ego dynamics
-            if (has_ego && g == 0) {
-                const float cg = prm.md.w_goal / (float)(T + 1);  // d/dp_t of w * mean((p - g)^2) = w (p_t - g) / (T+1)
+            // The serial recurrence (t = T..1) of the double integrator is  A_t = sum_{s>t} pbar_s,  V_t = sum_{s>=t} (vbar_s + dt A_s),
+            // grad u_{t-1} = dt V_t  (single integrator: grad u_{t-1} = vbar_t + dt sum_{s>=t} pbar_s): suffix sums, done by shuffle
+            // scans over the first W lanes of the group when the horizon fits (lane l owns t = l + 1), else by one thread.
+            const int FW = GP < 32 ? GP : 32;
+            const float cg_fold = prm.md.w_goal / (float)(T + 1);   // d/dp_t of w * mean((p - g)^2) = w (p_t - g) / (T+1)
+            if (has_ego && T <= FW && g < FW) {
+                float gx = 0.f, gy = 0.f;
+                if (prm.md.w_goal != 0.f) { gx = __ldg(prm.md.ego_goal + (size_t)s * 2); gy = __ldg(prm.md.ego_goal + (size_t)s * 2 + 1); }
+                const int l = g;
+                float4 eb = make_float4(0.f, 0.f, 0.f, 0.f);
+                float bx = 0.f, by = 0.f;
+                if (l < T) {
+                    eb = egobar[l + 1];
+                    for (int w = 1; w < prm.NW; ++w) {
+                        const float4 o = egobar[w * (T + 1) + l + 1];
+                        eb.x += o.x; eb.y += o.y; eb.z += o.z; eb.w += o.w;
+                    }
+                    const float4 x = ego[l + 1];
+                    bx = cg_fold * (x.x - gx); by = cg_fold * (x.y - gy);
+                }
+                float sx = eb.x, sy = eb.y, sbx = bx, sby = by;   // inclusive suffix sums over the group's lanes
+                for (int off = 1; off < FW; off <<= 1) {
+                    const float o0 = __shfl_down_sync(0xffffffffu, sx, off), o1 = __shfl_down_sync(0xffffffffu, sy, off);
+                    const float o2 = __shfl_down_sync(0xffffffffu, sbx, off), o3 = __shfl_down_sync(0xffffffffu, sby, off);
+                    if (l + off < FW) { sx += o0; sy += o1; sbx += o2; sby += o3; }
+                }
+                float outx, outy, goutx, gouty;
+                if (prm.pb.ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) {
+                    float vx = fmaf(dt, sx - eb.x, eb.z), vy = fmaf(dt, sy - eb.y, eb.w);
+                    float gvx = dt * (sbx - bx), gvy = dt * (sby - by);
+                    for (int off = 1; off < FW; off <<= 1) {
+                        const float o0 = __shfl_down_sync(0xffffffffu, vx, off), o1 = __shfl_down_sync(0xffffffffu, vy, off);
+                        const float o2 = __shfl_down_sync(0xffffffffu, gvx, off), o3 = __shfl_down_sync(0xffffffffu, gvy, off);
+                        if (l + off < FW) { vx += o0; vy += o1; gvx += o2; gvy += o3; }
+                    }
+                    outx = dt * vx; outy = dt * vy; goutx = dt * gvx; gouty = dt * gvy;
+                } else {
+                    outx = fmaf(dt, sx, eb.z); outy = fmaf(dt, sy, eb.w); goutx = dt * sbx; gouty = dt * sby;
+                }
+                if (l < T) {
+                    ctl[2 * l + 0] = sanitize(outx) + goutx;
+                    ctl[2 * l + 1] = sanitize(outy) + gouty;
+                }
+            } else if (has_ego && T > FW && g == 0) {
+                const float cg = cg_fold;
                 float gx = 0.f, gy = 0.f;
                 if (prm.md.w_goal != 0.f) { gx = __ldg(prm.md.ego_goal + (size_t)s * 2); gy = __ldg(prm.md.ego_goal + (size_t)s * 2 + 1); }
                 float apx = 0.f, apy = 0.f, avx = 0.f, avy = 0.f;     // environment part
@@ -726,8 +790,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     }
 
     if (prm.out.stats != nullptr) {
-        atomicAdd(prm.out.stats + 0, n_pairs);
-        atomicAdd(prm.out.stats + 1, n_ego);
+        atomicAdd(prm.out.stats + 0, (unsigned long long)n_pairs);
+        atomicAdd(prm.out.stats + 1, (unsigned long long)n_ego);
     }
 }
 
@@ -826,6 +890,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         prm.off_egobar = off; off += want_grad ? prm.NW * (prm.T + 1) * 4 : 0;
         prm.off_mus = off;    off += prm.T * prm.N * 4;
         prm.off_pos = off;    off += 2 * prm.NP4;
+        prm.off_dir = off;    off += want_grad ? round_up((prm.T - 1) * prm.N * 2, 4) : 0;
         prm.off_q = off;      off += round_up(prm.GP * 2, 4);
         prm.off_misc = off;   off += kMiscFloats;
         prm.off_tape = off;   off += (need_tape && tape_in_smem) ? (prm.T - 1) * prm.GP * 4 : 0;

@@ -46,6 +46,8 @@ def test_constraints(emul_lib, name):
     ("sf", "single", 2, 3, 12, 3, 5, {"goal": 0.5, "vel": 1.0, "pos": 1.0}),  # two warps per evaluation
     ("pf", "double", 2, 4, 5, 5, 7, {"goal": 0.5, "acc": 1.0, "vel": 1.0}),
     ("kalman", "double", 2, 3, 5, 1, 6, {"goal": 0.5, "acc": 1.0}),
+    ("sf", "double", 2, 3, 2, 2, 9, {"goal": 0.5, "acc": 1.0}),            # groups of 4 lanes, horizon > group: serial fold
+    ("sf", "single", 1, 5, 1, 2, 5, {"goal": 0.5, "acc": 1.0, "vel": 1.0}),  # groups of 2 lanes, one ado (no pair terms)
 ])
 def test_batched_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor, weights):
     kc.check_batched_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights)
