@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define MTB_ABI_VERSION 2
+#define MTB_ABI_VERSION 3
 
 /* environment kinds: mantrap/environment/social_forces.py, simplified/potential_field.py, simplified/kalman.py */
 #define MTB_ENV_SOCIAL_FORCES 0
@@ -40,6 +40,9 @@ extern "C" {
 #define MTB_EGO_DOUBLE_INTEGRATOR 0
 #define MTB_EGO_SINGLE_INTEGRATOR 1
 #define MTB_EGO_NONE 2
+
+/* objective columns of mtb_outputs.obj / obj_raw: goal, acc, vel, pos, prob */
+#define MTB_NUM_OBJECTIVES 5
 
 #define MTB_MAX_ADOS 64
 #define MTB_MAX_HORIZON 64
@@ -104,12 +107,17 @@ typedef struct mtb_modules {
      * graph_based.py:362-381); added to the seeds of the fused objectives. Level 0 is the current state (no gradient). */
     const float* seed_mus;
     const float* seed_sigmas;
+    /* InteractionProbabilityModule (prob_interact.py:57-86): minus the log-probability of the ego-free mean velocities
+     * (mus_wo) in the conditioned Normal(loc = mu_v, scale = variance), summed over (t, xy), averaged over the ados of
+     * the cost, clamped to [-max_prob, max_prob] (constants.py:100); w_prob = weight / max_prob (prob_interact.py:97). */
+    float w_prob;
+    float max_prob;
 } mtb_modules;
 
 /* Outputs; every pointer may be NULL (= not wanted). */
 typedef struct mtb_outputs {
-    float* obj;        /* [S,C,4] weighted+normalised goal, acc, vel, pos objectives (what module.objective returns) */
-    float* obj_raw;    /* [S,C,4] raw, un-clamped costs */
+    float* obj;        /* [S,C,MTB_NUM_OBJECTIVES] weighted+normalised goal, acc, vel, pos, prob objectives (what module.objective returns) */
+    float* obj_raw;    /* [S,C,MTB_NUM_OBJECTIVES] raw, un-clamped costs */
     float* total;      /* [S,C] sum of obj */
     float* grad;       /* [S,C,T,2] gradient of total (+ seeded loss) w.r.t. controls */
     float* grad_traj;  /* [S,C,T+1,4] the same gradient w.r.t. the ego trajectory rows (px,py,vx,vy), before it is

@@ -12,7 +12,7 @@ import torch
 ENV_SOCIAL_FORCES, ENV_POTENTIAL_FIELD, ENV_KALMAN = 0, 1, 2
 EGO_DOUBLE_INTEGRATOR, EGO_SINGLE_INTEGRATOR, EGO_NONE = 0, 1, 2
 MAX_ADOS, MAX_HORIZON = 64, 64
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 _f, _i, _p = ctypes.c_float, ctypes.c_int32, ctypes.c_void_p
 
@@ -33,7 +33,7 @@ class MtbModules(ctypes.Structure):
                 ("ego_goal", _p), ("mus_wo", _p), ("ado_mask", _p),
                 ("con_control", _i), ("con_speed", _i), ("con_min_distance", _i),
                 ("u_max", _f), ("v_max", _f), ("min_distance", _f), ("violation_eps", _f),
-                ("seed_mus", _p), ("seed_sigmas", _p)]
+                ("seed_mus", _p), ("seed_sigmas", _p), ("w_prob", _f), ("max_prob", _f)]
 
 
 class MtbOutputs(ctypes.Structure):

@@ -29,7 +29,8 @@ struct KParams {
     int has_ego, want_grad, want_env_adjoint, use_tape;
     float pair_cut2;                 // the float after the largest d^2 with sqrtf(d^2) <= interaction radius (strict <)
     // shared-memory layout (float units, per evaluation) -------------------------------------------------
-    int off_ctl, off_ego, off_egobar, off_mus, off_pos, off_dir, off_q, off_misc, off_tape, off_mask;
+    int off_ctl, off_ego, off_egobar, off_mus, off_pos, off_dir, off_var, off_q, off_misc, off_tape, off_mask;
+    int keep_var;                    // variances [T][N] kept in shared memory (InteractionProbabilityModule)
     int NP4;                         // N rounded up to 4: length of the SoA position rows used by the radius test
     int per_eval_f, red_f;
     int tape_in_smem;
@@ -41,7 +42,7 @@ struct KParams {
 };
 
 // misc slots (per evaluation)
-enum { kCoefAcc = 0, kCoefVel = 1, kCoefPos = 2, kNeedAdjoint = 3, kMiscFloats = 8 };
+enum { kCoefAcc = 0, kCoefVel = 1, kCoefPos = 2, kNeedAdjoint = 3, kCoefProb = 4, kMiscFloats = 8 };
 
 struct Red4 {
     float a, b, c, d;
@@ -146,8 +147,8 @@ MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py
 MTB_DEV float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 
 // Adjoint seed of the interaction objectives on mus[k, level] (level >= 1): (d/d mu_p, d/d mu_v).
-MTB_DEV float4 objective_seed(const KParams& prm, const float* misc, const float4* mus, const float* wo_scene,
-                              const float* seed_mus_ev, int k, int level, bool in_cost) {
+MTB_DEV float4 objective_seed(const KParams& prm, const float* misc, const float4* mus, const float2* varbuf,
+                              const float* wo_scene, const float* seed_mus_ev, int k, int level, bool in_cost) {
     float4 sd = make_float4(0.f, 0.f, 0.f, 0.f);
     if (seed_mus_ev != nullptr) sd = ld4(seed_mus_ev + (k * prm.T + level) * 4);   // caller's d(loss)/d(mus[k, level])
     if (!in_cost || wo_scene == nullptr) return sd;
@@ -179,6 +180,12 @@ MTB_DEV float4 objective_seed(const KParams& prm, const float* misc, const float
     if (cpos != 0.f) {   // positions vs. ego-free VELOCITIES (pos_interact.py:34-36), |.| per component
         sd.x += cpos * sgn(cur.x - wcur.z);
         sd.y += cpos * sgn(cur.y - wcur.w);
+    }
+    const float cprob = misc[kCoefProb];
+    if (cprob != 0.f) {  // log N(x; mu, s) with x = ego-free mean, s = variance used as scale: d/d mu = (x - mu) / s^2
+        const float2 sv = varbuf[level * N + k];
+        sd.z += cprob * (wcur.z - cur.z) / (sv.x * sv.x);
+        sd.w += cprob * (wcur.w - cur.w) / (sv.y * sv.y);
     }
     return sd;
 }
@@ -214,6 +221,10 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     float4* abar = prm.abar_global + ((size_t)blockIdx.x * prm.E + e) * (size_t)(T * N);
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);     // [GP]
     float2* accdir = reinterpret_cast<float2*>(sm + prm.off_dir); // [T-1][N] unit directions of the acceleration differences (GRAD)
+    // [T][N] variances of the weighted particle velocities (probability objective); the backward pass re-uses the rows as
+    // the adjoint seeds of the variances
+    float2* varbuf = reinterpret_cast<float2*>(sm + prm.off_var);
+    const bool keep_var = prm.keep_var != 0;
     float* misc = sm + prm.off_misc;
 
     // Backward tape, addressed per thread: row t of this particle is tape[t * tape_stride] = (p.x, p.y, u.x, u.y) before its
@@ -319,6 +330,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             sig_out[(m * T) * 2 + 0] = prm.pb.var_initial;
             sig_out[(m * T) * 2 + 1] = prm.pb.var_initial;
         }
+        if (keep_var && active && i == 0) varbuf[m] = make_float2(prm.pb.var_initial, prm.pb.var_initial);
         group_sync(GP, e);
 
         // ================================================================== forward rollout
@@ -388,7 +400,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                 mus[(t + 1) * N + m] = make_float4(npx, npy, mx, my);
                 posx[m] = npx;
                 posy[m] = npy;
-                if (sig_out != nullptr) {
+                if (sig_out != nullptr || keep_var) {
                     float vx = prm.pb.kalman_noise, vy = prm.pb.kalman_noise;
                     if (ENV != MTB_ENV_KALMAN) {
                         vx = 0.f; vy = 0.f;
@@ -400,8 +412,11 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                         vx /= (float)(P - 1);
                         vy /= (float)(P - 1);
                     }
-                    sig_out[(m * T + t + 1) * 2 + 0] = vx;
-                    sig_out[(m * T + t + 1) * 2 + 1] = vy;
+                    if (sig_out != nullptr) {
+                        sig_out[(m * T + t + 1) * 2 + 0] = vx;
+                        sig_out[(m * T + t + 1) * 2 + 1] = vy;
+                    }
+                    if (keep_var) varbuf[(t + 1) * N + m] = make_float2(vx, vy);
                 }
             }
             group_sync(GP, e);
@@ -445,6 +460,24 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             }
         }
         part = group_reduce4(part, GP, e, red);
+        // InteractionProbabilityModule (prob_interact.py:57-86): log-probability of the ego-free mean velocities in the
+        // conditioned Normal(loc = mu_v, scale = variance), summed over (t, xy), averaged over the ados of the cost
+        const bool want_prob = wo_scene != nullptr && keep_var && prm.md.w_prob != 0.f;
+        float lp_sum = 0.f;
+        if (want_prob) {
+            Red4 pr = {0.f, 0.f, 0.f, 0.f};
+            for (int idx = g; idx < N * T; idx += GP) {
+                const int k = idx / T, t = idx - k * T;
+                if (amask != nullptr && amask[k] == 0) continue;
+                const float4 cur = mus[t * N + k];
+                const float4 wcur = ld4(wo_scene + (k * T + t) * 4);
+                const float2 sv = varbuf[t * N + k];
+                const float zx = (wcur.z - cur.z) / sv.x, zy = (wcur.w - cur.w) / sv.y;
+                pr.a += (-0.5f * zx * zx - logf(sv.x) - 0.9189385332046727f) + (-0.5f * zy * zy - logf(sv.y) - 0.9189385332046727f);
+            }
+            pr = group_reduce4(pr, GP, e, red);
+            lp_sum = pr.a;
+        }
 
         // constraint rows + violation (optimization_module.py:512-533)
         Red4 vio = {0.f, 0.f, 0.f, 0.f};
@@ -508,6 +541,10 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             const float o_acc = prm.md.w_acc * fminf(raw_acc, prm.md.max_acc);
             const float o_vel = prm.md.w_vel * fminf(raw_vel, prm.md.max_vel);
             const float o_pos = prm.md.w_pos * fminf(raw_pos, prm.md.max_pos);
+            const float raw_prob = want_prob ? -lp_sum * invK : 0.f;
+            const float o_prob = want_prob ? prm.md.w_prob * fminf(fmaxf(raw_prob, -prm.md.max_prob), prm.md.max_prob) : 0.f;
+            // clamp(-max, max) passes the gradient on the closed interval; d(o_prob)/d(lp_sum) = -w / K
+            const float cprob = (want_prob && raw_prob >= -prm.md.max_prob && raw_prob <= prm.md.max_prob) ? -prm.md.w_prob * invK : 0.f;
             // clamp_max passes the gradient on raw <= max (torch), saturated objectives have zero gradient
             const float cacc = (want_interact && raw_acc <= prm.md.max_acc && T > 1) ? prm.md.w_acc * invK / ((float)(T - 1) * dt) : 0.f;
             const float cvel = (want_interact && raw_vel <= prm.md.max_vel) ? prm.md.w_vel * invK / (float)T : 0.f;
@@ -515,17 +552,18 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             misc[kCoefAcc] = cacc;
             misc[kCoefVel] = cvel;
             misc[kCoefPos] = cpos;
-            misc[kNeedAdjoint] = (cacc != 0.f || cvel != 0.f || cpos != 0.f) ? 1.f : 0.f;
+            misc[kCoefProb] = cprob;
+            misc[kNeedAdjoint] = (cacc != 0.f || cvel != 0.f || cpos != 0.f || cprob != 0.f) ? 1.f : 0.f;
             if (eval_valid) {
                 if (prm.out.obj != nullptr) {
-                    float* o = prm.out.obj + ev * 4;
-                    o[0] = o_goal; o[1] = o_acc; o[2] = o_vel; o[3] = o_pos;
+                    float* o = prm.out.obj + ev * MTB_NUM_OBJECTIVES;
+                    o[0] = o_goal; o[1] = o_acc; o[2] = o_vel; o[3] = o_pos; o[4] = o_prob;
                 }
                 if (prm.out.obj_raw != nullptr) {
-                    float* o = prm.out.obj_raw + ev * 4;
-                    o[0] = raw_goal; o[1] = raw_acc; o[2] = raw_vel; o[3] = raw_pos;
+                    float* o = prm.out.obj_raw + ev * MTB_NUM_OBJECTIVES;
+                    o[0] = raw_goal; o[1] = raw_acc; o[2] = raw_vel; o[3] = raw_pos; o[4] = raw_prob;
                 }
-                if (prm.out.total != nullptr) prm.out.total[ev] = ((o_goal + o_acc) + o_vel) + o_pos;
+                if (prm.out.total != nullptr) prm.out.total[ev] = (((o_goal + o_acc) + o_vel) + o_pos) + o_prob;
                 if (prm.out.violation != nullptr) {
                     const float eps = prm.md.violation_eps;
                     const float va = (fabsf(vio.a) < eps) ? 0.f : vio.a;
@@ -533,8 +571,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                     const float vc = (fabsf(vio.c) < eps) ? 0.f : vio.c;
                     prm.out.violation[ev] = (va + vb) + vc;
                 }
-                if (prm.out.stats != nullptr && want_interact &&
-                    (raw_acc > prm.md.max_acc || raw_vel > prm.md.max_vel || raw_pos > prm.md.max_pos))
+                if (prm.out.stats != nullptr && ((want_interact &&
+                    (raw_acc > prm.md.max_acc || raw_vel > prm.md.max_vel || raw_pos > prm.md.max_pos)) || (want_prob && cprob == 0.f)))
                     atomicAdd(prm.out.stats + 2, 1ull);
             }
         }
@@ -559,6 +597,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             // shuffles below are executed by every lane.
             const float* seed_mus_ev = (prm.md.seed_mus != nullptr) ? prm.md.seed_mus + ev * (size_t)N * T * 4 : nullptr;
             const float* seed_sig_ev = (prm.md.seed_sigmas != nullptr) ? prm.md.seed_sigmas + ev * (size_t)N * T * 2 : nullptr;
+            const bool prob_seed = keep_var && misc[kCoefProb] != 0.f;
             const bool env_adjoint = prm.want_env_adjoint != 0 &&
                                      (misc[kNeedAdjoint] != 0.f || seed_mus_ev != nullptr || seed_sig_ev != nullptr);
             bool any_adjoint = env_adjoint;
@@ -570,7 +609,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             // abar[level][k] = d(objectives)/d(mus[k, level]); the pair terms of the sweep below accumulate on top.
             if (env_adjoint) {
                 const bool acc_only = seed_mus_ev == nullptr && misc[kCoefVel] == 0.f && misc[kCoefPos] == 0.f &&
-                                      wo_scene != nullptr && prm.md.w_acc != 0.f;
+                                      misc[kCoefProb] == 0.f && wo_scene != nullptr && prm.md.w_acc != 0.f;
                 if (acc_only) {       // d/d mu_v[k, lv] of c * sum_t |a_t - a_t^wo|: c (dir[lv-1] - dir[lv]), directions kept by the epilogue
                     const float cacc = misc[kCoefAcc];            // includes the 1/dt of a = diff(mu_v) / dt
                     for (int idx = g; idx < (T - 1) * N; idx += GP) {
@@ -583,7 +622,19 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                     for (int idx = g; idx < (T - 1) * N; idx += GP) {
                         const int lv = idx / N, k = idx - lv * N;
                         const bool k_in_cost = amask == nullptr || amask[k] != 0;
-                        mtb_stcg_f4(abar + (lv + 1) * N + k, objective_seed(prm, misc, mus, wo_scene, seed_mus_ev, k, lv + 1, k_in_cost));
+                        mtb_stcg_f4(abar + (lv + 1) * N + k, objective_seed(prm, misc, mus, varbuf, wo_scene, seed_mus_ev, k, lv + 1, k_in_cost));
+                        if (prob_seed) {      // d log N / d s = (x - mu)^2 / s^3 - 1 / s; the variance row becomes its own adjoint seed
+                            float2 sb = make_float2(0.f, 0.f);
+                            if (k_in_cost) {
+                                const float4 cur = mus[(lv + 1) * N + k];
+                                const float4 wcur = ld4(wo_scene + (k * T + lv + 1) * 4);
+                                const float2 sv = varbuf[(lv + 1) * N + k];
+                                const float ex = wcur.z - cur.z, ey = wcur.w - cur.w;
+                                sb.x = misc[kCoefProb] * (ex * ex / (sv.x * sv.x * sv.x) - 1.0f / sv.x);
+                                sb.y = misc[kCoefProb] * (ey * ey / (sv.y * sv.y * sv.y) - 1.0f / sv.y);
+                            }
+                            varbuf[(lv + 1) * N + k] = sb;
+                        }
                     }
                 }
             }
@@ -607,7 +658,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                         tape_next = tape[(t - 1) * tape_stride];
                         vt = feasible(v2(tape_next.z, tape_next.w), u_ped);
                     }
-                    if (seed_sig_ev != nullptr) {
+                    if (seed_sig_ev != nullptr || prob_seed) {
                         // var[m,t+1] = sum_i (q_i - mean q)^2 / (P-1), q_i = w_i (v'_i + noise): d var / d v'_i =
                         // 2 w_i (q_i - mean) / (P-1)   (particle.py:175; the mean term cancels)
                         V2 vel = feasible(ut, u_ped);
@@ -618,7 +669,9 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                         }
                         const float4 mean = mus[(t + 1) * N + m];
                         const float c2 = 2.0f * pw / (float)(P - 1);
-                        const float sbx = __ldg(seed_sig_ev + (m * T + t + 1) * 2), sby = __ldg(seed_sig_ev + (m * T + t + 1) * 2 + 1);
+                        float sbx = 0.f, sby = 0.f;
+                        if (seed_sig_ev != nullptr) { sbx = __ldg(seed_sig_ev + (m * T + t + 1) * 2); sby = __ldg(seed_sig_ev + (m * T + t + 1) * 2 + 1); }
+                        if (prob_seed) { const float2 sb = varbuf[(t + 1) * N + m]; sbx += sb.x; sby += sb.y; }
                         vbar.x = fmaf(c2 * (vel.x * pw - mean.z), sbx, vbar.x);
                         vbar.y = fmaf(c2 * (vel.y * pw - mean.w), sby, vbar.y);
                     }
@@ -860,6 +913,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     prm.G = prm.N * prm.P;
     prm.MW = (prm.N + 31) / 32;
     prm.NP4 = round_up(prm.N, 4);
+    prm.keep_var = (md != nullptr && md->w_prob != 0.f && md->mus_wo != nullptr) ? 1 : 0;
     prm.has_ego = pb->ego_kind != MTB_EGO_NONE;
     prm.want_grad = want_grad ? 1 : 0;
     prm.pair_cut2 = nextafterf(pair_cut_squared(pb->sf_interaction_radius), INFINITY);   // d^2 < pair_cut2  <=>  norm <= radius
@@ -891,6 +945,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         prm.off_mus = off;    off += prm.T * prm.N * 4;
         prm.off_pos = off;    off += 2 * prm.NP4;
         prm.off_dir = off;    off += want_grad ? round_up((prm.T - 1) * prm.N * 2, 4) : 0;
+        prm.off_var = off;    off += prm.keep_var ? round_up(prm.T * prm.N * 2, 4) : 0;
         prm.off_q = off;      off += round_up(prm.GP * 2, 4);
         prm.off_misc = off;   off += kMiscFloats;
         prm.off_tape = off;   off += (need_tape && tape_in_smem) ? (prm.T - 1) * prm.GP * 4 : 0;
@@ -941,7 +996,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     prm.num_items = (int)((prm.num_evals + evals_per_unit - 1) / evals_per_unit);
     prm.use_tape = need_tape ? 1 : 0;
     prm.want_env_adjoint = (need_tape && md != nullptr &&
-                            ((md->mus_wo != nullptr && (md->w_acc != 0.f || md->w_vel != 0.f || md->w_pos != 0.f)) ||
+                            ((md->mus_wo != nullptr && (md->w_acc != 0.f || md->w_vel != 0.f || md->w_pos != 0.f || md->w_prob != 0.f)) ||
                              md->seed_mus != nullptr || md->seed_sigmas != nullptr)) ? 1 : 0;
     const int block = E * prm.GP;
     int blocks_per_sm = (int)((size_t)lim.smem_per_sm / (smem + 1024));
@@ -1050,7 +1105,7 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
     const int err = mtb::plan(problem, modules, out, want_grad, prm, info, ws);
     if (err != 0) return err;
     if (want_grad && problem->ego_kind == MTB_EGO_NONE) return MTB_ERR_BAD_ARGUMENT;
-    if (modules != nullptr && (modules->w_acc != 0.f || modules->w_vel != 0.f || modules->w_pos != 0.f) &&
+    if (modules != nullptr && (modules->w_acc != 0.f || modules->w_vel != 0.f || modules->w_pos != 0.f || modules->w_prob != 0.f) &&
         modules->mus_wo == nullptr)
         return MTB_ERR_BAD_ARGUMENT;
     if (modules != nullptr && modules->w_goal != 0.f && modules->ego_goal == nullptr) return MTB_ERR_BAD_ARGUMENT;

@@ -17,7 +17,8 @@ from . import _cabi, constants
 
 ENV_KINDS = {"sf": _cabi.ENV_SOCIAL_FORCES, "pf": _cabi.ENV_POTENTIAL_FIELD, "kalman": _cabi.ENV_KALMAN}
 EGO_KINDS = {"double": _cabi.EGO_DOUBLE_INTEGRATOR, "single": _cabi.EGO_SINGLE_INTEGRATOR, None: _cabi.EGO_NONE}
-OBJECTIVE_KEYS = ("goal", "acc", "vel", "pos")
+OBJECTIVE_KEYS = ("goal", "acc", "vel", "pos", "prob")     # columns of `obj` / `obj_raw` (MTB_NUM_OBJECTIVES)
+NUM_OBJECTIVES = len(OBJECTIVE_KEYS)
 
 
 @dataclasses.dataclass
@@ -128,6 +129,8 @@ def _module_struct(scene: SceneBatch, spec: ModuleSpec) -> _cabi.MtbModules:
     md.max_acc = constants.OBJECTIVE_ACC_INTERACT_MAX
     md.max_vel = constants.OBJECTIVE_VEL_INTERACT_MAX
     md.max_pos = constants.OBJECTIVE_POS_INTERACT_MAX
+    md.w_prob = w.get("prob", 0.0) / constants.OBJECTIVE_PROB_INTERACT_MAX
+    md.max_prob = constants.OBJECTIVE_PROB_INTERACT_MAX
     md.ego_goal = _cabi.ptr(scene.ego_goal)
     md.mus_wo = _cabi.ptr(spec.mus_wo)
     md.ado_mask = _cabi.ptr(spec.ado_mask, dtype=torch.uint8)
@@ -142,7 +145,7 @@ def _module_struct(scene: SceneBatch, spec: ModuleSpec) -> _cabi.MtbModules:
 
 
 OUTPUT_SHAPES = {
-    "obj": lambda s, c, t, n, r: (s, c, 4), "obj_raw": lambda s, c, t, n, r: (s, c, 4),
+    "obj": lambda s, c, t, n, r: (s, c, NUM_OBJECTIVES), "obj_raw": lambda s, c, t, n, r: (s, c, NUM_OBJECTIVES),
     "total": lambda s, c, t, n, r: (s, c), "grad": lambda s, c, t, n, r: (s, c, t, 2),
     "grad_traj": lambda s, c, t, n, r: (s, c, t + 1, 4),
     "cons": lambda s, c, t, n, r: (s, c, r), "violation": lambda s, c, t, n, r: (s, c),

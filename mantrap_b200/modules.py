@@ -18,7 +18,7 @@ import numpy as np
 import torch
 
 from . import constants, runtime
-from .engine import ModuleSpec, SceneBatch
+from .engine import OBJECTIVE_KEYS, ModuleSpec, SceneBatch
 
 
 def _np(x: torch.Tensor) -> np.ndarray:
@@ -86,7 +86,7 @@ class OptimizationModule:
             value = 0.0
             if self._objective_defined(ado_ids):
                 res = self._launch(ego_trajectory, ado_ids, want=("obj",))
-                value = float(res["obj"][0, 0, ("goal", "acc", "vel", "pos").index(self.fused_key)])
+                value = float(res["obj"][0, 0, OBJECTIVE_KEYS.index(self.fused_key)])
             self._obj_current[tag] = value                  # already weight * normalize(raw) (kernel epilogue)
             return value
         objective = self.compute_objective(ego_trajectory, ado_ids=ado_ids, tag=tag)
@@ -368,6 +368,19 @@ class InteractionPositionModule(_InteractionModule):
     @property
     def name(self) -> str:
         return "interaction_pos"
+
+
+class InteractionProbabilityModule(_InteractionModule):
+    """Minus the log-probability of the ego-free mean velocities in the distribution conditioned on the ego trajectory
+    (modules/prob_interact.py:13-122): `dist.log_prob(dist_un_conditioned.mean)` summed over (t, modes, xy), averaged over
+    `ado_ids`, clamped to +-OBJECTIVE_PROB_INTERACT_MAX and divided by it. The conditioned Normal uses the VARIANCE of the
+    weighted particle velocities as its scale (particle.py:175,180); the adjoint runs through both the means and the
+    variances inside the fused kernel. This is the interaction objective of `TrajOptSolver.module_defaults()`."""
+    fused_key, max_value = "prob", constants.OBJECTIVE_PROB_INTERACT_MAX
+
+    @property
+    def name(self) -> str:
+        return "interaction_prob"
 
 
 ###########################################################################

@@ -24,7 +24,7 @@ import numpy as np
 import torch
 
 from . import constants, modules as mods, runtime
-from .engine import ModuleSpec
+from .engine import OBJECTIVE_KEYS, ModuleSpec
 
 
 class TrajOptSolver:
@@ -111,10 +111,9 @@ class TrajOptSolver:
 
     @staticmethod
     def module_defaults():
-        """The reference's defaults are goal, interaction-probability, speed limits and HJ reachability
-        (trajopt.py:336-343); the probability module is a "next" row and the HJ value grid is not shipped, so
-        the default interaction objective here is the acceleration module of BASELINE config 1."""
-        return [mods.GoalNormModule, mods.InteractionAccelerationModule, mods.SpeedLimitModule]
+        """The reference's defaults: goal, interaction-probability, speed limits and HJ reachability (trajopt.py:336-343).
+        The HJ value grid (`third_party/reachability/2D.mat`) is not shipped with the reference, so that module is absent."""
+        return [mods.GoalNormModule, mods.InteractionProbabilityModule, mods.SpeedLimitModule]
 
     @staticmethod
     def module_hard():
@@ -156,7 +155,7 @@ class TrajOptSolver:
             if one.speed_limits:
                 spec.v_max = one.v_max
         if len(ado_ids) == 0:                       # interaction objectives are undefined without ados (-> 0)
-            for key in ("acc", "vel", "pos"):
+            for key in ("acc", "vel", "pos", "prob"):
                 spec.weights.pop(key, None)
         return spec
 
@@ -184,7 +183,7 @@ class TrajOptSolver:
             res = engine.evaluate(scene, controls, spec, want=("obj", "total", "grad", "cons", "violation"))
             obj = res["obj"][0, 0].cpu().numpy()
             cons = res["cons"][0, 0].cpu().numpy()
-            out.update(obj={m.name: float(obj[("goal", "acc", "vel", "pos").index(m.fused_key)]) for m in self.modules
+            out.update(obj={m.name: float(obj[OBJECTIVE_KEYS.index(m.fused_key)]) for m in self.modules
                             if getattr(m, "fused_key", None) is not None},
                        total=float(res["total"][0, 0]), grad=res["grad"][0, 0].cpu().numpy().flatten().astype(np.float64),
                        violation=float(res["violation"][0, 0]), cons=self._split_rows(cons, ado_ids, spec))
@@ -439,28 +438,31 @@ class SLSQPSolver(TrajOptSolver):
 
 
 class SearchIntermediate(TrajOptSolver):
-    """Sampling solvers: the reference evaluates ONE candidate per Python iteration until the time budget is spent
-    (solver/base/search.py:19-81); here every iteration evaluates `num_candidates` candidates in one launch and picks the
-    best feasible one with the device argmin."""
+    """Sampling solvers. Same frame as the reference (solver/base/search.py:19-81): an inner search step is repeated until it
+    reports completion or the time budget is spent, and its candidate replaces the incumbent only if it is not worse. The
+    reference evaluates ONE candidate per Python call of `evaluate` (search.py:98-103); here an inner step evaluates a whole
+    batch of candidates in one launch (`evaluate_batch`) and reduces it on the device."""
 
     def optimize_core(self, z0: torch.Tensor, ado_ids: typing.List[str], tag: str = constants.TAG_OPTIMIZATION,
-                      max_cpu_time: float = constants.SEARCH_MAX_CPU_TIME, num_candidates: int = 4096, max_rounds: int = None,
-                      **solver_kwargs):
+                      max_cpu_time: float = constants.SEARCH_MAX_CPU_TIME, max_rounds: int = None, **solver_kwargs):
         start = time.time()
         z_fallback = np.random.uniform(*self.z_bounds)
-        z_best, obj_best, rounds = None, np.inf, 0
+        z_best, obj_best, iteration, rounds, evaluated = None, np.inf, 0, 0, 0
         while True:
-            z_cand, obj_cand = self._optimize_inner(z_best, obj_best, num_candidates, tag, ado_ids)
+            z_cand, obj_cand, iteration_cand, finished, count = self._optimize_inner(z_best, obj_best, iteration, tag, ado_ids,
+                                                                                     **solver_kwargs)
+            evaluated += count
             if obj_cand <= obj_best and z_cand is not None:
-                z_best, obj_best = z_cand, obj_cand
+                z_best, obj_best, iteration = z_cand, obj_cand, iteration_cand
             rounds += 1
-            if (max_rounds is not None and rounds >= max_rounds) or time.time() - start > max_cpu_time:
+            if finished or (max_rounds is not None and rounds >= max_rounds) or time.time() - start > max_cpu_time:
                 break
         z_best = z_fallback if z_best is None else z_best
-        self._log = {"rounds": rounds, "candidates": rounds * num_candidates, "objective": obj_best}
+        self._log = {"rounds": rounds, "candidates": evaluated, "objective": obj_best, "iteration": iteration}
         return torch.from_numpy(np.asarray(z_best, dtype=np.float32)).view(-1, 2), self._log
 
-    def _optimize_inner(self, z_best, obj_best, num_candidates, tag, ado_ids):
+    def _optimize_inner(self, z_best, obj_best, iteration, tag, ado_ids, **kwargs):
+        """-> (candidate z or None, its objective, the search's iteration counter, finished?, candidates evaluated)"""
         raise NotImplementedError
 
     def evaluate_batch(self, z: np.ndarray, ado_ids: typing.List[str]):
@@ -487,22 +489,67 @@ class SearchIntermediate(TrajOptSolver):
 class RandomSearch(SearchIntermediate):
     """Uniform candidates within the control bounds, keep the best feasible (baselines/random_search.py:12-35)."""
 
-    def _optimize_inner(self, z_best, obj_best, num_candidates, tag, ado_ids):
+    def _optimize_inner(self, z_best, obj_best, iteration, tag, ado_ids, num_candidates: int = 4096, **unused):
         lb, ub = self.z_bounds
         z = np.random.uniform(lb, ub, size=(num_candidates, lb.size))
         total, violation, controls = self.evaluate_batch(z, ado_ids)
         idx, val, best = runtime.default_engine().argmin(total, violation, controls, constants.SOLVER_CONSTRAINT_LIMIT)
         if int(idx[0]) < 0:
-            return None, np.inf
-        return best[0].flatten().cpu().numpy().astype(np.float64), float(val[0])
+            return None, np.inf, iteration, False, num_candidates
+        return best[0].flatten().cpu().numpy().astype(np.float64), float(val[0]), iteration, False, num_candidates
 
     @property
     def name(self) -> str:
         return "random_search"
 
 
+class MonteCarloTreeSearch(SearchIntermediate):
+    """Monte-Carlo tree search over the control sequence (baselines/mcts.py:12-98). Search step i fixes the controls of the
+    steps before i to the incumbent, samples `num_breadth_samples` values for the control of step i ("priors") and, for each
+    prior, `num_depth_samples` random completions of the remaining steps. The value of a prior is the mean objective of its
+    FEASIBLE completions (violation < CONSTRAINT_VIOLATION_PRECISION, mcts.py:56); the best completion of the best prior is
+    returned and the search moves on to step i + 1, finishing after the last step.
+
+    The reference evaluates the breadth x depth completions one by one (2 x 2 by default, constants.py:87-88, because each
+    costs a Python rollout); here they are ONE launch, so the defaults are 64 x 64."""
+
+    def _optimize_inner(self, z_best, obj_best, iteration, tag, ado_ids, num_breadth_samples: int = 64,
+                        num_depth_samples: int = 64, **unused):
+        lb, ub = self.z_bounds
+        t_hor, nb, nd = self.planning_horizon, num_breadth_samples, num_depth_samples
+        assert len(lb) == len(ub) == 2 * t_hor and 0 <= iteration <= t_hor
+        if iteration >= t_hor:                      # the whole horizon has been searched
+            return z_best, obj_best, iteration, True, 0
+        z = np.empty((nb, nd, 2 * t_hor))
+        if iteration > 0:                           # controls before step i: the incumbent (mcts.py:46-49)
+            assert z_best is not None and len(z_best) == 2 * t_hor
+            z[:, :, :2 * iteration] = np.asarray(z_best)[:2 * iteration]
+        lo_i, hi_i = lb[2 * iteration:2 * iteration + 2], ub[2 * iteration:2 * iteration + 2]
+        z[:, :, 2 * iteration:2 * iteration + 2] = np.random.uniform(lo_i, hi_i, size=(nb, 1, 2))   # one value per prior
+        rest = 2 * (iteration + 1)
+        if rest < 2 * t_hor:
+            z[:, :, rest:] = np.random.uniform(lb[rest:], ub[rest:], size=(nb, nd, 2 * t_hor - rest))
+        total, violation, _ = self.evaluate_batch(z.reshape(nb * nd, 2 * t_hor), ado_ids)
+        total, violation = total.view(nb, nd), violation.view(nb, nd)
+        feasible = (violation < constants.CONSTRAINT_VIOLATION_PRECISION) & ~torch.isnan(total)
+        inf = torch.full_like(total, float("inf"))
+        count = feasible.sum(dim=1)
+        mean = torch.where(count > 0, torch.where(feasible, total, torch.zeros_like(total)).sum(dim=1) / count.clamp(min=1),
+                           inf[:, 0])                # np.mean of the feasible values, inf without any (mcts.py:68)
+        best_val, best_idx = torch.where(feasible, total, inf).min(dim=1)
+        prior = int(torch.argmin(mean))              # mcts.py:75
+        should_terminate = iteration + 1 == t_hor
+        if int(count[prior]) == 0:                   # no feasible completion: keep the incumbent (mcts.py:80-81)
+            return z_best, obj_best, iteration, should_terminate, nb * nd
+        return z[prior, int(best_idx[prior])].copy(), float(best_val[prior]), iteration + 1, should_terminate, nb * nd
+
+    @property
+    def name(self) -> str:
+        return "mcts"
+
+
 # `mantrap.solver.baselines.*` of the reference (solver/baselines/__init__.py:1-4)
 import types as _types  # noqa: E402
 
-baselines = _types.SimpleNamespace(RandomSearch=RandomSearch)
+baselines = _types.SimpleNamespace(RandomSearch=RandomSearch, MonteCarloTreeSearch=MonteCarloTreeSearch)
 base = _types.SimpleNamespace(TrajOptSolver=TrajOptSolver, SearchIntermediate=SearchIntermediate)

@@ -40,6 +40,7 @@ SF_MAX_INTERACTION_DISTANCE = 2.0        # :54
 PF_V0 = (2.0, 1.0)                       # :56
 PF_MAX_THETA = 30.0                      # :57
 OBJ_POS_MAX, OBJ_VEL_MAX, OBJ_ACC_MAX = 3.0, 1.0, 1.0   # :101-103
+OBJ_PROB_MAX = 120.0                                    # :100
 MIN_L2_DISTANCE = 0.5                    # :107
 VIOLATION_PRECISION = 1e-5               # :108
 
@@ -276,7 +277,28 @@ def interaction_raw(kind: str, mus, mus_wo, dt, ado_mask=None):
     return cost.clamp_max(max_value), cost
 
 
-INTERACT_MAX = {"acc": OBJ_ACC_MAX, "vel": OBJ_VEL_MAX, "pos": OBJ_POS_MAX}
+INTERACT_MAX = {"acc": OBJ_ACC_MAX, "vel": OBJ_VEL_MAX, "pos": OBJ_POS_MAX, "prob": OBJ_PROB_MAX}
+
+
+def prob_interact_raw(mus, sigmas, mus_wo, ado_mask=None):
+    """`InteractionProbabilityModule._objective_core` (modules/prob_interact.py:57-86): minus the log-probability of the
+    ego-free mean velocities in the conditioned distribution Normal(loc = mu_v, scale = sigmas) -- `sigmas` are VARIANCES
+    used as scale (particle.py:175,180) --, summed over (t, modes, xy), averaged over the ados of the
+    cost, clamped to +-OBJECTIVE_PROB_INTERACT_MAX. mus, mus_wo [B,N,T,4], sigmas [B,N,T,2] -> (clamped, unclamped) [B]."""
+    loc, scale, x = mus[..., 2:4], sigmas, mus_wo[..., 2:4]
+    if ado_mask is not None:
+        # ados outside `ado_ids` are not part of the reference's graph at all: give them harmless inputs instead of
+        # multiplying their (possibly overflowing) terms by zero, which would put 0 * inf = NaN into the backward pass.
+        sel = ado_mask.to(torch.bool)[..., None, None]
+        loc, scale = torch.where(sel, loc, x), torch.where(sel, scale, torch.ones_like(scale))
+    dist = torch.distributions.Normal(loc=loc, scale=scale, validate_args=False)
+    lp_ado = dist.log_prob(x).sum(dim=(-1, -2))                            # [B,N]
+    if ado_mask is None:
+        cost = -lp_ado.mean(dim=-1)
+    else:
+        m = ado_mask.to(lp_ado.dtype)
+        cost = -(lp_ado * m).sum(dim=-1) / m.sum(dim=-1).clamp(min=1.0)
+    return cost.clamp(-OBJ_PROB_MAX, OBJ_PROB_MAX), cost
 
 
 def min_distance_raw(ego_traj, mus):
@@ -337,17 +359,17 @@ def evaluate(scene: Scene, controls: torch.Tensor, mus_wo: typing.Optional[torch
     """One `IPOPTSolver.objective` + `gradient` evaluation (solver/base/trajopt.py:368-391, solver/ipopt.py:118-135)
     per batch entry: weighted, normalised module objectives and the gradient of their sum w.r.t. the controls.
 
-    weights: {"goal": w, "acc": w, "vel": w, "pos": w} (missing = module absent).
-    Returns dict(obj [B, 4] in the order goal/acc/vel/pos, total [B], grad [B,T,2], mus, sigmas, ego_traj, raw).
+    weights: {"goal": w, "acc": w, "vel": w, "pos": w, "prob": w} (missing = module absent).
+    Returns dict(obj [B, 5] in the order goal/acc/vel/pos/prob, total [B], grad [B,T,2], mus, sigmas, ego_traj, raw).
     """
     controls = controls.detach().clone().requires_grad_(want_grad)
     ego_traj = ego_unroll(scene.ego0, controls, scene.dt, scene.ego_kind)
     mus, sigmas = rollout(scene.env_kind, scene.ado0, scene.goal, scene.v0, scene.sigma, scene.weights,
                           scene.noise, ego_traj, scene.dt)
     b = controls.shape[0]
-    raw = torch.zeros((b, 4), dtype=controls.dtype)
+    raw = torch.zeros((b, 5), dtype=controls.dtype)
     cols = []
-    for i, key in enumerate(("goal", "acc", "vel", "pos")):
+    for i, key in enumerate(("goal", "acc", "vel", "pos", "prob")):
         wgt = weights.get(key, 0.0)
         if key == "goal":
             if key not in weights:
@@ -360,7 +382,10 @@ def evaluate(scene: Scene, controls: torch.Tensor, mus_wo: typing.Optional[torch
             if key not in weights or mus_wo is None:
                 cols.append(torch.zeros(b, dtype=controls.dtype))
                 continue
-            jc, ju = interaction_raw(key, mus, mus_wo, scene.dt, ado_mask)
+            if key == "prob":
+                jc, ju = prob_interact_raw(mus, sigmas, mus_wo, ado_mask)
+            else:
+                jc, ju = interaction_raw(key, mus, mus_wo, scene.dt, ado_mask)
             raw[:, i] = ju.detach()
             cols.append(wgt * jc / INTERACT_MAX[key])
     obj = torch.stack(cols, dim=1)

@@ -121,11 +121,12 @@ def generate(name, case):
     out["mus_wo"], out["sigmas_wo"] = rh.to_np(mus_wo), rh.to_np(sig_wo)
 
     module_classes = {"goal": mantrap.modules.GoalNormModule,
+                      "prob": mantrap.modules.InteractionProbabilityModule,
                       "acc": mantrap.modules.baselines.InteractionAccelerationModule,
                       "vel": mantrap.modules.baselines.InteractionVelocityModule,
                       "pos": mantrap.modules.baselines.InteractionPositionModule}
     ado_ids = env.ado_ids
-    for key in case["modules"]:
+    for key in (*case["modules"], "prob"):      # the probability module (TrajOptSolver.module_defaults) on every scene
         if key == "min_distance":
             continue
         torch.manual_seed(case["seed_wo"])
@@ -138,7 +139,13 @@ def generate(name, case):
         traj = env.ego.unroll_trajectory(u, dt=env.dt)
         torch.manual_seed(case["seed"])
         out[f"grad_{key}"] = np.asarray(module.gradient(traj, grad_wrt=u, ado_ids=ado_ids, tag="g"), dtype=np.float64)
-        if key != "goal":
+        if key == "prob":
+            # un-clamped cost: minus the mean over ados of the summed log-probabilities (prob_interact.py:74-78).
+            torch.manual_seed(case["seed"])
+            dist = env.compute_distributions(traj)
+            lp = sum(torch.sum(dist[i].log_prob(module._dist_un_conditioned[i].mean)) for i in ado_ids)
+            out["raw_prob"] = np.float64((-lp / n).item())
+        elif key != "goal":
             # un-clamped cost, to check gradients on unsaturated evaluations (SURVEY §8d "Parity gate").
             torch.manual_seed(case["seed"])
             summary = module.summarize_distribution(traj)

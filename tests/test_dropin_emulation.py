@@ -65,6 +65,15 @@ def test_closed_loop_random_search():
     dc.check_closed_loop(solver.RandomSearch, "sf", steps=2, num_candidates=32, max_rounds=1)
 
 
+def test_mcts():
+    dc.check_mcts(4, 6)
+
+
+def test_closed_loop_mcts():
+    from mantrap_b200 import solver
+    dc.check_closed_loop(solver.MonteCarloTreeSearch, "sf", steps=2, num_breadth_samples=4, num_depth_samples=8, max_cpu_time=60.0)
+
+
 def test_ipopt_solver_reports_missing_cyipopt():
     """cyipopt is a third-party dependency of the reference (ipopt==0.1.9) and not installed: the callbacks work, the
     interior-point call raises a clear ImportError instead of silently doing something else."""

@@ -55,3 +55,12 @@ def test_closed_loop_slsqp(env_kind):
 def test_closed_loop_random_search():
     from mantrap_b200 import solver
     dc.check_closed_loop(solver.RandomSearch, "sf", steps=4, num_candidates=4096, max_rounds=2)
+
+
+def test_mcts():
+    dc.check_mcts(8, 16)
+
+
+def test_closed_loop_mcts():
+    from mantrap_b200 import solver
+    dc.check_closed_loop(solver.MonteCarloTreeSearch, "sf", steps=4, num_breadth_samples=64, num_depth_samples=64, max_cpu_time=60.0)

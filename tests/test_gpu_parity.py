@@ -48,6 +48,9 @@ def test_constraints_golden(eng, name):
     ("sf", "double", 2, 33, 2, 2, 9, {"goal": 0.5, "acc": 1.0}),            # groups of 4 lanes, horizon > group: serial fold
     ("sf", "single", 1, 50, 1, 2, 5, {"goal": 0.5, "acc": 1.0, "vel": 1.0}),  # groups of 2 lanes, one ado (no pair terms)
     ("sf", "double", 2, 6, 9, 3, 40, {"goal": 0.5, "acc": 1.0}),            # horizon 40 > 32 lanes: serial fold
+    ("sf", "double", 4, 16, 20, 3, 12, {"goal": 0.5, "prob": 1.0, "acc": 1.0}),  # probability objective, config-4 shape
+    ("pf", "double", 2, 32, 5, 5, 15, {"goal": 0.5, "prob": 1.0}),
+    ("kalman", "double", 2, 5, 5, 1, 15, {"goal": 0.5, "prob": 1.0}),
 ])
 def test_batched_vs_oracle(eng, env_kind, ego_kind, s, c, n, p, t_hor, weights):
     kc.check_batched_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)

@@ -48,6 +48,8 @@ def test_constraints(emul_lib, name):
     ("kalman", "double", 2, 3, 5, 1, 6, {"goal": 0.5, "acc": 1.0}),
     ("sf", "double", 2, 3, 2, 2, 9, {"goal": 0.5, "acc": 1.0}),            # groups of 4 lanes, horizon > group: serial fold
     ("sf", "single", 1, 5, 1, 2, 5, {"goal": 0.5, "acc": 1.0, "vel": 1.0}),  # groups of 2 lanes, one ado (no pair terms)
+    ("sf", "double", 2, 3, 5, 4, 6, {"goal": 0.5, "prob": 1.0, "acc": 1.0}),  # probability objective (variance adjoint)
+    ("kalman", "double", 1, 2, 4, 1, 7, {"goal": 0.5, "prob": 1.0}),
 ])
 def test_batched_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor, weights):
     kc.check_batched_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights)
