@@ -15,6 +15,9 @@
  *   mtb_constraint_jacobian mantrap/solver/ipopt.py:140-154          IPOPTSolver.jacobian (MinDistance rows;
  *                           mantrap/modules/base/optimization_module.py:258-307, :428-434)
  *   mtb_argmin              mantrap/solver/baselines/random_search.py:28-35  keep-best-feasible candidate
+ *   mtb_attention           mantrap/attention/euclidean.py:22-29, closest.py:22-31   attention filters -> ado_mask
+ *   mtb_env_step            mantrap/environment/base/graph_based.py:82-124   GraphBasedEnvironment.step, batched
+ *                           mantrap/solver/base/trajopt.py:109-193           closed-loop solve(), warm-start shift
  *
  * Layouts are row-major float32, exactly the flattening the reference uses: controls z = (t, xy)
  * (trajopt.py:439-444), states (px, py, vx, vy), means mus = (mu_px, mu_py, mu_vx, mu_vy) per (ado, t).
@@ -29,7 +32,7 @@
 extern "C" {
 #endif
 
-#define MTB_ABI_VERSION 3
+#define MTB_ABI_VERSION 4
 
 /* environment kinds: mantrap/environment/social_forces.py, simplified/potential_field.py, simplified/kalman.py */
 #define MTB_ENV_SOCIAL_FORCES 0
@@ -112,6 +115,12 @@ typedef struct mtb_modules {
      * the cost, clamped to [-max_prob, max_prob] (constants.py:100); w_prob = weight / max_prob (prob_interact.py:97). */
     float w_prob;
     float max_prob;
+    /* InteractionEllipsoidModule (modules/baselines/ellipsoid_interact.py:28-78): rows [N,T] (one "mode" per ado in the
+     * particle environments), sum_xy (ego_p(t) - mu_p[k,t])^2 / max(scale[k,t], ellipsoid_min_scale) >= 1 with scale =
+     * the distribution's `stddev` (= the velocity variance, reference quirk), means and scales DETACHED: the Jacobian
+     * goes through the ego rollout only. Not normalised (ellipsoid_interact.py:91-99). */
+    int32_t con_ellipsoid;
+    float ellipsoid_min_scale; /* 0.01, ellipsoid_interact.py:52 */
 } mtb_modules;
 
 /* Outputs; every pointer may be NULL (= not wanted). */
@@ -123,7 +132,7 @@ typedef struct mtb_outputs {
     float* grad_traj;  /* [S,C,T+1,4] the same gradient w.r.t. the ego trajectory rows (px,py,vx,vy), before it is
                         * folded through the ego dynamics; raw: NaN is NOT replaced (grad applies np.nan_to_num as the reference does).
                         * grad == NULL && grad_traj == NULL = forward only */
-    float* cons;       /* [S,C,R] normalised constraint rows: control (2T or T) | speed 2(T+1) | min-distance N*T */
+    float* cons;       /* [S,C,R] normalised constraint rows: control (2T or T) | speed 2(T+1) | min-distance N*T | ellipsoid N*T */
     float* violation;  /* [S,C] summed constraint violation (optimization_module.py:512-533) */
     float* ego_traj;   /* [S,C,T+1,4] */
     float* mus;        /* [S,C,N,T,4] */
@@ -158,7 +167,8 @@ int mtb_query_launch(const mtb_problem* problem, int want_grad, mtb_launch_info*
  * OptimizationModule.jacobian returns it (optimization_module.py:258-307): control rows = identity for the double
  * integrator (control_limits.py:62-68, reference quirk) and u/||u|| for the single integrator, speed rows = velocity
  * block of dx_du (speed_limits.py:39-81, linear.py:169-196), min-distance rows = forward-mode tangents through the
- * ego rollout AND the environment rollout (replaces one autograd sweep per row, optimization_module.py:428-434).
+ * ego rollout AND the environment rollout (replaces one autograd sweep per row, optimization_module.py:428-434),
+ * ellipsoid rows = 2 (ego_p - mu_p) / max(scale, min) through the ego rollout only (means detached).
  * cons (optional, may be NULL) receives the un-normalised min-distance values [S,C,N*T]. */
 int mtb_constraint_jacobian(const mtb_problem* problem, const mtb_modules* modules, float* cons,
                             float* jac, void* workspace, size_t workspace_bytes, void* stream);
@@ -168,6 +178,30 @@ size_t mtb_jacobian_workspace_bytes(const mtb_problem* problem);
 int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, int32_t num_candidates,
                float feas_tol, const float* controls, int32_t t_horizon, int32_t* best_idx, float* best_val,
                float* best_controls, void* stream);
+
+/* Attention filters (mantrap/attention): mask[S,N] = 1 where the ado enters the cost. ego0 [S,4], ado0 [S,N,4].
+ *   MTB_ATTENTION_EUCLIDEAN  ||ado_p - ego_p|| < radius                                   (euclidean.py:22-29)
+ *   MTB_ATTENTION_CLOSEST    the same test after `distances[~argmin] = inf`: `~` of a 0-dim integer tensor is the bitwise
+ *                            NOT, i.e. index -(argmin + 1) = N - 1 - argmin is excluded (closest.py:26-28, reference quirk,
+ *                            reproduced; first minimum wins ties like torch.argmin) */
+#define MTB_ATTENTION_EUCLIDEAN 0
+#define MTB_ATTENTION_CLOSEST 1
+int mtb_attention(int kind, const float* ego0, const float* ado0, int32_t num_scenes, int32_t num_ados, float radius,
+                  uint8_t* mask, void* stream);
+
+/* One closed-loop environment step for S scenes in lock step (GraphBasedEnvironment.step, graph_based.py:82-124):
+ * the ego executes controls[s, 0] (controls [S,T,2], e.g. mtb_argmin's best_controls); every ado samples its next
+ * position from the one-step velocity distribution Normal(loc = v, scale = var_initial) (a one-control rollout has no
+ * particle step, particle.py:140-181 with t_horizon = 1): p' = p + dt (v + var_initial eps), v' = (p' - p) / dt.
+ * eps [S,N,2] are the caller's standard-normal draws (NULL = mean). ego0 [S,4] and ado0 [S,N,4] are updated IN PLACE.
+ * warm (optional, [S,T,2]) receives the shifted warm start of the next solve: controls[s, 1:] followed by zeros
+ * (trajopt.py:150-155).
+ * Both updates clamp their action like DTAgent.update does (make_controls_feasible, discrete.py:144-167, :358-370):
+ * ego_u_max = ROBOT_ACC_MAX per component (double integrator) or ROBOT_SPEED_MAX on the L2 norm (single integrator),
+ * ped_speed_max on the L2 norm of the ados' single-integrator action. */
+int mtb_env_step(int ego_kind, float dt, float var_initial, float ego_u_max, float ped_speed_max, float* ego0,
+                 float* ado0, const float* controls, const float* eps, int32_t num_scenes, int32_t num_ados,
+                 int32_t t_horizon, float* warm, void* stream);
 
 /* Batched ego (robot) dynamics, state rows (px, py, vx, vy, time); device pointers.
  *   mtb_ego_unroll          LinearDTAgent.unroll_trajectory  agents/base/linear.py:68-105   x0[B,5], controls[B,T,2] -> [B,T+1,5]

@@ -7,7 +7,7 @@ Sub-modules are imported lazily: importing the package needs neither a GPU nor t
 """
 import importlib
 
-_SUBMODULES = ("agents", "api", "autograd", "build", "constants", "engine", "environment", "modules", "parallel", "runtime",
+_SUBMODULES = ("agents", "api", "attention", "autograd", "build", "constants", "engine", "environment", "modules", "mpc", "parallel", "runtime",
                "scenarios", "solver")
 
 

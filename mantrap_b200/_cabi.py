@@ -12,7 +12,8 @@ import torch
 ENV_SOCIAL_FORCES, ENV_POTENTIAL_FIELD, ENV_KALMAN = 0, 1, 2
 EGO_DOUBLE_INTEGRATOR, EGO_SINGLE_INTEGRATOR, EGO_NONE = 0, 1, 2
 MAX_ADOS, MAX_HORIZON = 64, 64
-ABI_VERSION = 3
+ABI_VERSION = 4
+ATTENTION_EUCLIDEAN, ATTENTION_CLOSEST = 0, 1
 
 _f, _i, _p = ctypes.c_float, ctypes.c_int32, ctypes.c_void_p
 
@@ -33,7 +34,8 @@ class MtbModules(ctypes.Structure):
                 ("ego_goal", _p), ("mus_wo", _p), ("ado_mask", _p),
                 ("con_control", _i), ("con_speed", _i), ("con_min_distance", _i),
                 ("u_max", _f), ("v_max", _f), ("min_distance", _f), ("violation_eps", _f),
-                ("seed_mus", _p), ("seed_sigmas", _p), ("w_prob", _f), ("max_prob", _f)]
+                ("seed_mus", _p), ("seed_sigmas", _p), ("w_prob", _f), ("max_prob", _f),
+                ("con_ellipsoid", _i), ("ellipsoid_min_scale", _f)]
 
 
 class MtbOutputs(ctypes.Structure):
@@ -48,7 +50,7 @@ class MtbLaunchInfo(ctypes.Structure):
 
 EXPORTED_SYMBOLS = ("mtb_abi_version", "mtb_error_string", "mtb_num_constraint_rows", "mtb_workspace_bytes",
                     "mtb_evaluate", "mtb_query_launch", "mtb_constraint_jacobian", "mtb_jacobian_workspace_bytes",
-                    "mtb_argmin", "mtb_probe_launch", "mtb_ego_unroll", "mtb_ego_roll", "mtb_ego_unroll_adjoint",
+                    "mtb_argmin", "mtb_attention", "mtb_env_step", "mtb_probe_launch", "mtb_ego_unroll", "mtb_ego_roll", "mtb_ego_unroll_adjoint",
                     "mtb_ego_dx_du")
 
 
@@ -76,6 +78,10 @@ def bind(lib: ctypes.CDLL) -> ctypes.CDLL:
     lib.mtb_ego_unroll_adjoint.restype = ctypes.c_int
     lib.mtb_ego_unroll_adjoint.argtypes = [ctypes.c_int, _f, _p, _i, _i, _p, _p]
     lib.mtb_ego_dx_du.restype, lib.mtb_ego_dx_du.argtypes = ctypes.c_int, [ctypes.c_int, _f, _i, _p, _p]
+    lib.mtb_attention.restype = ctypes.c_int
+    lib.mtb_attention.argtypes = [ctypes.c_int, _p, _p, _i, _i, _f, _p, _p]
+    lib.mtb_env_step.restype = ctypes.c_int
+    lib.mtb_env_step.argtypes = [ctypes.c_int, _f, _f, _f, _f, _p, _p, _p, _p, _i, _i, _i, _p, _p]
     lib.mtb_argmin.restype = ctypes.c_int
     lib.mtb_argmin.argtypes = [_p, _p, _i, _i, _f, _p, _i, _p, _p, _p, _p]
     return lib

@@ -37,6 +37,10 @@ OBJECTIVE_VEL_INTERACT_MAX = 1.0                 # :102
 OBJECTIVE_ACC_INTERACT_MAX = 1.0                 # :103
 CONSTRAINT_MIN_L2_DISTANCE = 0.5                 # :107
 CONSTRAINT_VIOLATION_PRECISION = 1e-5            # :108
+CONSTRAINT_ELLIPSOID_NUM_MODES = 5               # :109
+CONSTRAINT_ELLIPSOID_MIN_SCALE = 0.01            # modules/baselines/ellipsoid_interact.py:52 (literal in the reference)
+ATTENTION_EUCLIDEAN_RADIUS = 4.0                 # :111
+ATTENTION_CLOSEST_RADIUS = 4.0                   # :112
 
 TAG_OPTIMIZATION = "optimization"                # :16
 TAG_WARM_START = "warm_start"                    # :17

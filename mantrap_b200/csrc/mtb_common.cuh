@@ -10,8 +10,15 @@
 #define MTB_SHARED_FLOAT4(name) extern __shared__ float4 name[]
 #define MTB_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
 // named barrier over `count` threads (a multiple of 32): synchronises one evaluation group, not the whole block
+// The id is an immediate (ptxas reserves all 16 barriers of a block for a register id, which caps the resident blocks per
+// SM); a block holds at most four groups of >= 64 threads plus, for larger blocks, one group = the whole block.
 static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
+    switch (id) {
+        case 0: asm volatile("bar.sync 0, %0;" ::"r"(count) : "memory"); break;
+        case 1: asm volatile("bar.sync 1, %0;" ::"r"(count) : "memory"); break;
+        case 2: asm volatile("bar.sync 2, %0;" ::"r"(count) : "memory"); break;
+        default: asm volatile("bar.sync 3, %0;" ::"r"(count) : "memory"); break;   // E <= 4 groups of >= 64 threads in <= 256 threads
+    }
 }
 // Fire-and-forget 16-byte float accumulation in L2 (REDG.E.ADD.F32x4, sm_90+): one instruction per pair adjoint instead
 // of four shared-memory compare-and-swap loops. The target lives in an L2-resident global scratch; loads / stores of it
@@ -91,18 +98,19 @@ static inline float pair_cut_squared(float radius) {
     return cut;
 }
 
-// constraint rows of the enabled constraint modules: control | speed | min-distance
+// constraint rows of the enabled constraint modules: control | speed | min-distance | ellipsoid
 struct ConstraintRows {
-    int control, speed, mind, total;
+    int control, speed, mind, ell, total;
 };
 static inline ConstraintRows constraint_rows(const mtb_problem* pb, const mtb_modules* md) {
-    ConstraintRows r = {0, 0, 0, 0};
+    ConstraintRows r = {0, 0, 0, 0, 0};
     if (md != nullptr && pb->ego_kind != MTB_EGO_NONE) {
         if (md->con_control) r.control = (pb->ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) ? 2 * pb->t_horizon : pb->t_horizon;
         if (md->con_speed) r.speed = 2 * (pb->t_horizon + 1);
         if (md->con_min_distance) r.mind = pb->num_ados * pb->t_horizon;
+        if (md->con_ellipsoid) r.ell = pb->num_ados * pb->t_horizon;
     }
-    r.total = r.control + r.speed + r.mind;
+    r.total = r.control + r.speed + r.mind + r.ell;
     return r;
 }
 

@@ -12,6 +12,7 @@
 //   control rows  control_limits.py:38-68     identity (double integrator, reference quirk) | u/||u|| (single)
 //   speed rows    speed_limits.py:39-81       velocity rows of dx_du (agents/base/linear.py:169-196)
 //   min-distance  constants.py:107 (north star): d ||ego_p(t) - mu_p[k,t]|| / du through ego AND environment rollout
+//   ellipsoid     baselines/ellipsoid_interact.py:47-57: means and scales detached, 2 (ego_p - mu_p) / max(scale, min) d ego_p / du
 #include "mtb_common.cuh"
 #include "mtb_math.cuh"
 
@@ -24,9 +25,9 @@ struct JParams {
     float* jac;
     int T, N, P, G, GP, MW, n_chunks;
     long long num_items;
-    int rows_control, rows_speed, rows_mind, R;
+    int rows_control, rows_speed, rows_mind, rows_ell, R;
     float pair_cut2;
-    int off_ctl, off_ego, off_mus, off_mud, off_q, off_qd;   // float offsets into dynamic shared memory
+    int off_ctl, off_ego, off_mus, off_mud, off_q, off_qd, off_var;   // float offsets into dynamic shared memory
 };
 
 // tangent of the ego state at time index t w.r.t. control j (same component): (d p, d v)   [SURVEY A.1]
@@ -59,6 +60,7 @@ __global__ void __launch_bounds__(MAXT) jacobian_kernel(const JParams prm) {
     float4* mud = reinterpret_cast<float4*>(sm + prm.off_mud);      // [2][N][D] tangents of the means (p.xy, v.xy)
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);       // [GP]
     float2* qd = reinterpret_cast<float2*>(sm + prm.off_qd);        // [GP][D]
+    float2* varl = reinterpret_cast<float2*>(sm + prm.off_var);     // [2][N] scales of the two rotating levels (ellipsoid rows)
 
     for (long long item = blockIdx.x; item < prm.num_items; item += gridDim.x) {
         const size_t ev = (size_t)(item / prm.n_chunks);
@@ -76,7 +78,10 @@ __global__ void __launch_bounds__(MAXT) jacobian_kernel(const JParams prm) {
             for (int t = g; t <= T; t += nthreads) ego[t] = *reinterpret_cast<const float4*>(x_g + t * 4);
         }
         const float* ado0_s = prm.pb.ado0 + (size_t)s * N * 4;
-        for (int k = g; k < N; k += nthreads) mus[k] = *reinterpret_cast<const float4*>(ado0_s + k * 4);
+        for (int k = g; k < N; k += nthreads) {
+            mus[k] = *reinterpret_cast<const float4*>(ado0_s + k * 4);
+            varl[k] = make_float2(prm.pb.var_initial, prm.pb.var_initial);
+        }
         for (int idx = g; idx < 2 * N * D; idx += nthreads) mud[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
         __syncthreads();
         if (traj_given) {                                           // controls by inverse dynamics (roll_trajectory)
@@ -153,9 +158,23 @@ __global__ void __launch_bounds__(MAXT) jacobian_kernel(const JParams prm) {
         const bool want_mind = prm.rows_mind > 0;
         float* cons = (prm.cons != nullptr && chunk == 0) ? prm.cons + ev * (size_t)N * T : nullptr;
         // min-distance rows of level `level` (means complete): d ||ego_p - mu_p[k]|| for the D directions of the chunk
-        auto write_rows = [&](int level, const float4* mus_l, const float4* mud_l) {
-            if (!want_mind) return;
+        const int base_ell = base_mind + prm.rows_mind;
+        auto write_rows = [&](int level, const float4* mus_l, const float4* mud_l, const float2* var_l) {
             const float4 eg = ego[level];
+            if (prm.rows_ell > 0) {
+                for (int idx = g; idx < N * D; idx += nthreads) {
+                    const int k = idx / D, d = idx - k * D, dg = d0 + d;
+                    if (dg >= two_t) continue;
+                    const float4 mu = mus_l[k];
+                    float2 sv = var_l[k];
+                    if (ENV == MTB_ENV_KALMAN) sv.x = sv.y = fmaf(prm.pb.kalman_noise, (float)level, prm.pb.var_initial);
+                    const float ep = ego_tangent(ego_kind, dt, level, dg >> 1).x;
+                    const float val = (dg & 1) ? 2.0f * (eg.y - mu.y) / fmaxf(sv.y, prm.md.ellipsoid_min_scale) * ep
+                                               : 2.0f * (eg.x - mu.x) / fmaxf(sv.x, prm.md.ellipsoid_min_scale) * ep;
+                    jac[(size_t)(base_ell + k * T + level) * two_t + dg] = val;
+                }
+            }
+            if (!want_mind) return;
             for (int idx = g; idx < N * D; idx += nthreads) {
                 const int k = idx / D, d = idx - k * D, dg = d0 + d;
                 const float4 mu = mus_l[k];
@@ -173,7 +192,7 @@ __global__ void __launch_bounds__(MAXT) jacobian_kernel(const JParams prm) {
                 jac[(size_t)(base_mind + k * T + level) * two_t + dg] = val;
             }
         };
-        write_rows(0, mus, mud);
+        write_rows(0, mus, mud, varl);
 
         // first time index at which an ego tangent of this chunk is non-zero: control j acts on ego[t] for t >= j + 1
         const int t_first = (d0 >> 1) + 1;
@@ -293,7 +312,17 @@ __global__ void __launch_bounds__(MAXT) jacobian_kernel(const JParams prm) {
                 float sx = 0.f, sy = 0.f;
                 for (int j = 0; j < P; ++j) { sx += qbuf[g + j].x; sy += qbuf[g + j].y; }
                 const float4 c = mus_t[m];
-                mus[nxt * N + m] = make_float4(fmaf(c.z, dt, c.x), fmaf(c.w, dt, c.y), sx / (float)P, sy / (float)P);
+                const float mx = sx / (float)P, my = sy / (float)P;
+                mus[nxt * N + m] = make_float4(fmaf(c.z, dt, c.x), fmaf(c.w, dt, c.y), mx, my);
+                if (prm.rows_ell > 0 && ENV != MTB_ENV_KALMAN) {     // unbiased variance of the weighted velocities (particle.py:175)
+                    float vx = 0.f, vy = 0.f;
+                    for (int j = 0; j < P; ++j) {
+                        const float ex = qbuf[g + j].x - mx, ey = qbuf[g + j].y - my;
+                        vx = fmaf(ex, ex, vx);
+                        vy = fmaf(ey, ey, vy);
+                    }
+                    varl[nxt * N + m] = make_float2(vx / (float)(P - 1), vy / (float)(P - 1));
+                }
             }
             for (int idx = g; idx < N * D; idx += nthreads) {
                 const int k = idx / D, d = idx - k * D;
@@ -306,7 +335,7 @@ __global__ void __launch_bounds__(MAXT) jacobian_kernel(const JParams prm) {
                 mud[nxt * N * D + idx] = make_float4(fmaf(c.z, dt, c.x), fmaf(c.w, dt, c.y), sx, sy);
             }
             __syncthreads();
-            write_rows(t + 1, mus + nxt * N, mud + nxt * N * D);
+            write_rows(t + 1, mus + nxt * N, mud + nxt * N * D, varl + nxt * N);
         }
         __syncthreads();
     }
@@ -329,7 +358,7 @@ static int plan_jacobian(const mtb_problem* pb, const mtb_modules* md, JParams& 
     prm.MW = (prm.N + 31) / 32;
     prm.pair_cut2 = pair_cut_squared(pb->sf_interaction_radius);
     const ConstraintRows rows = constraint_rows(pb, md);
-    prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.R = rows.total;
+    prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.rows_ell = rows.ell; prm.R = rows.total;
     if (prm.R == 0) return MTB_ERR_BAD_ARGUMENT;
     dirs = (prm.GP <= 256) ? 8 : 4;
     prm.n_chunks = (2 * prm.T + dirs - 1) / dirs;
@@ -341,6 +370,7 @@ static int plan_jacobian(const mtb_problem* pb, const mtb_modules* md, JParams& 
     prm.off_mud = off; off += 2 * prm.N * dirs * 4;
     prm.off_q = off;   off += round_up(prm.GP * 2, 4);
     prm.off_qd = off;  off += round_up(prm.GP * dirs * 2, 4);
+    prm.off_var = off; off += round_up(2 * prm.N * 2, 4);
     smem = (size_t)off * sizeof(float);
     const DeviceLimits lim = device_limits();
     if (smem > (size_t)lim.max_smem) return MTB_ERR_TOO_LARGE;

@@ -30,14 +30,14 @@ struct KParams {
     float pair_cut2;                 // the float after the largest d^2 with sqrtf(d^2) <= interaction radius (strict <)
     // shared-memory layout (float units, per evaluation) -------------------------------------------------
     int off_ctl, off_ego, off_egobar, off_mus, off_pos, off_dir, off_var, off_q, off_misc, off_tape, off_mask;
-    int keep_var;                    // variances [T][N] kept in shared memory (InteractionProbabilityModule)
+    int keep_var;                    // variances [T][N] kept in shared memory (InteractionProbabilityModule, ellipsoid rows)
     int NP4;                         // N rounded up to 4: length of the SoA position rows used by the radius test
     int per_eval_f, red_f;
     int tape_in_smem;
     float4* abar_global;             // [grid][E][T][N] adjoints of the means: objective seeds + pair terms (L2 vector reductions)
     float4* tape_global;             // [grid][T-1][block]   when the tape does not fit in shared memory
     unsigned* mask_global;           // [grid][T-1][block][MW]
-    int rows_control, rows_speed, rows_mind, R;
+    int rows_control, rows_speed, rows_mind, rows_ell, R;
     size_t ws_abar_bytes, ws_tape_bytes, ws_mask_bytes;   // workspace layout: mean adjoints | tape | interaction masks
 };
 
@@ -49,10 +49,10 @@ struct Red4 {
 };
 
 // Barrier over the threads of one evaluation group. Sub-warp groups live inside one warp (all groups of a warp run in
-// lock step), larger groups use one named barrier each (id 1 + e; at most 8 groups of >= 64 threads per block).
+// lock step), larger groups use one named barrier each (id e; at most 8 groups of >= 64 threads per block).
 MTB_DEV void group_sync(int GP, int e) {
     if (GP <= 32) __syncwarp();
-    else mtb_bar_sync(1 + e, GP);
+    else mtb_bar_sync(e, GP);
 }
 
 // Sum over the GP threads of a group; result valid in every thread of the group. Must be reached by all threads of
@@ -522,6 +522,21 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                     if (cons != nullptr) cons[base + idx] = val;
                     if (amask == nullptr || amask[k] != 0) vio.c += fmaxf(prm.md.min_distance - val, 0.f);
                 }
+                base += prm.rows_mind;
+            }
+            if (prm.rows_ell > 0) {                               // ellipsoid_interact.py:47-57, every ado of the scene
+                for (int idx = g; idx < N * T; idx += GP) {
+                    const int k = idx / T, t = idx - k * T;
+                    const float4 mu = mus[t * N + k];
+                    float2 sv = varbuf[t * N + k];
+                    // Kalman: scale of the POSITIONAL distribution, var_initial + Q t (kalman.py:79-92)
+                    if (ENV == MTB_ENV_KALMAN) sv.x = sv.y = fmaf(prm.pb.kalman_noise, (float)t, prm.pb.var_initial);
+                    const float4 x = ego[t];
+                    const float dx = x.x - mu.x, dy = x.y - mu.y;
+                    const float val = dx * dx / fmaxf(sv.x, prm.md.ellipsoid_min_scale) + dy * dy / fmaxf(sv.y, prm.md.ellipsoid_min_scale);
+                    if (cons != nullptr) cons[base + idx] = val;
+                    vio.d += fmaxf(1.0f - val, 0.f);
+                }
             }
             vio = group_reduce4(vio, GP, e, red);
         }
@@ -569,7 +584,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                     const float va = (fabsf(vio.a) < eps) ? 0.f : vio.a;
                     const float vb = (fabsf(vio.b) < eps) ? 0.f : vio.b;
                     const float vc = (fabsf(vio.c) < eps) ? 0.f : vio.c;
-                    prm.out.violation[ev] = (va + vb) + vc;
+                    const float vd = (fabsf(vio.d) < eps) ? 0.f : vio.d;
+                    prm.out.violation[ev] = ((va + vb) + vc) + vd;
                 }
                 if (prm.out.stats != nullptr && ((want_interact &&
                     (raw_acc > prm.md.max_acc || raw_vel > prm.md.max_vel || raw_pos > prm.md.max_pos)) || (want_prob && cprob == 0.f)))
@@ -913,7 +929,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     prm.G = prm.N * prm.P;
     prm.MW = (prm.N + 31) / 32;
     prm.NP4 = round_up(prm.N, 4);
-    prm.keep_var = (md != nullptr && md->w_prob != 0.f && md->mus_wo != nullptr) ? 1 : 0;
+    prm.keep_var = (md != nullptr && ((md->w_prob != 0.f && md->mus_wo != nullptr) || (md->con_ellipsoid && pb->ego_kind != MTB_EGO_NONE))) ? 1 : 0;
     prm.has_ego = pb->ego_kind != MTB_EGO_NONE;
     prm.want_grad = want_grad ? 1 : 0;
     prm.pair_cut2 = nextafterf(pair_cut_squared(pb->sf_interaction_radius), INFINITY);   // d^2 < pair_cut2  <=>  norm <= radius
@@ -928,7 +944,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     // constraint rows
     {
         const ConstraintRows rows = constraint_rows(pb, md);
-        prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.R = rows.total;
+        prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.rows_ell = rows.ell; prm.R = rows.total;
     }
 
     const DeviceLimits lim = device_limits();
@@ -956,7 +972,12 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         return (size_t)(prm.red_f + E * prm.per_eval_f) * sizeof(float);
     };
 
-    int E = (prm.GP >= kDefaultBlock) ? 1 : kDefaultBlock / prm.GP;
+    int target_block = kDefaultBlock;
+    {
+        const int knob = env_flag("MTB_BLOCK");             // development knob: 64 / 128 / 256 threads per block
+        if (knob == 64 || knob == 128 || knob == 256) target_block = knob;
+    }
+    int E = (prm.GP >= target_block) ? 1 : target_block / prm.GP;
     const long long total_evals = (long long)pb->num_scenes * pb->num_candidates;
     if ((long long)E > total_evals) E = (int)total_evals;
     // the block must be a multiple of a warp: with sub-warp groups keep E a multiple of 32 / GP
@@ -1044,6 +1065,18 @@ template <int ENV, bool GRAD>
 static int launch_evaluate(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
     if (info.block > kDefaultBlock) return launch_evaluate_t<ENV, GRAD, kMaxThreads, 1>(prm, info, stream);
     const int force = env_flag("MTB_MINB");
+#ifdef MTB_EXPERIMENT
+    if (ENV == MTB_ENV_SOCIAL_FORCES && info.block <= 64) {
+        if (force == 16) return launch_evaluate_t<ENV, GRAD, 64, 16>(prm, info, stream);
+        if (force == 14) return launch_evaluate_t<ENV, GRAD, 64, 14>(prm, info, stream);
+        return launch_evaluate_t<ENV, GRAD, 64, 12>(prm, info, stream);
+    }
+    if (ENV == MTB_ENV_SOCIAL_FORCES && info.block <= 128) {
+        if (force == 8) return launch_evaluate_t<ENV, GRAD, 128, 8>(prm, info, stream);
+        if (force == 7) return launch_evaluate_t<ENV, GRAD, 128, 7>(prm, info, stream);
+        return launch_evaluate_t<ENV, GRAD, 128, 6>(prm, info, stream);
+    }
+#endif
     if (force == 4) return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 4>(prm, info, stream);
     if (force == 3 || (force == 0 && info.blocks_per_sm >= 3)) return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 3>(prm, info, stream);
     return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 2>(prm, info, stream);
@@ -1085,6 +1118,14 @@ size_t mtb_workspace_bytes(const mtb_problem* problem, int want_grad) {
     mtb_launch_info info;
     size_t ws = 0;
     if (mtb::plan(problem, nullptr, nullptr, want_grad != 0, prm, info, ws) != 0) return 0;
+    // modules that keep the variances in shared memory change the block layout (and possibly the tape placement): take
+    // the larger of the two plans so the size is valid for every module set
+    mtb_modules with_var;
+    std::memset(&with_var, 0, sizeof(with_var));
+    with_var.con_ellipsoid = 1;
+    size_t ws_var = 0;
+    if (problem->ego_kind != MTB_EGO_NONE && mtb::plan(problem, &with_var, nullptr, want_grad != 0, prm, info, ws_var) == 0 && ws_var > ws)
+        ws = ws_var;
     return ws;
 }
 

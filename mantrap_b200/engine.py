@@ -17,6 +17,7 @@ from . import _cabi, constants
 
 ENV_KINDS = {"sf": _cabi.ENV_SOCIAL_FORCES, "pf": _cabi.ENV_POTENTIAL_FIELD, "kalman": _cabi.ENV_KALMAN}
 EGO_KINDS = {"double": _cabi.EGO_DOUBLE_INTEGRATOR, "single": _cabi.EGO_SINGLE_INTEGRATOR, None: _cabi.EGO_NONE}
+ATTENTION_KINDS = {"euclidean": _cabi.ATTENTION_EUCLIDEAN, "closest": _cabi.ATTENTION_CLOSEST}
 OBJECTIVE_KEYS = ("goal", "acc", "vel", "pos", "prob")     # columns of `obj` / `obj_raw` (MTB_NUM_OBJECTIVES)
 NUM_OBJECTIVES = len(OBJECTIVE_KEYS)
 
@@ -80,6 +81,7 @@ class ModuleSpec:
     control_limits: bool = False
     speed_limits: bool = False
     min_distance: bool = False
+    ellipsoid: bool = False
     u_max: float = constants.ROBOT_ACC_MAX
     v_max: float = constants.ROBOT_SPEED_MAX
     d_min: float = constants.CONSTRAINT_MIN_L2_DISTANCE
@@ -137,6 +139,8 @@ def _module_struct(scene: SceneBatch, spec: ModuleSpec) -> _cabi.MtbModules:
     md.con_control = int(spec.control_limits)
     md.con_speed = int(spec.speed_limits)
     md.con_min_distance = int(spec.min_distance)
+    md.con_ellipsoid = int(spec.ellipsoid)
+    md.ellipsoid_min_scale = constants.CONSTRAINT_ELLIPSOID_MIN_SCALE
     md.u_max, md.v_max, md.min_distance = spec.u_max, spec.v_max, spec.d_min
     md.violation_eps = constants.CONSTRAINT_VIOLATION_PRECISION
     md.seed_mus = _cabi.ptr(spec.seed_mus)
@@ -195,7 +199,7 @@ def launch_evaluate(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Option
 def launch_jacobian(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Optional[torch.Tensor], spec: ModuleSpec,
                     stream: int = 0, want_values: bool = False, ego_traj: torch.Tensor = None):
     """One `mtb_constraint_jacobian` launch: dense UN-normalised Jacobian [S,C,R,2T] of every constraint row enabled
-    in `spec` (control | speed | min-distance, the row order of `cons`) w.r.t. the flattened controls; optionally the
+    in `spec` (control | speed | min-distance | ellipsoid, the row order of `cons`) w.r.t. the flattened controls; optionally the
     un-normalised min-distance values [S,C,N,T]."""
     t_horizon = controls.shape[2] if controls is not None else ego_traj.shape[2] - 1
     pb = _problem_struct(scene, controls, t_horizon, ego_traj)
@@ -210,6 +214,30 @@ def launch_jacobian(lib: ctypes.CDLL, scene: SceneBatch, controls: typing.Option
     code = lib.mtb_constraint_jacobian(ctypes.byref(pb), ctypes.byref(md), _cabi.ptr(values), _cabi.ptr(jac), None, 0, stream)
     _cabi.check(lib, code, "mtb_constraint_jacobian")
     return (jac, values) if want_values else jac
+
+
+def launch_attention(lib: ctypes.CDLL, kind: str, ego0: torch.Tensor, ado0: torch.Tensor, radius: float, stream: int = 0
+                     ) -> torch.Tensor:
+    """`mtb_attention`: mask [S,N] uint8 of the ados an attention filter keeps (mantrap/attention)."""
+    s, n = ado0.shape[0], ado0.shape[1]
+    mask = torch.empty((s, n), dtype=torch.uint8, device=ado0.device)
+    code = lib.mtb_attention(ATTENTION_KINDS[kind], _cabi.ptr(ego0), _cabi.ptr(ado0), s, n, radius,
+                             _cabi.ptr(mask, dtype=torch.uint8), stream)
+    _cabi.check(lib, code, "mtb_attention")
+    return mask
+
+
+def launch_env_step(lib: ctypes.CDLL, scene: SceneBatch, controls: torch.Tensor, eps: typing.Optional[torch.Tensor],
+                    warm: typing.Optional[torch.Tensor] = None, stream: int = 0):
+    """`mtb_env_step`: advance `scene.ego0` / `scene.ado0` IN PLACE by one closed-loop step with controls[:, 0]
+    (controls [S,T,2]); eps [S,N,2] standard-normal draws or None (mean step); `warm` [S,T,2] receives the shifted
+    warm start."""
+    s, t_horizon = controls.shape[0], controls.shape[1]
+    ego_u_max = constants.ROBOT_ACC_MAX if scene.ego_kind == "double" else constants.ROBOT_SPEED_MAX
+    code = lib.mtb_env_step(EGO_KINDS[scene.ego_kind], scene.dt, constants.ENV_VAR_INITIAL, ego_u_max,
+                            constants.PED_SPEED_MAX, _cabi.ptr(scene.ego0), _cabi.ptr(scene.ado0), _cabi.ptr(controls),
+                            _cabi.ptr(eps), s, scene.num_ados, t_horizon, _cabi.ptr(warm), stream)
+    _cabi.check(lib, code, "mtb_env_step")
 
 
 def query_launch(lib: ctypes.CDLL, scene: SceneBatch, controls: torch.Tensor, want_grad: bool) -> typing.Dict[str, int]:
@@ -345,6 +373,23 @@ class Engine:
             out = launch_argmin(self.lib, total, violation, controls, feas_tol, stream=self._stream())
         self.launches += 1
         return out
+
+    def attention(self, kind: str, ego0: torch.Tensor, ado0: torch.Tensor, radius: float = None) -> torch.Tensor:
+        """Attention filter of S scenes -> mask [S,N] uint8 (`kind` = "euclidean" | "closest")."""
+        self._check(ego0, ado0)
+        if radius is None:
+            radius = constants.ATTENTION_EUCLIDEAN_RADIUS if kind == "euclidean" else constants.ATTENTION_CLOSEST_RADIUS
+        with self._guard():
+            mask = launch_attention(self.lib, kind, ego0, ado0, radius, stream=self._stream())
+        self.launches += 1
+        return mask
+
+    def env_step(self, scene: SceneBatch, controls: torch.Tensor, eps: torch.Tensor = None, warm: torch.Tensor = None):
+        """One closed-loop step of every scene, in place (GraphBasedEnvironment.step for S scenes in lock step)."""
+        self._check(scene.ego0, scene.ado0, controls, eps, warm)
+        with self._guard():
+            launch_env_step(self.lib, scene, controls, eps, warm, stream=self._stream())
+        self.launches += 1
 
     def launch_info(self, scene: SceneBatch, controls: torch.Tensor, want_grad: bool = True):
         return query_launch(self.lib, scene, controls, want_grad)

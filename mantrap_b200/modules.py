@@ -519,11 +519,64 @@ class MinDistanceModule(_FusedConstraintModule):
         return "min_distance"
 
 
+class InteractionEllipsoidModule(_FusedConstraintModule):
+    """sum_xy (ego_p(t) - mu_p[k, t])^2 / max(scale[k, t], 0.01) >= 1 for EVERY ado of the scene (the reference's core ignores
+    `ado_ids` once it is non-empty) and t = 0..T-1: N*T rows, not normalised; means and scales are detached, so the
+    Jacobian goes through the ego rollout only (modules/baselines/ellipsoid_interact.py:13-125). One particle draw per
+    call, like the reference's `env.compute_distributions`."""
+    spec_flag = "ellipsoid"
+    needs_rollout = True
+
+    def __init__(self, env, t_horizon: int, **unused):
+        super().__init__(env=env, t_horizon=t_horizon, **{k: v for k, v in unused.items() if k == "num_particles"})
+
+    def _spec(self, ado_ids) -> ModuleSpec:
+        return ModuleSpec(ellipsoid=True)
+
+    def _defined(self, ado_ids) -> bool:
+        return not (ado_ids is not None and len(ado_ids) == 0) and self._env.num_ados > 0      # ellipsoid_interact.py:37-38
+
+    def constraint(self, ego_trajectory, ado_ids, tag) -> np.ndarray:
+        if not self._defined(ado_ids):
+            return self._return_constraint(np.array([]), tag=tag)
+        return super().constraint(ego_trajectory, ado_ids, tag)
+
+    def compute_constraint(self, ego_trajectory, ado_ids, tag):
+        if not self._defined(ado_ids):
+            return None
+        return super().compute_constraint(ego_trajectory, ado_ids, tag)
+
+    def compute_jacobian_analytically(self, ego_trajectory, grad_wrt, ado_ids, tag) -> np.ndarray:
+        if not self._defined(ado_ids):
+            return np.array([])
+        if not self.gradient_condition():                         # optimization_module.py:298-301 (Kalman: zeros)
+            return np.zeros(self._env.num_ados * self.t_horizon * int(grad_wrt.numel()))
+        return _np(self._dense_jacobian(ego_trajectory, ado_ids)).astype(np.float64).flatten()
+
+    def gradient_condition(self) -> bool:
+        return self._env.is_differentiable_wrt_ego                # ellipsoid_interact.py:80-89
+
+    def normalize(self, x):
+        return x                                                  # ellipsoid_interact.py:91-99
+
+    def _constraint_limits(self):
+        return 1, None                                            # ellipsoid_interact.py:104-112
+
+    def _num_constraints(self, ado_ids) -> int:
+        num_modes = min(constants.CONSTRAINT_ELLIPSOID_NUM_MODES, self._env.num_modes)
+        return num_modes * (self._env.num_ados if ado_ids is None else len(ado_ids)) * self.t_horizon
+
+    @property
+    def name(self) -> str:
+        return "ellipsoid_interaction"
+
+
 # `mantrap.modules.baselines.*` of the reference (modules/baselines/__init__.py:1-5)
 import types as _types  # noqa: E402
 
 baselines = _types.SimpleNamespace(InteractionAccelerationModule=InteractionAccelerationModule,
                                    InteractionVelocityModule=InteractionVelocityModule,
-                                   InteractionPositionModule=InteractionPositionModule)
+                                   InteractionPositionModule=InteractionPositionModule,
+                                   InteractionEllipsoidModule=InteractionEllipsoidModule)
 base = _types.SimpleNamespace(OptimizationModule=OptimizationModule, PureObjectiveModule=PureObjectiveModule,
                               PureConstraintModule=PureConstraintModule)

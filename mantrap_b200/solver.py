@@ -150,11 +150,13 @@ class TrajOptSolver:
             spec.control_limits |= one.control_limits
             spec.speed_limits |= one.speed_limits
             spec.min_distance |= one.min_distance
+            spec.ellipsoid |= one.ellipsoid
             if one.control_limits:
                 spec.u_max = one.u_max
             if one.speed_limits:
                 spec.v_max = one.v_max
         if len(ado_ids) == 0:                       # interaction objectives are undefined without ados (-> 0)
+            spec.ellipsoid = False                  # ellipsoid_interact.py:37-38: no rows
             for key in ("acc", "vel", "pos", "prob"):
                 spec.weights.pop(key, None)
         return spec
@@ -196,11 +198,13 @@ class TrajOptSolver:
         return out
 
     def _split_rows(self, rows: np.ndarray, ado_ids, spec: ModuleSpec) -> typing.Dict[str, np.ndarray]:
-        """Kernel row order (control | speed | min-distance) -> per module, min-distance restricted to `ado_ids`."""
+        """Kernel row order (control | speed | min-distance | ellipsoid) -> per module, min-distance restricted to
+        `ado_ids` (the ellipsoid rows cover every ado, like the reference's core)."""
         t_hor, n = self.planning_horizon, self.env.num_ados
         out, base = {}, 0
         for flag, count, name in (("control_limits", 2 * t_hor if self.env.ego.ego_kind == "double" else t_hor, "control_limits"),
-                                  ("speed_limits", 2 * (t_hor + 1), "speed_limits"), ("min_distance", n * t_hor, "min_distance")):
+                                  ("speed_limits", 2 * (t_hor + 1), "speed_limits"), ("min_distance", n * t_hor, "min_distance"),
+                                  ("ellipsoid", n * t_hor, "ellipsoid_interaction")):
             if not getattr(spec, flag):
                 continue
             block = rows[base:base + count]

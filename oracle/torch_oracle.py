@@ -414,3 +414,81 @@ def min_distance_jacobian(scene: Scene, controls: torch.Tensor):
         gr = torch.autograd.grad(g[i], controls, retain_graph=True, allow_unused=True)[0]
         rows.append(torch.zeros_like(controls).flatten() if gr is None else gr.flatten())
     return g.detach(), torch.nan_to_num(torch.stack(rows))
+
+
+###########################################################################
+# Ellipsoid constraint, attention filters, closed-loop step ###############
+###########################################################################
+ELLIPSOID_MIN_SCALE = 0.01               # modules/baselines/ellipsoid_interact.py:52
+ATTENTION_RADIUS = 4.0                   # constants.py:111-112
+
+
+def ellipsoid_raw(ego_traj, mus, sigmas, env_kind: str = "sf"):
+    """`InteractionEllipsoidModule._constraint_core` (modules/baselines/ellipsoid_interact.py:28-57) with the one "mode"
+    the particle environments have: sum_xy (ego_p(t) - mu_p[k,t])^2 / clamp(scale[k,t], min=0.01), means and scales
+    DETACHED (:74-75). scale = `distribution.stddev` of the positional distribution = the velocity variance for the
+    particle environments (particle.py:177-183), var_initial + Q t for Kalman (kalman.py:79-92).
+    ego_traj [B,T+1,4], mus [B,N,T,4], sigmas [B,N,T,2] -> [B,N,T]."""
+    t_horizon = mus.shape[2]
+    if env_kind == "kalman":
+        sigmas = kalman_pos_sigma(mus.shape[0], mus.shape[1], t_horizon).to(mus.dtype)
+    scale = sigmas.detach().clamp(min=ELLIPSOID_MIN_SCALE)
+    dxy = ego_traj[:, None, :t_horizon, 0:2] - mus[..., 0:2].detach()
+    return (dxy.pow(2) / scale).sum(dim=-1)
+
+
+def ellipsoid_jacobian(scene: Scene, controls: torch.Tensor):
+    """Row-by-row autograd Jacobian of the ellipsoid rows (optimization_module.py:428-434). controls [1,T,2] ->
+    g [N*T], jac [N*T, 2T]."""
+    controls = controls.detach().clone().requires_grad_(True)
+    ego_traj = ego_unroll(scene.ego0, controls, scene.dt, scene.ego_kind)
+    mus, sigmas = rollout(scene.env_kind, scene.ado0, scene.goal, scene.v0, scene.sigma, scene.weights,
+                          scene.noise, ego_traj, scene.dt)
+    g = ellipsoid_raw(ego_traj, mus, sigmas, scene.env_kind)[0].flatten()
+    rows = []
+    for i in range(g.numel()):
+        gr = torch.autograd.grad(g[i], controls, retain_graph=True, allow_unused=True)[0]
+        rows.append(torch.zeros_like(controls).flatten() if gr is None else gr.flatten())
+    return g.detach(), torch.nan_to_num(torch.stack(rows))
+
+
+def attention_mask(kind: str, ego0: torch.Tensor, ado0: torch.Tensor, radius: float = ATTENTION_RADIUS) -> torch.Tensor:
+    """`EuclideanModule._compute` (attention/euclidean.py:22-29) / `ClosestModule._compute` (attention/closest.py:22-31)
+    as 0/1 masks. ego0 [B,4], ado0 [B,N,4] -> uint8 [B,N]. The closest filter writes inf at `~index_min` with
+    index_min a 0-dim integer tensor, i.e. at index -(index_min + 1) (bitwise not), exactly as the reference does."""
+    out = torch.zeros(ado0.shape[0:2], dtype=torch.uint8)
+    for b in range(ado0.shape[0]):
+        distances = torch.norm(ado0[b, :, 0:2] - ego0[b, 0:2], dim=1)
+        if kind == "closest":
+            index_min = torch.argmin(distances)
+            distances[~index_min] = np.inf
+        out[b] = (distances < radius).to(torch.uint8)
+    return out
+
+
+def _clamp_action(u: torch.Tensor, limit: float, per_component: bool) -> torch.Tensor:
+    """`DTAgent.make_controls_feasible` (agents/base/discrete.py:358-370)."""
+    norm = u.abs() if per_component else torch.norm(u, dim=-1, keepdim=True)
+    return u / norm.clamp(min=1e-6) * norm.clamp(-limit, limit)
+
+
+def env_step(ego_kind: str, dt: float, ego0: torch.Tensor, ado0: torch.Tensor, action: torch.Tensor,
+             eps: typing.Optional[torch.Tensor]):
+    """`GraphBasedEnvironment.step` (environment/base/graph_based.py:82-124) for a batch of scenes.
+    ego0 [B,4], ado0 [B,N,4], action [B,2], eps [B,N,2] standard-normal draws behind `Normal.sample` -> next (ego, ados).
+
+    The ego executes the (clamped) action with its own dynamics (discrete.py:144-167). A one-control rollout performs no
+    particle step (particle.py:140-181, t_horizon = 1), so every ado samples its velocity from Normal(loc = v, scale =
+    ENV_VAR_INITIAL), moves to p + dt sample (`integrate_numerical`), and is updated through its inverse dynamics:
+    action = (p' - p) / dt, clamped to the pedestrian speed limit, v' = action, p' = p + action dt."""
+    if ego_kind == "double":
+        u = _clamp_action(action, ROBOT_ACC_MAX, per_component=True)
+        ego = torch.cat((ego0[:, 0:2] + dt * ego0[:, 2:4], ego0[:, 2:4] + dt * u), dim=1)
+    else:
+        u = _clamp_action(action, ROBOT_SPEED_MAX, per_component=False)
+        ego = torch.cat((ego0[:, 0:2] + dt * u, u), dim=1)
+    sample = ado0[..., 2:4] if eps is None else ado0[..., 2:4] + ENV_VAR_INITIAL * eps
+    pos = ado0[..., 0:2] + sample * dt
+    act = _clamp_action((pos - ado0[..., 0:2]) / dt, PED_SPEED_MAX, per_component=False)
+    ados = torch.cat((ado0[..., 0:2] + act * dt, act), dim=-1)
+    return ego, ados

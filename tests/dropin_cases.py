@@ -148,6 +148,20 @@ def check_modules(name):
             assert all((x is None and np.isnan(r)) or (x is not None and abs(x - r) < 1e-6) for x, r in zip(got, ref))
         structure = module.jacobian_structure(ado_ids=ado_ids, tag="g")                      # test_modules.py:290-306
         assert set(np.nonzero(g[f"jac_{key}"])[0]) <= set(structure.tolist())
+    # InteractionEllipsoidModule (modules/baselines/ellipsoid_interact.py), the reference's call sequence and seeds
+    module = modules.baselines.InteractionEllipsoidModule(env=env, t_horizon=t_hor, num_particles=num_p)
+    u = controls.clone().requires_grad_(True)
+    traj = env.ego.unroll_trajectory(u, dt=env.dt)
+    torch.manual_seed(int(g["seed"]))
+    gio.assert_parity(module.constraint(traj, ado_ids=ado_ids, tag="g"), g["con_ellipsoid"], gio.RTOL_ROLLOUT, "ellipsoid rows")
+    torch.manual_seed(int(g["seed"]))
+    gio.assert_parity(module.jacobian(traj, grad_wrt=u, ado_ids=ado_ids, tag="g"), g["jac_ellipsoid"], gio.RTOL_GRAD, "jacobian ellipsoid")
+    torch.manual_seed(int(g["seed"]))
+    gio.assert_parity(module.compute_violation(traj, ado_ids=ado_ids, tag="g"), g["vio_ellipsoid"], 1e-4, "violation ellipsoid", atol=1e-6)
+    lower, upper = module.constraint_boundaries(ado_ids=ado_ids)
+    assert lower == g["lb_ellipsoid"].tolist() and all(x is None for x in upper) and len(upper) == module.num_constraints(ado_ids)
+    assert module.constraint(traj, ado_ids=[], tag="g").size == 0 and module.jacobian(traj, grad_wrt=u, ado_ids=[], tag="g").size == 0
+    assert module.name == "ellipsoid_interaction" and module.normalize(3.0) == 3.0
     if "con_min_distance" in g:
         module = modules.MinDistanceModule(env=env, t_horizon=t_hor, num_particles=num_p)
         u = controls.clone().requires_grad_(True)
@@ -163,6 +177,28 @@ def check_modules(name):
                           "jacobian min distance (ado subset)")
         assert module.num_constraints(ado_ids[1:3]) == 2 * t_hor
         assert module.constraint_boundaries(ado_ids)[0][0] == 0.5 and module.constraint_boundaries(ado_ids)[1][0] is None
+
+
+def check_attention():
+    """mantrap_b200.attention.{EuclideanModule, ClosestModule}.compute() against the reference's filters on the recorded
+    scenes (ids of the selected ados), and as the `attention_module` of a solver."""
+    from mantrap_b200 import attention
+    g = gio.load("scene_ops")
+    for i in range(len(g["att_n"])):
+        n = int(g["att_n"][i])
+        env = environment.PotentialFieldEnvironment(ego_position=gio.t(g["att_ego"][i][0:2]), ego_velocity=torch.zeros(2),
+                                                    ego_type=agents.DoubleIntegratorDTAgent, dt=0.4)
+        for k in range(n):
+            env.add_ado(position=gio.t(g["att_ado"][i][k, 0:2]), velocity=torch.zeros(2), identifier=f"a{k:02d}")
+        for key, cls in (("euclidean", attention.EuclideanModule), ("closest", attention.ClosestModule)):
+            module = cls(env=env, t_horizon=5)
+            expect = [env.ado_ids[m] for m in np.nonzero(g[f"att_{key}"][i][:n])[0]]
+            assert module.compute() == expect == module.ids_current and module.name == key
+    env, goal = small_scene("sf")
+    sol = solver.RandomSearch(env, goal=goal, t_planning=4, attention_module=attention.EuclideanModule,
+                              modules=[modules.GoalNormModule, modules.InteractionAccelerationModule, modules.ControlLimitModule])
+    z = sol.optimize(torch.zeros(8), tag="t", num_candidates=8, max_rounds=1)
+    assert z.numel() == 8 and sol._attention_module.ids_current == attention.EuclideanModule(env=sol.env, t_horizon=4).compute()
 
 
 def check_autograd_route(name):

@@ -177,6 +177,24 @@ def generate(name, case):
         out[f"lb_{key}"] = np.array([np.nan if x is None else x for x in lower], dtype=np.float64)
         out[f"ub_{key}"] = np.array([np.nan if x is None else x for x in upper], dtype=np.float64)
 
+    # InteractionEllipsoidModule (modules/baselines/ellipsoid_interact.py): one particle draw per call, pinned.
+    module = mantrap.modules.baselines.InteractionEllipsoidModule(env=env, t_horizon=t_hor)
+    u = controls.clone().requires_grad_(True)
+    traj = env.ego.unroll_trajectory(u, dt=env.dt)
+    torch.manual_seed(case["seed"])
+    out["con_ellipsoid"] = np.asarray(module.constraint(traj, ado_ids=ado_ids, tag="g"), dtype=np.float64)
+    torch.manual_seed(case["seed"])
+    out["jac_ellipsoid"] = np.asarray(module.jacobian(traj, grad_wrt=u, ado_ids=ado_ids, tag="g"), dtype=np.float64)
+    torch.manual_seed(case["seed"])
+    out["vio_ellipsoid"] = np.float64(module.compute_violation(traj, ado_ids=ado_ids, tag="g"))
+    lower, upper = module.constraint_boundaries(ado_ids=ado_ids)
+    out["lb_ellipsoid"] = np.array([np.nan if x is None else x for x in lower], dtype=np.float64)
+    out["ub_ellipsoid"] = np.array([np.nan if x is None else x for x in upper], dtype=np.float64)
+
+    # attention filters (mantrap/attention): selected ado indices at the current states.
+    for key, cls in (("euclidean", mantrap.attention.EuclideanModule), ("closest", mantrap.attention.ClosestModule)):
+        out[f"att_{key}"] = np.asarray(cls(env=env, t_horizon=t_hor)._compute(), dtype=np.int64)
+
     # MinDistance: the module does not exist at this commit. Compose reference pieces only:
     # reference positional rollout + torch.norm + OptimizationModule.compute_gradient_auto_grad.
     if "min_distance" in case["modules"]:
@@ -227,8 +245,85 @@ def generate_agent_kats():
     print("agent_kats: ok")
 
 
+def generate_scene_ops():
+    """Attention filters and the closed-loop environment step of the reference on random scenes -> scene_ops.npz.
+
+    attention: 48 scenes (N = 1..8 ados within a few metres of the ego so that the 4 m radius and the `~argmin` quirk of
+    closest.py:27 are exercised), outputs = 0/1 masks from `EuclideanModule._compute` / `ClosestModule._compute`.
+    step: 6 scenes x 5 consecutive `env.step(action)` calls (graph_based.py:82-124) under a pinned seed; the standard-normal
+    draws behind `Normal.sample` are re-drawn with the same generator sequence (particle parameters first)
+    and stored, so the device step can be fed the identical numbers."""
+    mantrap = rh.import_reference()
+    rng = np.random.RandomState(2024)
+    att = dict(att_n=[], att_ego=[], att_ado=[], att_euclidean=[], att_closest=[])
+    for case_id in range(48):
+        n = 1 + case_id % 8
+        ego = np.array([*rng.uniform(-3, 3, 2), 0.0, 0.0], dtype=np.float32)
+        ados = np.zeros((8, 4), dtype=np.float32)
+        ados[:n, 0:2] = ego[0:2] + rng.uniform(-6, 6, (n, 2))
+        if case_id % 6 == 5 and n >= 2:
+            ados[1, 0:2] = 2 * ego[0:2] - ados[0, 0:2]      # exact tie of the two smallest distances
+        scene = dict(env="pf", ego_kind="double", ego_pos=ego[0:2].tolist(), ego_vel=(0, 0), dt=0.4,
+                     ados=[dict(pos=a[0:2].tolist(), vel=(0, 0), goal=(0, 0)) for a in ados[:n]])
+        env = rh.build_env(scene)
+        masks = {}
+        for key, cls in (("euclidean", mantrap.attention.EuclideanModule), ("closest", mantrap.attention.ClosestModule)):
+            idx = np.asarray(cls(env=env, t_horizon=5)._compute(), dtype=np.int64)
+            masks[key] = np.zeros(8, dtype=np.uint8)
+            masks[key][idx] = 1
+        att["att_n"].append(n)
+        att["att_ego"].append(ego)
+        att["att_ado"].append(ados)
+        att["att_euclidean"].append(masks["euclidean"])
+        att["att_closest"].append(masks["closest"])
+    out = {k: np.stack(v) if k != "att_n" else np.array(v, dtype=np.int64) for k, v in att.items()}
+
+    steps = 5
+    step = dict(step_env=[], step_ego_kind=[], step_n=[], step_seed=[], step_ego0=[], step_ado0=[], step_actions=[],
+                step_eps=[], step_ego_states=[], step_ado_states=[])
+    for case_id, (env_kind, ego_kind, n) in enumerate((("sf", "double", 3), ("sf", "single", 4), ("pf", "double", 5),
+                                                       ("pf", "single", 2), ("kalman", "double", 3), ("sf", "double", 6))):
+        ego = np.array([*rng.uniform(-4, 4, 2), *rng.uniform(-1, 1, 2)], dtype=np.float32)
+        ados = np.zeros((n, 6), dtype=np.float32)
+        ados[:, 0:2] = rng.uniform(-8, 8, (n, 2))
+        ados[:, 2:4] = rng.uniform(-1.5, 1.5, (n, 2))
+        ados[:, 4:6] = rng.uniform(-8, 8, (n, 2))
+        if case_id == 5:
+            ados[0, 2:4] = (2.4, 1.9)                          # faster than PED_SPEED_MAX: the update clamps the action
+        scene = dict(env=env_kind, ego_kind=ego_kind, ego_pos=ego[0:2].tolist(), ego_vel=ego[2:4].tolist(), dt=0.4,
+                     ados=[dict(pos=a[0:2].tolist(), vel=a[2:4].tolist(), goal=a[4:6].tolist()) for a in ados])
+        env = rh.build_env(scene)
+        actions = rng.uniform(-3.0 if case_id == 5 else -2.0, 3.0 if case_id == 5 else 2.0, (steps, 2)).astype(np.float32)
+        seed = 4000 + case_id
+        eps_all, ego_states, ado_states = [], [], []
+        for k in range(steps):
+            # the draws of this step: particle parameters of the one-control rollout first, then one Normal.sample per ado
+            if env_kind != "kalman":
+                rh.redraw_params(env_kind, n, 5, 0, seed + k)
+            else:
+                torch.manual_seed(seed + k)
+            eps = torch.stack([torch.randn((1, 1, 1, 2)) for _ in range(n)]).view(n, 2)
+            torch.manual_seed(seed + k)
+            ado_next, ego_next = env.step(torch.tensor(actions[k]))
+            eps_all.append(rh.to_np(eps))
+            ego_states.append(rh.to_np(ego_next)[0:4])
+            ado_states.append(rh.to_np(ado_next)[:, 0:4])
+        for key, val in (("step_env", env_kind), ("step_ego_kind", ego_kind), ("step_n", n), ("step_seed", seed),
+                         ("step_ego0", ego), ("step_ado0", np.pad(ados[:, 0:4], ((0, 6 - n), (0, 0)))),
+                         ("step_actions", actions), ("step_eps", np.pad(np.stack(eps_all), ((0, 0), (0, 6 - n), (0, 0)))),
+                         ("step_ego_states", np.stack(ego_states)),
+                         ("step_ado_states", np.pad(np.stack(ado_states), ((0, 0), (0, 6 - n), (0, 0))))):
+            step[key].append(val)
+    out.update({k: np.array(v) if isinstance(v[0], (str, int)) else np.stack(v) for k, v in step.items()})
+    np.savez_compressed(os.path.join(HERE, "scene_ops.npz"), **out)
+    print("scene_ops: attention selected", int(out["att_euclidean"].sum()), "/", int(out["att_closest"].sum()),
+          "steps", out["step_ego_states"].shape)
+
+
 if __name__ == "__main__":
     only = sys.argv[1:]
+    if not only or "scene_ops" in only:
+        generate_scene_ops()
     if not only or "agent_kats" in only:
         generate_agent_kats()
     for case_name, case_spec in CASES.items():

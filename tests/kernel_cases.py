@@ -320,3 +320,177 @@ def check_batched_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_can
         to.violation(ref_cons[:, n_ctl + n_spd:], to.MIN_L2_DISTANCE, None)
     gio.assert_parity(np_(res["violation"]).reshape(b), vio, 1e-4, "violation", atol=1e-5)
     return res, ref, stats
+
+
+def check_ellipsoid_golden(lib, device, name):
+    """InteractionEllipsoidModule rows (values + violation from the evaluation kernel, Jacobian from the tangent kernel)
+    against the reference module's `constraint`, `compute_violation` and `jacobian` on the pinned draw."""
+    g = gio.load(name)
+    scene = scene_from_golden(g, device)
+    t_hor, n = int(g["T"]), g["ado0"].shape[0]
+    controls = gio.t(g["controls"])[None, None].to(device).contiguous()
+    spec = engine.ModuleSpec(ellipsoid=True)
+    res = engine.launch_evaluate(lib, scene, controls, spec, want=("cons", "violation"))
+    jac = engine.launch_jacobian(lib, scene, controls, spec)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    assert res["cons"].shape == (1, 1, n * t_hor) and jac.shape == (1, 1, n * t_hor, 2 * t_hor)
+    gio.assert_parity(np_(res["cons"][0, 0]), g["con_ellipsoid"], gio.RTOL_ROLLOUT, "ellipsoid rows")
+    gio.assert_parity(np_(res["violation"][0, 0]), g["vio_ellipsoid"], 1e-4, "ellipsoid violation", atol=1e-6)
+    if str(g["env"]) == "kalman":
+        # the reference reports zeros for a non-differentiable environment (optimization_module.py:298-301; the host module
+        # does the same); the kernel's rows are the true derivative through the ego rollout -> compare with the oracle
+        from oracle import torch_oracle as to
+        assert not np.any(g["jac_ellipsoid"])
+        _, j_ref = to.ellipsoid_jacobian(oracle_scene_from_golden(g), gio.t(g["controls"])[None])
+        gio.assert_parity(np_(jac[0, 0]), j_ref.numpy(), gio.RTOL_GRAD, "jac ellipsoid (kalman, oracle)")
+    else:
+        gio.assert_parity(np_(jac[0, 0]).flatten(), g["jac_ellipsoid"], gio.RTOL_GRAD, "jac ellipsoid")
+    # ... and after the other row blocks, in the documented order control | speed | min-distance | ellipsoid
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True, ellipsoid=True)
+    res2 = engine.launch_evaluate(lib, scene, controls, spec, want=("cons",))
+    jac2 = engine.launch_jacobian(lib, scene, controls, spec)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    assert torch.equal(res2["cons"][0, 0, -n * t_hor:], res["cons"][0, 0])
+    assert torch.equal(jac2[0, 0, -n * t_hor:], jac[0, 0])
+
+
+def check_ellipsoid_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, seed=0):
+    """Random batch: ellipsoid rows, violation and Jacobian vs. the CPU oracle (row-by-row autograd). Controls are scaled so
+    that some trajectories pass through ellipsoids (non-zero violation)."""
+    from oracle import torch_oracle as to
+    from mantrap_b200 import scenarios
+    scene_cpu = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=900 + seed,
+                                           param_seed=950 + seed, regular_sigma=True)
+    scene_cpu.ado0[:, 0, 0:2] = scene_cpu.ego0[:, 0:2] + 0.05          # one ado on top of the ego: rows below the bound
+    controls_cpu = scenarios.candidate_controls(num_scenes, num_candidates, t_hor, seed=970 + seed, u_max=1.0)
+    spec = engine.ModuleSpec(ellipsoid=True)
+    res = engine.launch_evaluate(lib, scene_cpu.to(device), controls_cpu.to(device).contiguous(), spec, want=("cons", "violation"))
+    jac = engine.launch_jacobian(lib, scene_cpu.to(device), controls_cpu.to(device).contiguous(), spec)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    cons, vio, jac = np_(res["cons"]), np_(res["violation"]), np_(jac)
+    osc = oracle_scene(scene_cpu, num_candidates)
+    any_violation = False
+    for b in range(num_scenes * num_candidates):
+        one = to.Scene(*[(x[b:b + 1] if isinstance(x, torch.Tensor) else x) for x in osc])
+        u = controls_cpu.reshape(-1, t_hor, 2)[b:b + 1]
+        g_ref, j_ref = to.ellipsoid_jacobian(one, u)
+        g64, j64 = to.ellipsoid_jacobian(to.scene_to(one, torch.float64), u.double())
+        f_val, f_jac = float((g_ref.double() - g64).abs().max()), float((j_ref.double() - j64).abs().max())
+        sc, c = divmod(b, num_candidates)
+        gio.assert_parity(cons[sc, c], g_ref.numpy(), gio.RTOL_ROLLOUT, "ellipsoid rows", atol=gio.ATOL + 2 * f_val)
+        gio.assert_parity(jac[sc, c], j_ref.numpy(), gio.RTOL_GRAD, "jac ellipsoid", atol=gio.ATOL + 2 * f_jac)
+        v_ref = float(to.violation(g_ref.numpy()[None], 1.0, None)[0])
+        any_violation |= v_ref > 0
+        gio.assert_parity(vio[sc, c], v_ref, 1e-4, "ellipsoid violation", atol=1e-5 + 2 * f_val * n * t_hor)
+    assert any_violation
+
+
+def check_attention_golden(lib, device):
+    """Attention masks against the reference's EuclideanModule / ClosestModule on the 48 recorded scenes (bit-exact), one
+    launch per ado count, plus the oracle on a large random batch."""
+    from oracle import torch_oracle as to
+    g = gio.load("scene_ops")
+    for n in sorted(set(g["att_n"].tolist())):
+        sel = np.nonzero(g["att_n"] == n)[0]
+        ego0 = gio.t(g["att_ego"][sel]).to(device).contiguous()
+        ado0 = gio.t(g["att_ado"][sel][:, :n]).to(device).contiguous()
+        for kind in ("euclidean", "closest"):
+            mask = engine.launch_attention(lib, kind, ego0, ado0, 4.0)
+            if device != "cpu":
+                torch.cuda.synchronize()
+            assert np.array_equal(np_(mask), g[f"att_{kind}"][sel][:, :n]), (kind, n)
+    gen = torch.Generator().manual_seed(5)
+    for s, n in ((257, 20), (64, 64), (33, 1), (40, 33)):
+        ego0 = torch.cat((torch.rand((s, 2), generator=gen) * 10 - 5, torch.zeros((s, 2))), dim=1)
+        ado0 = torch.cat((torch.rand((s, n, 2), generator=gen) * 14 - 7, torch.zeros((s, n, 2))), dim=2)
+        for kind in ("euclidean", "closest"):
+            mask = engine.launch_attention(lib, kind, ego0.to(device).contiguous(), ado0.to(device).contiguous(), 4.0)
+            if device != "cpu":
+                torch.cuda.synchronize()
+            assert np.array_equal(np_(mask), to.attention_mask(kind, ego0, ado0).numpy()), (kind, s, n)
+
+
+def check_env_step_golden(lib, device):
+    """Closed-loop step kernel against five consecutive `env.step` calls of the reference per recorded scene (fed the same
+    standard-normal draws), and the warm-start shift."""
+    g = gio.load("scene_ops")
+    for c in range(len(g["step_n"])):
+        n, ego_kind = int(g["step_n"][c]), str(g["step_ego_kind"][c])
+        scene = engine.SceneBatch(env_kind="kalman", ego_kind=ego_kind, dt=0.4, ego0=gio.t(g["step_ego0"][c])[None].clone(),
+                                  ego_goal=None, ado0=gio.t(g["step_ado0"][c][:n])[None].clone()).to(device)
+        for k in range(g["step_actions"].shape[1]):
+            t_hor = 3
+            controls = torch.zeros((1, t_hor, 2))
+            controls[0, 0] = gio.t(g["step_actions"][c][k])
+            controls[0, 1:] = torch.tensor([[1.0, 2.0], [3.0, 4.0]])
+            warm = torch.full((1, t_hor, 2), -7.0).to(device)
+            eps = gio.t(g["step_eps"][c][k][:n])[None].to(device).contiguous()
+            engine.launch_env_step(lib, scene, controls.to(device).contiguous(), eps, warm)
+            if device != "cpu":
+                torch.cuda.synchronize()
+            gio.assert_parity(np_(scene.ego0[0]), g["step_ego_states"][c][k], gio.RTOL_ROLLOUT, f"ego state {c}/{k}")
+            gio.assert_parity(np_(scene.ado0[0]), g["step_ado_states"][c][k][:n], gio.RTOL_ROLLOUT, f"ado states {c}/{k}")
+            assert np_(warm[0]).tolist() == [[1.0, 2.0], [3.0, 4.0], [0.0, 0.0]]
+
+
+def check_closed_loop(lib, device, env_kind="sf", ego_kind="double", num_scenes=3, n=4, p=3, t_hor=5, num_candidates=6,
+                      steps=3, attention=None):
+    """Batched closed-loop MPC (`mantrap_b200.mpc.BatchedClosedLoop`: attention -> baseline -> candidates -> argmin -> step)
+    against a per-scene loop over the CPU oracle fed the same candidates and standard-normal draws."""
+    from oracle import torch_oracle as to
+    from mantrap_b200 import mpc, scenarios
+    eng = engine.Engine.from_library(lib, device) if device == "cpu" else engine.Engine(device)
+    scene_cpu = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=77, param_seed=78,
+                                           regular_sigma=True)
+    scene_cpu.ego_goal = scene_cpu.ego0[:, 0:2] + torch.tensor([[0.6, 0.3]])           # close goals: some scenes finish early
+    scene_cpu.ego_goal[-1] += 6.0
+    scene_cpu.ado0[:, 0, 0:2] = scene_cpu.ego0[:, 0:2] + 1.5                            # one ado inside the attention radius
+    gen = torch.Generator().manual_seed(9)
+    candidates = [(torch.rand((num_scenes, num_candidates, t_hor, 2), generator=gen) * 2 - 1) * 2.0 for _ in range(steps)]
+    eps = [torch.randn((num_scenes, n, 2), generator=gen) for _ in range(steps)]
+    weights = {"goal": 0.5, "acc": 1.0}
+    loop = mpc.BatchedClosedLoop(eng, scene_cpu, t_planning=t_hor, weights=weights, num_candidates=num_candidates, attention=attention)
+    out = loop.solve(steps, candidates=candidates, eps=eps)
+    if device != "cpu":
+        torch.cuda.synchronize()
+
+    for sc in range(num_scenes):
+        ego, ado = scene_cpu.ego0[sc:sc + 1].clone(), scene_cpu.ado0[sc:sc + 1].clone()
+        warm = torch.zeros((t_hor, 2))
+        done_at = steps
+        for k in range(steps):
+            cand = candidates[k][sc].clone()
+            cand[0] = warm
+            rep = lambda x: x[sc:sc + 1].expand(num_candidates, *x.shape[1:])
+            osc = to.Scene(env_kind, ego_kind, scene_cpu.dt, ego.expand(num_candidates, -1), rep(scene_cpu.ego_goal),
+                           ado.expand(num_candidates, -1, -1), rep(scene_cpu.ado_goal), rep(scene_cpu.v0), rep(scene_cpu.sigma),
+                           rep(scene_cpu.weight), None)
+            mask = None
+            if attention is not None:
+                mask = to.attention_mask(attention, ego, ado).bool().expand(num_candidates, -1)
+            mus_wo, _ = to.rollout(env_kind, osc.ado0[:1], osc.goal[:1], osc.v0[:1], osc.sigma[:1], osc.weights[:1], None, t_hor, osc.dt)
+            res = to.evaluate(osc, cand, mus_wo.expand(num_candidates, -1, -1, -1), weights, ado_mask=mask, want_grad=False)
+            vio = to.violation(to.control_limit_raw(res["ego_traj"], osc.dt, ego_kind).numpy() / to.ROBOT_ACC_MAX, None, 1.0) + \
+                to.violation(to.speed_limit_raw(res["ego_traj"]).numpy() / to.ROBOT_SPEED_MAX, -1.0, 1.0)
+            total = res["total"].numpy().copy()
+            feasible = vio < 1e-3
+            idx = int(np.argmin(np.where(feasible, total, np.inf))) if feasible.any() else -1
+            assert int(out.best_index[sc, k]) == idx, (sc, k, idx, total, vio)
+            best = cand[idx] if idx >= 0 else warm
+            gio.assert_parity(np_(out.objective[sc, k]), total[max(idx, 0)], gio.RTOL_ROLLOUT, "objective", atol=gio.ATOL_OBJ)
+            ego, ado = to.env_step(ego_kind, osc.dt, ego, ado, best[0:1], eps[k][sc:sc + 1])
+            warm = torch.cat((best[1:], torch.zeros((1, 2))))
+            gio.assert_parity(np_(out.ego_trajectory[sc, k + 1]), ego[0].numpy(), gio.RTOL_ROLLOUT, f"ego {sc}/{k}")
+            gio.assert_parity(np_(out.ado_trajectories[sc, :, k + 1]), ado[0].numpy(), gio.RTOL_ROLLOUT, f"ados {sc}/{k}")
+            gio.assert_parity(np_(out.controls[sc, k]), best[0].numpy(), gio.RTOL_ROLLOUT, f"control {sc}/{k}")
+            if float(torch.norm(ego[0, 0:2] - scene_cpu.ego_goal[sc])) < 0.5:
+                done_at = k + 1
+                break
+        assert int(out.steps[sc]) == done_at, (sc, int(out.steps[sc]), done_at)
+        # frozen after the goal
+        for k in range(done_at, steps):
+            assert torch.equal(out.ego_trajectory[sc, k + 1], out.ego_trajectory[sc, done_at])
+    return out

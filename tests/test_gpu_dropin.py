@@ -42,6 +42,10 @@ def test_solver_callbacks(name):
     dc.check_solver_callbacks(name)
 
 
+def test_attention():
+    dc.check_attention()
+
+
 def test_random_search():
     dc.check_random_search(4096)
 

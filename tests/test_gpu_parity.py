@@ -85,6 +85,56 @@ def test_seeded_adjoint(eng, env_kind, ego_kind, s, c, n, p, t_hor):
     kc.check_seeded_adjoint(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, seed=3)
 
 
+@pytest.mark.parametrize("name", gio.case_names())
+def test_ellipsoid_golden(eng, name):
+    kc.check_ellipsoid_golden(eng.lib, DEV, name)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 3, 4, 4, 3, 10),
+    ("sf", "double", 2, 3, 20, 3, 12),          # config-4 shape
+    ("sf", "single", 1, 2, 40, 8, 6),           # 320 particles: D = 4 Jacobian instantiation, large-block evaluation
+    ("pf", "single", 2, 5, 5, 5, 15),
+    ("kalman", "double", 1, 3, 5, 1, 15),
+])
+def test_ellipsoid_vs_oracle(eng, env_kind, ego_kind, s, c, n, p, t_hor):
+    kc.check_ellipsoid_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor)
+
+
+def test_attention(eng):
+    kc.check_attention_golden(eng.lib, DEV)
+
+
+def test_env_step(eng):
+    kc.check_env_step_golden(eng.lib, DEV)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,attention,s,n,c", [("sf", "double", None, 5, 6, 16), ("pf", "single", "euclidean", 4, 5, 8),
+                                                            ("sf", "double", "closest", 3, 20, 12)])
+def test_closed_loop(eng, env_kind, ego_kind, attention, s, n, c):
+    kc.check_closed_loop(eng.lib, DEV, env_kind=env_kind, ego_kind=ego_kind, attention=attention, num_scenes=s, n=n, num_candidates=c,
+                         steps=4)
+
+
+def test_closed_loop_full_size(eng):
+    """4096 ETH-shaped scenes x 64 candidates, 3 closed-loop steps on the device: every executed control is feasible, the ego
+    moves by its own dynamics, frozen scenes stay frozen, and the chosen plan is never worse than the warm start."""
+    from mantrap_b200 import mpc
+    s, n, p, t_hor, c = 4096, 20, 3, 12, 64
+    scene = scenarios.synthetic_scenes(s, n, p, regular_sigma=True)
+    loop = mpc.BatchedClosedLoop(eng, scene, t_planning=t_hor, num_candidates=c, attention="euclidean", seed=3)
+    out = loop.solve(3)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.ego_trajectory).all() and torch.isfinite(out.ado_trajectories).all()
+    assert float(out.controls.abs().max()) <= 2.0 + 1e-6
+    dt = scene.dt
+    x0, x1 = out.ego_trajectory[:, 0], out.ego_trajectory[:, 1]
+    assert torch.allclose(x1[:, 0:2], x0[:, 0:2] + dt * x0[:, 2:4], atol=1e-6)
+    assert torch.allclose(x1[:, 2:4], x0[:, 2:4] + dt * out.controls[:, 0], atol=1e-6)
+    speed = torch.norm(out.ado_trajectories[..., 2:4], dim=-1)
+    assert float(speed.max()) <= 2.5 + 1e-5
+
+
 def test_argmin(eng):
     total = torch.tensor([[3.0, 1.0, 2.0, 0.5], [4.0, -1.0, 5.0, 6.0], [1.0, 2.0, 3.0, 4.0]], device=DEV)
     vio = torch.tensor([[0.0, 0.0, 0.0, 1.0], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]], device=DEV)

@@ -80,6 +80,34 @@ def test_seeded_adjoint(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor):
     kc.check_seeded_adjoint(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, seed=3)
 
 
+@pytest.mark.parametrize("name", gio.case_names())
+def test_ellipsoid_golden(emul_lib, name):
+    kc.check_ellipsoid_golden(emul_lib, "cpu", name)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 2, 2, 4, 3, 6),
+    ("pf", "single", 1, 3, 5, 2, 5),
+    ("kalman", "double", 1, 2, 3, 1, 5),
+])
+def test_ellipsoid_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor):
+    kc.check_ellipsoid_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor)
+
+
+def test_attention(emul_lib):
+    kc.check_attention_golden(emul_lib, "cpu")
+
+
+def test_env_step(emul_lib):
+    kc.check_env_step_golden(emul_lib, "cpu")
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,attention", [("sf", "double", None), ("pf", "single", "euclidean"),
+                                                        ("sf", "double", "closest")])
+def test_closed_loop(emul_lib, env_kind, ego_kind, attention):
+    kc.check_closed_loop(emul_lib, "cpu", env_kind=env_kind, ego_kind=ego_kind, attention=attention)
+
+
 def test_argmin(emul_lib):
     total = torch.tensor([[3.0, 1.0, 2.0, 0.5], [4.0, -1.0, 5.0, 6.0], [1.0, 2.0, 3.0, 4.0]])
     vio = torch.tensor([[0.0, 0.0, 0.0, 1.0], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]])

@@ -120,3 +120,43 @@ def test_kalman_properties():
     assert torch.all(sigmas[0, :, 1:] >= sigmas[0, :, :-1])
     pos_sig = to.kalman_pos_sigma(1, 5, 15)
     assert math.isclose(float(pos_sig[0, 0, 3, 0]), 1e-6 + 0.6, rel_tol=1e-5)
+
+
+@pytest.mark.parametrize("name", gio.case_names())
+def test_ellipsoid(name):
+    """InteractionEllipsoidModule (modules/baselines/ellipsoid_interact.py): rows, violation, bounds and Jacobian."""
+    g = gio.load(name)
+    scene = scene_from_golden(g)
+    con, jac = to.ellipsoid_jacobian(scene, gio.t(g["controls"])[None])
+    gio.assert_parity(con.numpy(), g["con_ellipsoid"], gio.RTOL_ROLLOUT, "ellipsoid rows")
+    if scene.env_kind == "kalman":   # not differentiable w.r.t. the ego: the reference returns zeros (optimization_module.py:298-301)
+        assert not np.any(g["jac_ellipsoid"]) and g["jac_ellipsoid"].size == jac.numel()
+    else:
+        gio.assert_parity(jac.numpy().flatten(), g["jac_ellipsoid"], gio.RTOL_GRAD, "ellipsoid jacobian")
+    gio.assert_parity(to.violation(con.numpy()[None], 1.0, None)[0], g["vio_ellipsoid"], 1e-4, "ellipsoid violation", atol=1e-6)
+    assert np.all(g["lb_ellipsoid"] == 1.0) and np.all(np.isnan(g["ub_ellipsoid"]))
+
+
+def test_attention_filters():
+    """EuclideanModule / ClosestModule (mantrap/attention) on the recorded scenes, incl. the `~argmin` quirk and ties."""
+    g = gio.load("scene_ops")
+    quirk = 0
+    for i in range(len(g["att_n"])):
+        n = int(g["att_n"][i])
+        ego, ado = gio.t(g["att_ego"][i])[None], gio.t(g["att_ado"][i][:n])[None]
+        for kind in ("euclidean", "closest"):
+            assert np.array_equal(to.attention_mask(kind, ego, ado)[0].numpy(), g[f"att_{kind}"][i][:n]), (i, kind)
+        quirk += int(g["att_closest"][i].sum() > 1)
+    assert quirk > 0          # the closest filter keeps more than one ado in some scenes: the reference's behaviour
+
+
+def test_env_step():
+    """GraphBasedEnvironment.step, five consecutive steps per recorded scene, with the recorded standard-normal draws."""
+    g = gio.load("scene_ops")
+    for c in range(len(g["step_n"])):
+        n, ego_kind = int(g["step_n"][c]), str(g["step_ego_kind"][c])
+        ego, ado = gio.t(g["step_ego0"][c])[None], gio.t(g["step_ado0"][c][:n])[None]
+        for k in range(g["step_actions"].shape[1]):
+            ego, ado = to.env_step(ego_kind, 0.4, ego, ado, gio.t(g["step_actions"][c][k])[None], gio.t(g["step_eps"][c][k][:n])[None])
+            gio.assert_parity(ego[0].numpy(), g["step_ego_states"][c][k], gio.RTOL_ROLLOUT, f"ego {c}/{k}")
+            gio.assert_parity(ado[0].numpy(), g["step_ado_states"][c][k][:n], gio.RTOL_ROLLOUT, f"ados {c}/{k}")

@@ -39,9 +39,13 @@ def run(eng, env_kind, s, c, n, p, t_hor, weights, iters=5, grad=True):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--big", action="store_true")
+    ap.add_argument("--only", default="")
     args = ap.parse_args()
     eng = engine.Engine("cuda:0")
     w = {"goal": 0.5, "acc": 1.0}
+    if args.only == "c4":
+        run(eng, "sf", 2048, 256, 20, 3, 12, w)
+        sys.exit(0)
     run(eng, "sf", 1024, 256, 20, 3, 12, w)
     run(eng, "sf", 1024, 256, 20, 3, 12, w, grad=False)
     run(eng, "sf", 8192, 256, 20, 3, 12, w)
