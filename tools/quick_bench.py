@@ -36,6 +36,26 @@ def run(eng, env_kind, s, c, n, p, t_hor, weights, iters=5, grad=True):
     return ms
 
 
+def run_jacobian(eng, env_kind, s, c, n, p, t_hor, iters=5, ellipsoid=False):
+    """Constraint-Jacobian kernel (control | speed | min-distance [| ellipsoid] rows) on one shape."""
+    scene = scenarios.synthetic_scenes(s, n, p, env_kind=env_kind).to("cuda:0")
+    controls = scenarios.candidate_controls(s, c, t_hor).to("cuda:0")
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True, ellipsoid=ellipsoid)
+    jac = eng.constraint_jacobian(scene, controls, spec)
+    torch.cuda.synchronize()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(iters):
+        eng.constraint_jacobian(scene, controls, spec)
+    stop.record()
+    torch.cuda.synchronize()
+    ms = start.elapsed_time(stop) / iters
+    rows = jac.shape[2]
+    print(f"jacobian {env_kind} S={s} C={c} N={n} P={p} T={t_hor} rows={rows} cols={2 * t_hor}: {ms:.3f} ms/launch, "
+          f"{s * c / ms * 1e3:.3e} Jacobians/s, {jac.numel() * 4 / ms / 1e6:.1f} GB/s written", flush=True)
+    return ms
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--big", action="store_true")
@@ -45,6 +65,13 @@ if __name__ == "__main__":
     w = {"goal": 0.5, "acc": 1.0}
     if args.only == "c4":
         run(eng, "sf", 2048, 256, 20, 3, 12, w)
+        sys.exit(0)
+    if args.only == "jac":
+        run_jacobian(eng, "sf", 1024, 1, 10, 4, 20)
+        run_jacobian(eng, "sf", 1024, 16, 10, 4, 20)
+        run_jacobian(eng, "sf", 1024, 16, 10, 4, 20, ellipsoid=True)
+        run_jacobian(eng, "sf", 256, 16, 20, 3, 12)
+        run_jacobian(eng, "pf", 256, 64, 5, 5, 15)
         sys.exit(0)
     run(eng, "sf", 1024, 256, 20, 3, 12, w)
     run(eng, "sf", 1024, 256, 20, 3, 12, w, grad=False)
