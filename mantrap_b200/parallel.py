@@ -129,3 +129,39 @@ def sharded_search(engine, scene, controls: torch.Tensor, make_spec: typing.Call
     else:
         out = reduce_best_candidate_partitioned(val, idx, best, offset, group)
     return (*out, res)
+
+
+def sharded_closed_loop(engine, scene, time_steps: int, candidates: typing.Sequence[torch.Tensor] = None,
+                        eps: typing.Sequence[torch.Tensor] = None, group=None, **loop_kwargs):
+    """Scene-partitioned batched closed-loop MPC (`mpc.BatchedClosedLoop`, i.e. `TrajOptSolver.solve` for many scenes):
+    rank r advances the scenes `shard_range(S, r, world)` for `time_steps` steps with NO exchange during the loop (scenes
+    are independent), then ONE all-gather returns the trajectories of all scenes to every rank. `scene`, `candidates[k]`
+    [S,C,T,2] and `eps[k]` [S,N,2] describe the whole problem; with `candidates` / `eps` omitted every rank draws its own
+    (seeded by `seed` + rank). Returns a `ClosedLoopResult` over all S scenes."""
+    from . import mpc
+    rank, world = _world(group)
+    s_total = scene.num_scenes
+    lo, hi = shard_range(s_total, rank, world)
+    kwargs = dict(loop_kwargs)
+    kwargs["seed"] = kwargs.get("seed", 0) + rank
+    loop = mpc.BatchedClosedLoop(engine, slice_scene(scene, lo, hi), **kwargs)
+    out = loop.solve(time_steps, candidates=None if candidates is None else [c[lo:hi] for c in candidates],
+                     eps=None if eps is None else [e[lo:hi] for e in eps])
+    if world == 1:
+        return out
+    # one flat float32 row per scene: ego trajectory | ado trajectories | controls | objective | index | steps
+    n_loc = hi - lo
+    rows = torch.cat([out.ego_trajectory.reshape(n_loc, -1), out.ado_trajectories.reshape(n_loc, -1), out.controls.reshape(n_loc, -1),
+                      out.objective, out.best_index.to(torch.float32), out.steps.to(torch.float32)[:, None]], dim=1)
+    sizes = [shard_range(s_total, r, world) for r in range(world)]
+    width = max(b - a for a, b in sizes)
+    if n_loc < width:
+        rows = torch.cat((rows, rows.new_zeros((width - n_loc, rows.shape[1]))))
+    gathered = rows.new_empty((world * width, rows.shape[1]))
+    dist.all_gather_into_tensor(gathered, rows.contiguous(), group=group)
+    rows = torch.cat([gathered[r * width:r * width + (b - a)] for r, (a, b) in enumerate(sizes)])
+    k, n = time_steps, scene.num_ados
+    cuts = [4 * (k + 1), 4 * n * (k + 1), 2 * k, k, k, 1]
+    ego, ado, ctl, obj, idx, steps = torch.split(rows, cuts, dim=1)
+    return mpc.ClosedLoopResult(ego.reshape(s_total, k + 1, 4).contiguous(), ado.reshape(s_total, n, k + 1, 4).contiguous(),
+                                ctl.reshape(s_total, k, 2).contiguous(), obj.contiguous(), idx.to(torch.int32), steps[:, 0].to(torch.int32))

@@ -65,6 +65,34 @@ def _worker(rank, world, port, shape):
         dist.destroy_process_group()
 
 
+def _loop_worker(rank, world, port):
+    for path in (ROOT, HERE, os.path.join(HERE, "host_emul")):
+        if path not in sys.path:
+            sys.path.insert(0, path)
+    import build_emul
+    from mantrap_b200 import _cabi, engine, mpc, parallel
+    torch.set_num_threads(1)
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        eng = engine.Engine.from_library(_cabi.bind(ctypes.CDLL(build_emul.build())), "cpu")
+        s, c, n, p, t_hor, steps = 5, 4, 3, 2, 4, 2                            # ragged: 5 scenes over 2 ranks
+        scene, _ = _problem(s, c, n, p, t_hor)
+        gen = torch.Generator().manual_seed(21)
+        candidates = [(torch.rand((s, c, t_hor, 2), generator=gen) * 2 - 1) * 2.0 for _ in range(steps)]
+        eps = [torch.randn((s, n, 2), generator=gen) for _ in range(steps)]
+        kwargs = dict(t_planning=t_hor, num_candidates=c, attention="euclidean")
+        ref = mpc.BatchedClosedLoop(eng, scene, **kwargs).solve(steps, candidates=candidates, eps=eps)   # whole problem, one process
+        out = parallel.sharded_closed_loop(eng, scene, steps, candidates=candidates, eps=eps, **kwargs)
+        for a, b in zip(out, ref):
+            assert a.shape == b.shape and torch.equal(a, b)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_closed_loop_world2():
+    mp.spawn(_loop_worker, args=(2, _free_port()), nprocs=2, join=True)
+
+
 @pytest.mark.parametrize("shape", [(5, 6, 3, 2, 4), (2, 9, 4, 3, 5)])        # ragged: 5 scenes / 9 candidates over 2 ranks
 def test_sharded_search_world2(shape):
     mp.spawn(_worker, args=(2, _free_port(), shape), nprocs=2, join=True)
