@@ -185,6 +185,43 @@ def measure_peaks(eng, torch):
     return res
 
 
+def secondary_measurements(eng, torch, dev):
+    """Outside the timed region, N = 1 only: the two other kernels of the path on their BASELINE shapes, device-timed.
+    (a) config 3: dense constraint Jacobian (control | speed | min-distance rows) of SocialForces N=10 P=4 T=20;
+    (b) batched closed-loop MPC on the bench workload (attention -> baseline -> 256 candidates -> argmin -> step)."""
+    from mantrap_b200 import engine, mpc, scenarios
+    out = {}
+    scene = scenarios.synthetic_scenes(1024, 10, 4, seed=31, param_seed=32).to(dev)
+    controls = scenarios.candidate_controls(1024, 16, 20, seed=33).to(dev)
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True)
+    jac = eng.constraint_jacobian(scene, controls, spec)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    a.record()
+    for _ in range(3):
+        eng.constraint_jacobian(scene, controls, spec)
+    b.record()
+    torch.cuda.synchronize(dev)
+    ms = a.elapsed_time(b) / 3
+    out["jacobian_config3"] = {"value": 1024 * 16 / ms * 1e3, "unit": "Jacobians/s", "rows": int(jac.shape[2]), "cols": int(jac.shape[3]),
+                               "ms_per_launch": ms, "workload": "SocialForces N=10 P=4 T=20, 1024 scenes x 16 candidates, "
+                               "control + speed + min-distance rows (forward-mode tangent kernel)"}
+    s = 2048
+    loop = mpc.BatchedClosedLoop(eng, scenarios.synthetic_scenes(s, N_ADOS, N_PARTICLES, seed=41, param_seed=42), t_planning=T_HORIZON,
+                                 num_candidates=N_CANDIDATES, attention="euclidean", seed=5)
+    loop.solve(1)
+    torch.cuda.synchronize(dev)
+    a.record()
+    loop.solve(3)
+    b.record()
+    torch.cuda.synchronize(dev)
+    ms = a.elapsed_time(b) / 3
+    out["closed_loop"] = {"value": s / ms * 1e3, "unit": "scene-steps/s", "ms_per_step": ms,
+                          "workload": f"{s} ETH-shaped scenes in lock step, {N_CANDIDATES} candidates per scene and step, euclidean "
+                                      "attention, goal + interaction-acceleration objective, control + speed limits"}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -356,6 +393,8 @@ def main():
             "saturated_fraction": pair_stats[2] / evals_per_launch,
             "launch": eng.launch_info(scene, controls, True),
         }
+        if world == 1:
+            line["secondary"] = secondary_measurements(eng, torch, dev)
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         print(json.dumps(line), flush=True)

@@ -24,6 +24,7 @@ struct JParams {
     float* cons;
     float* jac;
     int T, N, P, G, GP, MW, n_chunks;
+    int E, per_item_f;               // work items per block (threads [e * G, (e + 1) * G) own item e), floats of shared memory per item
     long long num_items;
     int rows_control, rows_speed, rows_mind, rows_ell, R;
     float pair_cut2;
@@ -44,10 +45,15 @@ __global__ void __launch_bounds__(MAXT, MINB) jacobian_kernel(const JParams prm)
     MTB_SHARED_FLOAT4(smem4);
     float* sm = reinterpret_cast<float*>(smem4);
     const int T = prm.T, N = prm.N, P = prm.P, G = prm.G, R = prm.R;
-    const int g = threadIdx.x, nthreads = blockDim.x;
-    const bool active = g < G;
-    const int m = active ? g / P : 0;
-    const int i = g - m * P;
+    // A block holds E work items; item e is owned by the G consecutive threads [e * G, (e + 1) * G) (not warp aligned: the
+    // lanes a warp-padded group would leave idle are filled by the next item). All items of a block run the same T - 1
+    // steps, so the block-wide barriers are reached uniformly; threads beyond E * G and items beyond the end idle.
+    const int e = threadIdx.x / G;
+    const int g0 = threadIdx.x - e * G, nthreads = G;
+    const bool owner = e < prm.E;
+    sm += (owner ? e : 0) * prm.per_item_f;
+    const int m = g0 / P;
+    const int i = g0 - m * P;
     const float dt = prm.pb.dt;
     const float u_ped = prm.pb.ped_speed_max;
     const float inv_tau = 1.0f / prm.pb.sf_tau;
@@ -62,7 +68,12 @@ __global__ void __launch_bounds__(MAXT, MINB) jacobian_kernel(const JParams prm)
     float2* qd = reinterpret_cast<float2*>(sm + prm.off_qd);        // [GP][D]
     float2* varl = reinterpret_cast<float2*>(sm + prm.off_var);     // [2][N] scales of the two rotating levels (ellipsoid rows)
 
-    for (long long item = blockIdx.x; item < prm.num_items; item += gridDim.x) {
+    for (long long base = (long long)blockIdx.x * prm.E; base < prm.num_items; base += (long long)gridDim.x * prm.E) {
+        // idle threads (beyond E * G, or items beyond the end) only take part in the barriers: their strided loops are empty
+        const bool valid = owner && base + e < prm.num_items;
+        const long long item = valid ? base + e : prm.num_items - 1;
+        const bool active = valid;
+        const int g = valid ? g0 : (1 << 28);
         const size_t ev = (size_t)(item / prm.n_chunks);
         const int chunk = (int)(item - (long long)ev * prm.n_chunks);
         const int d0 = chunk * D;
@@ -374,14 +385,22 @@ static int plan_jacobian(const mtb_problem* pb, const mtb_modules* md, JParams& 
     smem = (size_t)off * sizeof(float);
     const DeviceLimits lim = device_limits();
     if (smem > (size_t)lim.max_smem) return MTB_ERR_TOO_LARGE;
-    block = prm.GP;
+    // items per block: fill ~128 threads with whole items of G threads each (G <= 128), else one item per block
+    prm.E = (prm.G <= 64) ? 128 / prm.G : 1;
+    if ((long long)prm.E > prm.num_items) prm.E = (int)prm.num_items;
+    prm.per_item_f = round_up(off, 4);
+    while (prm.E > 1 && (size_t)prm.E * prm.per_item_f * sizeof(float) > (size_t)48 * 1024) --prm.E;   // keep >= 4 blocks per SM
+    smem = (size_t)prm.E * prm.per_item_f * sizeof(float);
+    if (smem > (size_t)lim.max_smem) return MTB_ERR_TOO_LARGE;
+    block = round_up(prm.E * prm.G, 32);
     int per_sm = (int)((size_t)lim.smem_per_sm / (smem + 1024));
     const int by_threads = (prm.GP <= 256 ? 2048 : 1024) / block;      // register budget: 128 (D = 8) / 64 (large blocks)
     if (per_sm > by_threads) per_sm = by_threads;
     if (per_sm > 32) per_sm = 32;
     if (per_sm < 1) per_sm = 1;
     long long gl = (long long)lim.sms * per_sm;
-    if (gl > prm.num_items) gl = prm.num_items;
+    const long long max_grid = (prm.num_items + prm.E - 1) / prm.E;
+    if (gl > max_grid) gl = max_grid;
     grid = (int)gl;
     return 0;
 }
