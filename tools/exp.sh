@@ -1,6 +1,7 @@
-# development experiment: register budget / direction chunk of the Jacobian kernel on the config-3 shape (needs -DMTB_EXPERIMENT)
-run() { echo "== $*"; env "$@" python tools/quick_bench.py --only jac 2>&1 | cut -c1-120 | head -2 | tail -1; }
-run MTB_JAC_VARIANT=1
-run MTB_JAC_VARIANT=5
-run MTB_JAC_VARIANT=6
-run MTB_JAC_VARIANT=7
+# development experiment: threads per block (work items packed per block) of the Jacobian kernel (needs -DMTB_EXPERIMENT)
+run() { echo "== $*"; env "$@" python tools/quick_bench.py --only jac 2>&1 | cut -c1-120 | sed -n '2p;4p;5p'; }
+run MTB_JAC_THREADS=64
+run MTB_JAC_THREADS=96
+run MTB_JAC_THREADS=128
+run MTB_JAC_THREADS=192
+run MTB_JAC_THREADS=256
