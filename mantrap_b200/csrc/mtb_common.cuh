@@ -10,15 +10,12 @@
 #define MTB_SHARED_FLOAT4(name) extern __shared__ float4 name[]
 #define MTB_LAUNCH(kernel, grid, block, smem, stream, ...) kernel<<<grid, block, smem, stream>>>(__VA_ARGS__)
 // named barrier over `count` threads (a multiple of 32): synchronises one evaluation group, not the whole block
-// The id is an immediate (ptxas reserves all 16 barriers of a block for a register id, which caps the resident blocks per
-// SM); a block holds at most four groups of >= 64 threads plus, for larger blocks, one group = the whole block.
+// The id is a register operand: ptxas then reserves all 16 barriers of the block (at most 4 resident blocks per SM, above the
+// 3 the register budget allows anyway). Immediate ids selected by a switch were measured SLOWER on B200 (config-4 shape,
+// 524288 evaluations: 22.76 ms vs 21.10 ms) -- the extra branches at every group barrier cost more than the freed barrier
+// resources buy (smaller blocks with more resident blocks did not pay either).
 static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
-    switch (id) {
-        case 0: asm volatile("bar.sync 0, %0;" ::"r"(count) : "memory"); break;
-        case 1: asm volatile("bar.sync 1, %0;" ::"r"(count) : "memory"); break;
-        case 2: asm volatile("bar.sync 2, %0;" ::"r"(count) : "memory"); break;
-        default: asm volatile("bar.sync 3, %0;" ::"r"(count) : "memory"); break;   // E <= 4 groups of >= 64 threads in <= 256 threads
-    }
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
 // Fire-and-forget 16-byte float accumulation in L2 (REDG.E.ADD.F32x4, sm_90+): one instruction per pair adjoint instead
 // of four shared-memory compare-and-swap loops. The target lives in an L2-resident global scratch; loads / stores of it

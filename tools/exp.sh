@@ -1,7 +1,6 @@
-# development experiment: threads per block (work items packed per block) of the Jacobian kernel (needs -DMTB_EXPERIMENT)
-run() { echo "== $*"; env "$@" python tools/quick_bench.py --only jac 2>&1 | cut -c1-120 | sed -n '2p;4p;5p'; }
-run MTB_JAC_THREADS=64
-run MTB_JAC_THREADS=96
-run MTB_JAC_THREADS=128
-run MTB_JAC_THREADS=192
-run MTB_JAC_THREADS=256
+# development experiment: immediate vs register barrier ids in the fused kernel
+run() { echo "== $*"; env "$@" python tools/quick_bench.py --only c4 2>&1 | cut -c1-100 | head -1; }
+run A=immediate
+MTB_NVCC_EXTRA="-DMTB_BAR_DYNAMIC" python -m mantrap_b200.build >/dev/null 2>&1
+run A=dynamic
+run A=dynamic
