@@ -17,6 +17,7 @@ Mirrors: GraphBasedEnvironment environment/base/graph_based.py:14-560, ParticleE
 SocialForcesEnvironment environment/social_forces.py:11-210, PotentialFieldEnvironment environment/simplified/
 potential_field.py:10-99, KalmanEnvironment environment/simplified/kalman.py:11-124.
 """
+import math
 import typing
 
 import torch
@@ -278,6 +279,16 @@ class GraphBasedEnvironment:
         return True
 
 
+_SCALARS: typing.Dict[float, torch.Tensor] = {}
+
+
+def _scalar_tensor(value: float) -> torch.Tensor:
+    t = _SCALARS.get(value)
+    if t is None:
+        t = _SCALARS[value] = torch.tensor(value, dtype=torch.float32)
+    return t
+
+
 class ParticleEnvironment(GraphBasedEnvironment):
     """Particle rollout collapsed to one Gaussian per ado and step (environment/base/particle.py:14-205)."""
     # parameter name -> (mean, "variance" used as std) in the reference's dict order (A.4)
@@ -294,9 +305,13 @@ class ParticleEnvironment(GraphBasedEnvironment):
             for ip, key in enumerate(names):
                 override = param_dicts.get(f"{key}_dict")
                 loc, scale = override[ado_id] if override is not None else self.param_defaults[key]
-                dist = torch.distributions.Normal(loc=loc, scale=scale)
-                draw = dist.sample((num_particles,))
-                samples[m, ip], cdfs[m, ip] = draw, dist.cdf(draw)
+                # Normal(loc, scale).sample((P,)) and .cdf(draw) spelled out with torch's own expressions (distributions/
+                # normal.py:77-82, :104-110): the same generator consumption and bits, without building 2 N distribution
+                # objects per callback (this draw is the largest host cost of a solver callback)
+                loc_t, scale_t = _scalar_tensor(float(loc)), _scalar_tensor(float(scale))
+                draw = torch.normal(loc_t.expand((num_particles,)), scale_t.expand((num_particles,)))
+                samples[m, ip] = draw
+                cdfs[m, ip] = 0.5 * (1 + torch.erf((draw - loc_t) * scale_t.reciprocal() / math.sqrt(2)))
         weight = torch.prod(cdfs, dim=1)
         weight = weight / torch.norm(weight, dim=0)               # over the ADO axis (reference quirk, particle.py:141)
         out = {"v0": samples[None, :, 0].contiguous(), "weight": weight[None].contiguous(),
