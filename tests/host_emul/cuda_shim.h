@@ -64,7 +64,11 @@ inline thread_local dim3 threadIdx, blockIdx, blockDim, gridDim;
 static inline void __syncthreads() { emul::tl_block->bar.arrive_and_wait(); }
 static inline emul::Warp& emul_warp() { return emul::tl_block->warps[threadIdx.x >> 5]; }
 static inline void __syncwarp(unsigned = 0xffffffffu) { emul_warp().bar.arrive_and_wait(); }
+#ifdef MTB_EMUL_BREAK_GROUP_BARRIER   // self-test of tools/tsan_emulation.py: without the group barrier ThreadSanitizer must report races
+static inline void mtb_bar_sync(int, int) {}
+#else
 static inline void mtb_bar_sync(int id, int count) { emul::tl_block->named_barrier(id, count).arrive_and_wait(); }
+#endif
 
 template <class T>
 static inline T emul_exchange(T v, int src_lane) {
