@@ -164,6 +164,53 @@ def test_host_pipeline_matches_synchronous_api(eng):
         assert torch.allclose(got[k]["grad"], ref_out.grad, rtol=1e-4, atol=1e-6), k
 
 
+def test_jacobian_full_size_properties(eng):
+    """Config-3 shape at BASELINE size (1024 scenes, SocialForces N=10 P=4 T=20, control + speed + min-distance + ellipsoid
+    rows), properties that need no oracle: (1) duplicated candidates give bit-identical Jacobians wherever they land in the
+    grid (the tangent kernel has no atomics), (2) block-triangular structure: a row of time index t does not depend on
+    controls j >= t - 1 through the positions of a double integrator, (3) the values returned with the
+    Jacobian equal the rows of the evaluation kernel, (4) central finite differences of the evaluation kernel's rows
+    reproduce sampled Jacobian columns on >= 90 % of the entries (the rest cross a kink of the piecewise-smooth model)."""
+    s, c, n, p, t_hor = 1024, 2, 10, 4, 20
+    scene = scenarios.synthetic_scenes(s, n, p, regular_sigma=True).to(DEV)
+    controls = scenarios.candidate_controls(s, c, t_hor, u_max=1.0)
+    controls[:, 1] = controls[:, 0]
+    controls = controls.to(DEV)
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True, ellipsoid=True)
+    jac, values = eng.constraint_jacobian(scene, controls, spec, want_values=True)
+    cons = eng.evaluate(scene, controls, spec, want=("cons",))["cons"]
+    torch.cuda.synchronize()
+    n_ctl, n_spd, n_md = 2 * t_hor, 2 * (t_hor + 1), n * t_hor
+    assert jac.shape == (s, c, n_ctl + n_spd + 2 * n_md, 2 * t_hor) and torch.isfinite(jac).all()
+    assert torch.equal(jac[:, 0], jac[:, 1])                                                        # (1)
+    md = jac[:, 0, n_ctl + n_spd:n_ctl + n_spd + n_md].reshape(s, n, t_hor, t_hor, 2)
+    ell = jac[:, 0, n_ctl + n_spd + n_md:].reshape(s, n, t_hor, t_hor, 2)
+    for t in range(t_hor):                                                                          # (2)
+        assert not md[:, :, t, max(t - 1, 0):].any(), t
+        assert not ell[:, :, t, max(t - 1, 0):].any(), t
+    assert md.abs().amax() > 0 and ell.abs().amax() > 0
+    gio.assert_parity(kc.np_(values[:, 0].reshape(s, -1)), kc.np_(cons[:, 0, n_ctl + n_spd:n_ctl + n_spd + n_md]), gio.RTOL_ROLLOUT,
+                      "min-distance values: jacobian kernel vs evaluation kernel")                  # (3)
+    # (4) float32 central differences, h = 2^-6: compare on the min-distance block of 16 scenes, 3 control columns
+    h = 2.0 ** -6
+    sub = 16
+    scene_sub = __import__("mantrap_b200").parallel.slice_scene(scene, 0, sub)
+    for col in (0, 7, 2 * (t_hor - 4) + 1):
+        up, dn = controls[:sub, :1].clone(), controls[:sub, :1].clone()
+        up.view(sub, -1)[:, col] += h
+        dn.view(sub, -1)[:, col] -= h
+        spec_md = engine.ModuleSpec(min_distance=True)
+        f_up = eng.evaluate(scene_sub, up.contiguous(), spec_md, want=("cons",))["cons"][:, 0]
+        f_dn = eng.evaluate(scene_sub, dn.contiguous(), spec_md, want=("cons",))["cons"][:, 0]
+        fd = (f_up - f_dn) / (2 * h)
+        an = jac[:sub, 0, n_ctl + n_spd:n_ctl + n_spd + n_md, col]
+        # The model is piecewise smooth (interaction radius, force / speed clamps, goal radius): a finite step crosses a
+        # kink in some (scene, row) entries, so the check is on the bulk of the entries, not on the maximum.
+        tol = 2e-2 * max(float(an.abs().max()), 1e-2) + 2e-3
+        frac_ok = float(((fd - an).abs() <= tol).float().mean())
+        assert frac_ok >= 0.9, (col, frac_ok, float((fd - an).abs().median()))
+
+
 def test_argmin(eng):
     total = torch.tensor([[3.0, 1.0, 2.0, 0.5], [4.0, -1.0, 5.0, 6.0], [1.0, 2.0, 3.0, 4.0]], device=DEV)
     vio = torch.tensor([[0.0, 0.0, 0.0, 1.0], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]], device=DEV)
