@@ -260,9 +260,9 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # NCCL prints "NCCL version ..." on stdout at NCCL_DEBUG=VERSION (the image default): keep stdout to the ONE JSON line
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL writes its banner ("NCCL version ...") and warnings to stdout by default: send them to stderr so that stdout
+        # carries the ONE JSON line only
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     eng = engine.Engine(dev)
 
