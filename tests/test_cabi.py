@@ -50,3 +50,24 @@ def test_engine_requires_gpu():
         pytest.skip("GPU present")
     with pytest.raises(RuntimeError):
         engine.Engine()
+
+
+def test_argument_validation_returns_error_codes(lib_path):
+    """Bad arguments are rejected with MTB_ERR_* before any device work (no GPU needed): the error behaviour of the boundary."""
+    lib = _cabi.bind(ctypes.CDLL(lib_path))
+    dummy = ctypes.c_void_p(16)          # never dereferenced: validation fails first
+    assert lib.mtb_attention(_cabi.ATTENTION_EUCLIDEAN, None, dummy, 1, 1, 4.0, dummy, None) == -1
+    assert lib.mtb_attention(7, dummy, dummy, 1, 1, 4.0, dummy, None) == -1
+    assert lib.mtb_attention(_cabi.ATTENTION_CLOSEST, dummy, dummy, 1, _cabi.MAX_ADOS + 1, 4.0, dummy, None) == -2
+    assert lib.mtb_env_step(_cabi.EGO_DOUBLE_INTEGRATOR, 0.4, 1e-6, 2.0, 2.5, None, dummy, dummy, None, 1, 1, 1, None, None) == -1
+    assert lib.mtb_env_step(_cabi.EGO_NONE, 0.4, 1e-6, 2.0, 2.5, dummy, dummy, dummy, None, 1, 1, 1, None, None) == -1
+    assert lib.mtb_env_step(_cabi.EGO_DOUBLE_INTEGRATOR, 0.4, 1e-6, 2.0, 2.5, dummy, dummy, dummy, None, 1, 1, 0, None, None) == -1
+    pb, md = _cabi.MtbProblem(), _cabi.MtbModules()
+    assert lib.mtb_num_constraint_rows(ctypes.byref(pb), ctypes.byref(md)) == -1          # empty problem
+    pb.num_scenes = pb.num_candidates = pb.t_horizon = 1
+    pb.num_ados, pb.num_particles, pb.ado0 = _cabi.MAX_ADOS + 1, 2, 16
+    assert lib.mtb_num_constraint_rows(ctypes.byref(pb), ctypes.byref(md)) == -2          # too many ados
+    assert lib.mtb_argmin(None, None, 1, 1, 1e-3, None, 0, None, None, None, None) == -1
+    assert lib.mtb_constraint_jacobian(ctypes.byref(pb), ctypes.byref(md), None, None, None, 0, None) == -1
+    for code, text in ((-1, b"bad argument"), (-2, b"exceeds"), (-3, b"workspace")):
+        assert text in lib.mtb_error_string(code)
