@@ -16,6 +16,7 @@
  *                           mantrap/modules/base/optimization_module.py:258-307, :428-434)
  *   mtb_argmin              mantrap/solver/baselines/random_search.py:28-35  keep-best-feasible candidate
  *   mtb_attention           mantrap/attention/euclidean.py:22-29, closest.py:22-31   attention filters -> ado_mask
+ *   mtb_warm_start_encoding mantrap/solver/base/trajopt.py:466-499, :308-331   scene encoding + nearest pre-computed solution
  *   mtb_env_step            mantrap/environment/base/graph_based.py:82-124   GraphBasedEnvironment.step, batched
  *                           mantrap/solver/base/trajopt.py:109-193           closed-loop solve(), warm-start shift
  *
@@ -32,7 +33,7 @@
 extern "C" {
 #endif
 
-#define MTB_ABI_VERSION 4
+#define MTB_ABI_VERSION 5
 
 /* environment kinds: mantrap/environment/social_forces.py, simplified/potential_field.py, simplified/kalman.py */
 #define MTB_ENV_SOCIAL_FORCES 0
@@ -188,6 +189,18 @@ int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, i
 #define MTB_ATTENTION_CLOSEST 1
 int mtb_attention(int kind, const float* ego0, const float* ado0, int32_t num_scenes, int32_t num_ados, float radius,
                   uint8_t* mask, void* stream);
+
+/* Scene encoding and warm start from pre-computed solutions (TrajOptSolver.encode, trajopt.py:466-499, and
+ * _warm_start_encoding, trajopt.py:308-331): encoding[s] = (R p_closest_ado, v_ego) with R the rotation into the
+ * robot -> goal frame (utility/maths.py:226-233) and the closest ado by L2 distance to the robot (first minimum);
+ * match[s] = argmin_j ||encoding_db[j] - encoding[s]||_2 (first minimum); warm[s] = solution_db[match[s], :T, :].
+ * ego0 [S,4], ego_goal [S,2], ado0 [S,N,4], encoding_db [M,4], solution_db [M,H,2] with H >= T (the reference's database:
+ * third_party/warm_start/encoding.pt, solution.pt, M = 100, H = 10); encoding [S,4], match [S], warm [S,T,2] are optional
+ * outputs (NULL = not wanted). */
+int mtb_warm_start_encoding(const float* ego0, const float* ego_goal, const float* ado0, int32_t num_scenes,
+                            int32_t num_ados, const float* encoding_db, const float* solution_db, int32_t num_entries,
+                            int32_t db_horizon, int32_t t_horizon, float* encoding, int32_t* match, float* warm,
+                            void* stream);
 
 /* One closed-loop environment step for S scenes in lock step (GraphBasedEnvironment.step, graph_based.py:82-124):
  * the ego executes controls[s, 0] (controls [S,T,2], e.g. mtb_argmin's best_controls); every ado samples its next

@@ -12,7 +12,7 @@ import torch
 ENV_SOCIAL_FORCES, ENV_POTENTIAL_FIELD, ENV_KALMAN = 0, 1, 2
 EGO_DOUBLE_INTEGRATOR, EGO_SINGLE_INTEGRATOR, EGO_NONE = 0, 1, 2
 MAX_ADOS, MAX_HORIZON = 64, 64
-ABI_VERSION = 4
+ABI_VERSION = 5
 ATTENTION_EUCLIDEAN, ATTENTION_CLOSEST = 0, 1
 
 _f, _i, _p = ctypes.c_float, ctypes.c_int32, ctypes.c_void_p
@@ -50,7 +50,7 @@ class MtbLaunchInfo(ctypes.Structure):
 
 EXPORTED_SYMBOLS = ("mtb_abi_version", "mtb_error_string", "mtb_num_constraint_rows", "mtb_workspace_bytes",
                     "mtb_evaluate", "mtb_query_launch", "mtb_constraint_jacobian", "mtb_jacobian_workspace_bytes",
-                    "mtb_argmin", "mtb_attention", "mtb_env_step", "mtb_probe_launch", "mtb_ego_unroll", "mtb_ego_roll", "mtb_ego_unroll_adjoint",
+                    "mtb_argmin", "mtb_attention", "mtb_warm_start_encoding", "mtb_env_step", "mtb_probe_launch", "mtb_ego_unroll", "mtb_ego_roll", "mtb_ego_unroll_adjoint",
                     "mtb_ego_dx_du")
 
 
@@ -80,6 +80,8 @@ def bind(lib: ctypes.CDLL) -> ctypes.CDLL:
     lib.mtb_ego_dx_du.restype, lib.mtb_ego_dx_du.argtypes = ctypes.c_int, [ctypes.c_int, _f, _i, _p, _p]
     lib.mtb_attention.restype = ctypes.c_int
     lib.mtb_attention.argtypes = [ctypes.c_int, _p, _p, _i, _i, _f, _p, _p]
+    lib.mtb_warm_start_encoding.restype = ctypes.c_int
+    lib.mtb_warm_start_encoding.argtypes = [_p, _p, _p, _i, _i, _p, _p, _i, _i, _i, _p, _p, _p, _p]
     lib.mtb_env_step.restype = ctypes.c_int
     lib.mtb_env_step.argtypes = [ctypes.c_int, _f, _f, _f, _f, _p, _p, _p, _p, _i, _i, _i, _p, _p]
     lib.mtb_argmin.restype = ctypes.c_int

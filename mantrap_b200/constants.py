@@ -45,4 +45,6 @@ ATTENTION_CLOSEST_RADIUS = 4.0                   # :112
 TAG_OPTIMIZATION = "optimization"                # :16
 TAG_WARM_START = "warm_start"                    # :17
 WARM_START_HARD = "hard"                         # :72
+WARM_START_ENCODING = "encoding"                 # :72
 WARM_START_ZEROS = "zeros"                       # :76
+WARM_START_PRE_COMPUTATION_FILE = ("encoding.pt", "solution.pt")   # :79 (third_party/warm_start/ of the reference)

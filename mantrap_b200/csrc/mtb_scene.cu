@@ -113,6 +113,60 @@ __global__ void __launch_bounds__(kSceneBlock) env_step_kernel(int ego_kind, flo
     }
 }
 
+// Scene encoding + nearest pre-computed solution (trajopt.py:466-499, :308-331). One warp per scene: lanes stride over the
+// ados (closest one, first minimum like torch.argmin), lane 0 rotates its position into the robot -> goal frame
+// (utility/maths.py:226-233: R = [[c, s], [-s, c]], theta = atan2(goal - ego), applied to the ABSOLUTE ado position as the
+// reference does), the encoding is (R p_ado, v_ego); lanes then stride over the M database rows for the L2-nearest encoding
+// and copy the first T controls of its solution.
+__global__ void __launch_bounds__(kSceneBlock) warm_start_kernel(const float* __restrict__ ego0, const float* __restrict__ ego_goal,
+                                                                 const float* __restrict__ ado0, int S, int N,
+                                                                 const float* __restrict__ enc_db, const float* __restrict__ sol_db,
+                                                                 int M, int H, int T, float* __restrict__ encoding,
+                                                                 int32_t* __restrict__ match, float* __restrict__ warm) {
+    const int lane = threadIdx.x & 31;
+    const int warps_per_block = blockDim.x >> 5;
+    for (int s = blockIdx.x * warps_per_block + (threadIdx.x >> 5); s < S; s += gridDim.x * warps_per_block) {
+        const float4 eg = *reinterpret_cast<const float4*>(ego0 + (size_t)s * 4);
+        unsigned long long best = ~0ull;
+        for (int k = lane; k < N; k += 32) {
+            const float4 a = *reinterpret_cast<const float4*>(ado0 + ((size_t)s * N + k) * 4);
+            const float dx = a.x - eg.x, dy = a.y - eg.y;
+            const unsigned long long key = ((unsigned long long)__float_as_uint(sqrtf(dx * dx + dy * dy)) << 32) | (unsigned)k;
+            best = key < best ? key : best;
+        }
+        for (int off = 16; off > 0; off >>= 1) {
+            const unsigned hi = __shfl_xor_sync(0xffffffffu, (unsigned)(best >> 32), off);
+            const unsigned lo = __shfl_xor_sync(0xffffffffu, (unsigned)(best & 0xffffffffu), off);
+            const unsigned long long o = ((unsigned long long)hi << 32) | lo;
+            best = o < best ? o : best;
+        }
+        const int closest = (int)(best & 0xffffffffu);
+        const float4 a = *reinterpret_cast<const float4*>(ado0 + ((size_t)s * N + closest) * 4);
+        const float theta = atan2f(ego_goal[(size_t)s * 2 + 1] - eg.y, ego_goal[(size_t)s * 2 + 0] - eg.x);
+        const float c = cosf(theta), sn = sinf(theta);
+        const float e0 = c * a.x + sn * a.y, e1 = -sn * a.x + c * a.y, e2 = eg.z, e3 = eg.w;
+        if (encoding != nullptr && lane == 0) *reinterpret_cast<float4*>(encoding + (size_t)s * 4) = make_float4(e0, e1, e2, e3);
+        best = ~0ull;
+        for (int j = lane; j < M; j += 32) {
+            const float4 d = *reinterpret_cast<const float4*>(enc_db + (size_t)j * 4);
+            const float q0 = d.x - e0, q1 = d.y - e1, q2 = d.z - e2, q3 = d.w - e3;
+            const float dist = sqrtf(q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3);     // torch.norm(encoding_db - encoding, dim=1)
+            const unsigned long long key = ((unsigned long long)__float_as_uint(dist) << 32) | (unsigned)j;
+            best = key < best ? key : best;
+        }
+        for (int off = 16; off > 0; off >>= 1) {
+            const unsigned hi = __shfl_xor_sync(0xffffffffu, (unsigned)(best >> 32), off);
+            const unsigned lo = __shfl_xor_sync(0xffffffffu, (unsigned)(best & 0xffffffffu), off);
+            const unsigned long long o = ((unsigned long long)hi << 32) | lo;
+            best = o < best ? o : best;
+        }
+        const int row = (int)(best & 0xffffffffu);
+        if (match != nullptr && lane == 0) match[s] = row;
+        if (warm != nullptr)
+            for (int idx = lane; idx < 2 * T; idx += 32) warm[(size_t)s * 2 * T + idx] = sol_db[(size_t)row * 2 * H + idx];
+    }
+}
+
 static int scene_grid(int S) {
     const DeviceLimits lim = device_limits();
     const int warps_per_block = kSceneBlock / 32;
@@ -134,6 +188,24 @@ int mtb_attention(int kind, const float* ego0, const float* ado0, int32_t num_sc
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     MTB_LAUNCH(mtb::attention_kernel, mtb::scene_grid(num_scenes), mtb::kSceneBlock, (size_t)0, st, kind, ego0, ado0,
                (int)num_scenes, (int)num_ados, radius, mask);
+#ifndef MTB_HOST_EMUL
+    return (int)cudaGetLastError();
+#else
+    return 0;
+#endif
+}
+
+int mtb_warm_start_encoding(const float* ego0, const float* ego_goal, const float* ado0, int32_t num_scenes, int32_t num_ados,
+                            const float* encoding_db, const float* solution_db, int32_t num_entries, int32_t db_horizon,
+                            int32_t t_horizon, float* encoding, int32_t* match, float* warm, void* stream) {
+    if (ego0 == nullptr || ego_goal == nullptr || ado0 == nullptr || encoding_db == nullptr || num_scenes < 1 || num_ados < 1 ||
+        num_entries < 1)
+        return MTB_ERR_BAD_ARGUMENT;
+    if (warm != nullptr && (solution_db == nullptr || t_horizon < 1 || t_horizon > db_horizon)) return MTB_ERR_BAD_ARGUMENT;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    MTB_LAUNCH(mtb::warm_start_kernel, mtb::scene_grid(num_scenes), mtb::kSceneBlock, (size_t)0, st, ego0, ego_goal, ado0,
+               (int)num_scenes, (int)num_ados, encoding_db, solution_db, (int)num_entries, (int)db_horizon, (int)t_horizon, encoding,
+               match, warm);
 #ifndef MTB_HOST_EMUL
     return (int)cudaGetLastError();
 #else

@@ -227,6 +227,20 @@ def launch_attention(lib: ctypes.CDLL, kind: str, ego0: torch.Tensor, ado0: torc
     return mask
 
 
+def launch_warm_start_encoding(lib: ctypes.CDLL, ego0: torch.Tensor, ego_goal: torch.Tensor, ado0: torch.Tensor,
+                               encoding_db: torch.Tensor, solution_db: typing.Optional[torch.Tensor], t_horizon: int, stream: int = 0):
+    """`mtb_warm_start_encoding`: (encoding [S,4], match [S] int32, warm [S,T,2] or None without a solution database)."""
+    s, n, dev = ado0.shape[0], ado0.shape[1], ado0.device
+    encoding = torch.empty((s, 4), dtype=torch.float32, device=dev)
+    match = torch.empty(s, dtype=torch.int32, device=dev)
+    warm = torch.empty((s, t_horizon, 2), dtype=torch.float32, device=dev) if solution_db is not None else None
+    code = lib.mtb_warm_start_encoding(_cabi.ptr(ego0), _cabi.ptr(ego_goal), _cabi.ptr(ado0), s, n, _cabi.ptr(encoding_db),
+                                       _cabi.ptr(solution_db), encoding_db.shape[0], 0 if solution_db is None else solution_db.shape[1],
+                                       t_horizon, _cabi.ptr(encoding), _cabi.ptr(match, dtype=torch.int32), _cabi.ptr(warm), stream)
+    _cabi.check(lib, code, "mtb_warm_start_encoding")
+    return encoding, match, warm
+
+
 def launch_env_step(lib: ctypes.CDLL, scene: SceneBatch, controls: torch.Tensor, eps: typing.Optional[torch.Tensor],
                     warm: typing.Optional[torch.Tensor] = None, stream: int = 0):
     """`mtb_env_step`: advance `scene.ego0` / `scene.ado0` IN PLACE by one closed-loop step with controls[:, 0]
@@ -383,6 +397,15 @@ class Engine:
             mask = launch_attention(self.lib, kind, ego0, ado0, radius, stream=self._stream())
         self.launches += 1
         return mask
+
+    def warm_start_encoding(self, ego0, ego_goal, ado0, encoding_db, solution_db, t_horizon: int):
+        """Scene encodings of S scenes, their nearest pre-computed scenario and its solution as warm start
+        (`TrajOptSolver.encode` + `_warm_start_encoding`)."""
+        self._check(ego0, ego_goal, ado0, encoding_db, solution_db)
+        with self._guard():
+            out = launch_warm_start_encoding(self.lib, ego0, ego_goal, ado0, encoding_db, solution_db, t_horizon, stream=self._stream())
+        self.launches += 1
+        return out
 
     def env_step(self, scene: SceneBatch, controls: torch.Tensor, eps: torch.Tensor = None, warm: torch.Tensor = None):
         """One closed-loop step of every scene, in place (GraphBasedEnvironment.step for S scenes in lock step)."""

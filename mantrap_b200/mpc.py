@@ -74,9 +74,10 @@ class BatchedClosedLoop:
         return best, val, idx
 
     def solve(self, time_steps: int, candidates: typing.Sequence[torch.Tensor] = None, eps: typing.Sequence[torch.Tensor] = None,
-              sample: bool = True) -> ClosedLoopResult:
+              sample: bool = True, warm_start_db: typing.Tuple[torch.Tensor, torch.Tensor] = None) -> ClosedLoopResult:
         """`time_steps` closed-loop steps. `candidates[k]` / `eps[k]` override the device draws of step k (tests); `sample
-        = False` moves the ados along the mean of their one-step distribution."""
+        = False` moves the ados along the mean of their one-step distribution; `warm_start_db` = (encodings [M,4], solutions
+        [M,H,2]) starts every scene from its nearest pre-computed scenario instead of zeros."""
         eng, scene = self.engine, self.scene
         s, n, dev = scene.num_scenes, scene.num_ados, eng.device
         ego_traj = torch.empty((s, time_steps + 1, 4), device=dev)
@@ -87,7 +88,11 @@ class BatchedClosedLoop:
         steps = torch.full((s,), time_steps, dtype=torch.int32, device=dev)
         done = torch.zeros(s, dtype=torch.bool, device=dev)
         ego_traj[:, 0], ado_traj[:, :, 0] = scene.ego0, scene.ado0
-        warm = torch.zeros((s, self.t_planning, 2), device=dev)            # WARM_START_ZEROS (constants.py:76)
+        if warm_start_db is not None:                                      # WARM_START_ENCODING for every scene (trajopt.py:308-331)
+            enc_db, sol_db = (x.to(dev).float().contiguous() for x in warm_start_db)
+            _, _, warm = eng.warm_start_encoding(scene.ego0, scene.ego_goal, scene.ado0, enc_db, sol_db, self.t_planning)
+        else:
+            warm = torch.zeros((s, self.t_planning, 2), device=dev)        # WARM_START_ZEROS (constants.py:76)
         next_warm = torch.empty_like(warm)
         for k in range(time_steps):
             best, val, idx = self.plan(warm, None if candidates is None else candidates[k])

@@ -97,7 +97,8 @@ class TrajOptSolver:
     # ---- warm start --------------------------------------------------------------------------------------------
     def warm_start(self, method: str = constants.WARM_START_HARD) -> torch.Tensor:
         """"hard": the same problem with the hard modules only, started from full throttle towards the goal
-        (trajopt.py:248-306); "zeros": zero controls. (Encoding / soft / potential need data or modules out of scope.)"""
+        (trajopt.py:248-306); "zeros": zero controls; "encoding": nearest pre-computed scenario (trajopt.py:308-331; needs the
+        reference's database, see `warm_start_database`). ("soft" / "potential" need modules out of scope.)"""
         if method == constants.WARM_START_HARD:
             part = self.__class__(env=self.env, goal=self.goal, modules=self.module_hard(), t_planning=self.planning_horizon,
                                   config_name=self.config_name, fused=self._fused, num_particles=self._num_particles)
@@ -107,7 +108,49 @@ class TrajOptSolver:
             return part.optimize(z0=init.flatten(), tag=constants.TAG_WARM_START)
         if method == constants.WARM_START_ZEROS:
             return torch.zeros(2 * self.planning_horizon)
+        if method == constants.WARM_START_ENCODING:
+            return self._warm_start_encoding()
         raise ValueError(f"Invalid warm starting-method {method} !")
+
+    # ---- encoding / pre-computed warm starts ---------------------------------------------------------------------
+    def _scene_arrays(self):
+        engine = runtime.default_engine()
+        ego_state, ado_states = self.env.states()
+        return (engine, runtime.to_device(ego_state[0:4].view(1, 4), engine), runtime.to_device(self.goal.view(1, 2), engine),
+                runtime.to_device(ado_states[:, 0:4].reshape(1, self.env.num_ados, 4), engine))
+
+    def warm_start_database(self) -> typing.Tuple[torch.Tensor, torch.Tensor]:
+        """(encoding_db [M,4], solution_db [M,H,2]): the `warm_start_db` solver parameter -- a pair of tensors or a directory
+        holding the reference's `encoding.pt` / `solution.pt` (constants.py:79, third_party/warm_start/) -- else the directory
+        named by $MANTRAP_WARM_START_DIR. The database is data of the reference and is not shipped with this package."""
+        import os
+        db = self._solver_params.get("warm_start_db", os.environ.get("MANTRAP_WARM_START_DIR"))
+        if db is None:
+            raise FileNotFoundError("warm start 'encoding' needs the pre-computed database: pass warm_start_db=(encodings, solutions) "
+                                    "or a directory with encoding.pt / solution.pt, or set MANTRAP_WARM_START_DIR")
+        if isinstance(db, (str, os.PathLike)):
+            enc_file, sol_file = constants.WARM_START_PRE_COMPUTATION_FILE
+            db = (torch.load(os.path.join(db, enc_file)), torch.load(os.path.join(db, sol_file)))
+        enc_db, sol_db = db
+        assert enc_db.ndim == 2 and enc_db.shape[1] == 4 and sol_db.ndim == 3 and sol_db.shape[2] == 2
+        return enc_db, sol_db
+
+    def encode(self) -> torch.Tensor:
+        """Four-dimensional scene encoding (trajopt.py:466-499): closest ado in the robot -> goal frame + robot velocity."""
+        engine, ego0, goal, ado0 = self._scene_arrays()
+        dummy = torch.zeros((1, 4), dtype=torch.float32, device=engine.device)
+        encoding, _, _ = engine.warm_start_encoding(ego0, goal, ado0, dummy, None, self.planning_horizon)
+        return encoding[0].cpu()
+
+    def _warm_start_encoding(self) -> torch.Tensor:
+        """Solution of the nearest pre-computed scenario (trajopt.py:308-331), flattened z."""
+        assert self.env.dt == constants.ENV_DT_DEFAULT            # pre-computation only for the default time step (:313)
+        enc_db, sol_db = self.warm_start_database()
+        assert sol_db.shape[1] >= self.planning_horizon
+        engine, ego0, goal, ado0 = self._scene_arrays()
+        _, _, warm = engine.warm_start_encoding(ego0, goal, ado0, runtime.to_device(enc_db, engine), runtime.to_device(sol_db, engine),
+                                                self.planning_horizon)
+        return warm[0].cpu().flatten()
 
     @staticmethod
     def module_defaults():

@@ -492,3 +492,24 @@ def env_step(ego_kind: str, dt: float, ego0: torch.Tensor, ado0: torch.Tensor, a
     act = _clamp_action((pos - ado0[..., 0:2]) / dt, PED_SPEED_MAX, per_component=False)
     ados = torch.cat((ado0[..., 0:2] + act * dt, act), dim=-1)
     return ego, ados
+
+
+def scene_encoding(ego0: torch.Tensor, ego_goal: torch.Tensor, ado0: torch.Tensor) -> torch.Tensor:
+    """`TrajOptSolver.encode` (solver/base/trajopt.py:466-499) for a batch: position of the ado closest to the robot rotated
+    into the robot -> goal frame (`maths.rotation_matrix`, utility/maths.py:226-233, applied to the absolute position) and
+    the robot velocity. ego0 [B,4], ego_goal [B,2], ado0 [B,N,4] -> [B,4]."""
+    out = torch.zeros((ego0.shape[0], 4))
+    for b in range(ego0.shape[0]):
+        xy = ego_goal[b] - ego0[b, 0:2]
+        theta = torch.atan2(xy[1], xy[0])
+        rot = torch.tensor([[torch.cos(theta), torch.sin(theta)], [-torch.sin(theta), torch.cos(theta)]])
+        closest = torch.argmin(torch.norm(ado0[b, :, 0:2] - ego0[b, 0:2], dim=1))
+        out[b] = torch.cat((torch.matmul(rot, ado0[b, closest, 0:2]), ego0[b, 2:4]))
+    return out
+
+
+def warm_start_encoding(encoding: torch.Tensor, encoding_db: torch.Tensor, solution_db: torch.Tensor, t_horizon: int):
+    """`TrajOptSolver._warm_start_encoding` (trajopt.py:308-331): nearest database encoding (L2, first minimum) and the first
+    `t_horizon` controls of its pre-computed solution. encoding [B,4] -> (match [B], warm [B,T,2])."""
+    match = torch.stack([torch.argmin(torch.norm(encoding_db - e, dim=1)) for e in encoding])
+    return match, solution_db[match, :t_horizon]

@@ -201,6 +201,30 @@ def check_attention():
     assert z.numel() == 8 and sol._attention_module.ids_current == attention.EuclideanModule(env=sol.env, t_horizon=4).compute()
 
 
+def check_warm_start_encoding():
+    """TrajOptSolver.encode() / warm_start("encoding") of the drop-in solver against the reference on the recorded scenes."""
+    g = gio.load("scene_ops")
+    db = (gio.t(g["ws_encoding_db"]), gio.t(g["ws_solution_db"]))
+    for i in range(0, len(g["ws_n"]), 3):
+        n, t_hor = int(g["ws_n"][i]), int(g["ws_T"][i])
+        env = environment.PotentialFieldEnvironment(ego_position=gio.t(g["ws_ego"][i][0:2]), ego_velocity=gio.t(g["ws_ego"][i][2:4]),
+                                                    ego_type=agents.DoubleIntegratorDTAgent, dt=0.4)
+        for k in range(n):
+            env.add_ado(position=gio.t(g["ws_ado"][i][k, 0:2]), velocity=torch.zeros(2), identifier=f"a{k:02d}")
+        sol = solver.RandomSearch(env, goal=gio.t(g["ws_goal"][i]), t_planning=t_hor, modules=[modules.GoalNormModule], warm_start_db=db)
+        gio.assert_parity(sol.encode().numpy(), g["ws_encoding"][i], gio.RTOL_ROLLOUT, f"encode {i}", atol=1e-6)
+        z = sol.warm_start(method="encoding")
+        assert z.shape == (2 * t_hor,) and np.array_equal(z.view(-1, 2).numpy(), g["ws_warm"][i][:t_hor])
+    sol = solver.RandomSearch(env, goal=gio.t(g["ws_goal"][i]), t_planning=3, modules=[modules.GoalNormModule])
+    import os
+    if "MANTRAP_WARM_START_DIR" not in os.environ:
+        try:
+            sol.warm_start(method="encoding")
+            raise AssertionError("expected FileNotFoundError")
+        except FileNotFoundError:
+            pass
+
+
 def check_autograd_route(name):
     """A user-defined cost written with torch ops on `env.compute_distributions` (what a custom OptimizationModule does)
     gets its gradient from torch.autograd through the EgoUnroll / ParticleRollout nodes: it must equal the reference's

@@ -315,6 +315,35 @@ def generate_scene_ops():
                          ("step_ado_states", np.pad(np.stack(ado_states), ((0, 0), (0, 6 - n), (0, 0))))):
             step[key].append(val)
     out.update({k: np.array(v) if isinstance(v[0], (str, int)) else np.stack(v) for k, v in step.items()})
+
+    # scene encoding + warm start from the reference's pre-computed database (trajopt.py:466-499, :308-331). The database
+    # tensors (third_party/warm_start/encoding.pt [100,4], solution.pt [100,10,2]) are recorded as inputs of the fixture.
+    ws = dict(ws_n=[], ws_ego=[], ws_goal=[], ws_ado=[], ws_T=[], ws_encoding=[], ws_match=[], ws_warm=[])
+    enc_db = torch.load(os.path.join(rh.REFERENCE_ROOT, "third_party", "warm_start", "encoding.pt"))
+    sol_db = torch.load(os.path.join(rh.REFERENCE_ROOT, "third_party", "warm_start", "solution.pt"))
+    cwd = os.getcwd()
+    for case_id in range(40):
+        n, t_hor = 1 + case_id % 8, (3, 5, 8, 10)[case_id % 4]
+        ego = np.array([*rng.uniform(-8, 8, 2), *rng.uniform(-2, 2, 2)], dtype=np.float32)
+        goal = rng.uniform(-8, 8, 2).astype(np.float32)
+        ados = np.zeros((8, 4), dtype=np.float32)
+        ados[:n, 0:2] = rng.uniform(-9, 9, (n, 2))
+        scene = dict(env="pf", ego_kind="double", ego_pos=ego[0:2].tolist(), ego_vel=ego[2:4].tolist(), dt=0.4,
+                     ados=[dict(pos=a[0:2].tolist(), vel=(0, 0), goal=(0, 0)) for a in ados[:n]])
+        env = rh.build_env(scene)
+        solver = mantrap.solver.IPOPTSolver(env, goal=torch.tensor(goal), t_planning=t_hor, modules=[mantrap.modules.GoalNormModule])
+        encoding = solver.encode()
+        warm = solver.warm_start(method=mantrap.constants.WARM_START_ENCODING)
+        match = int(torch.argmin(torch.norm(enc_db - encoding, dim=1)))
+        assert torch.equal(warm, sol_db[match, :t_hor])
+        warm_pad = np.zeros((10, 2), dtype=np.float32)
+        warm_pad[:t_hor] = rh.to_np(warm)
+        for key, val in (("ws_n", n), ("ws_ego", ego), ("ws_goal", goal), ("ws_ado", ados), ("ws_T", t_hor),
+                         ("ws_encoding", rh.to_np(encoding)), ("ws_match", match), ("ws_warm", warm_pad)):
+            ws[key].append(val)
+    os.chdir(cwd)
+    out.update({k: np.array(v) if isinstance(v[0], int) else np.stack(v) for k, v in ws.items()})
+    out["ws_encoding_db"], out["ws_solution_db"] = rh.to_np(enc_db), rh.to_np(sol_db)
     np.savez_compressed(os.path.join(HERE, "scene_ops.npz"), **out)
     print("scene_ops: attention selected", int(out["att_euclidean"].sum()), "/", int(out["att_closest"].sum()),
           "steps", out["step_ego_states"].shape)

@@ -496,3 +496,58 @@ def check_closed_loop(lib, device, env_kind="sf", ego_kind="double", num_scenes=
         for k in range(done_at, steps):
             assert torch.equal(out.ego_trajectory[sc, k + 1], out.ego_trajectory[sc, done_at])
     return out
+
+
+def check_warm_start_encoding(lib, device):
+    """Scene encoding + nearest pre-computed solution against `TrajOptSolver.encode` / `warm_start("encoding")` of the reference
+    on 40 recorded scenes (database recorded with the fixture), and against the oracle on a random batch."""
+    from oracle import torch_oracle as to
+    g = gio.load("scene_ops")
+    enc_db, sol_db = gio.t(g["ws_encoding_db"]).to(device).contiguous(), gio.t(g["ws_solution_db"]).to(device).contiguous()
+    for i in range(len(g["ws_n"])):
+        n, t_hor = int(g["ws_n"][i]), int(g["ws_T"][i])
+        ego0, goal = gio.t(g["ws_ego"][i])[None].to(device), gio.t(g["ws_goal"][i])[None].to(device)
+        ado0 = gio.t(g["ws_ado"][i][:n])[None].to(device).contiguous()
+        enc, match, warm = engine.launch_warm_start_encoding(lib, ego0, goal, ado0, enc_db, sol_db, t_hor)
+        if device != "cpu":
+            torch.cuda.synchronize()
+        gio.assert_parity(np_(enc[0]), g["ws_encoding"][i], gio.RTOL_ROLLOUT, f"encoding {i}", atol=1e-6)
+        assert int(match[0]) == int(g["ws_match"][i]), i
+        assert np.array_equal(np_(warm[0]), g["ws_warm"][i][:t_hor]), i
+    gen = torch.Generator().manual_seed(17)
+    s, n, t_hor = 300, 20, 7
+    ego0 = torch.cat((torch.rand((s, 2), generator=gen) * 16 - 8, torch.rand((s, 2), generator=gen) * 4 - 2), dim=1)
+    goal = torch.rand((s, 2), generator=gen) * 16 - 8
+    ado0 = torch.cat((torch.rand((s, n, 2), generator=gen) * 18 - 9, torch.zeros((s, n, 2))), dim=2)
+    enc, match, warm = engine.launch_warm_start_encoding(lib, ego0.to(device), goal.to(device), ado0.to(device).contiguous(), enc_db,
+                                                         sol_db, t_hor)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    enc_ref = to.scene_encoding(ego0, goal, ado0)
+    match_ref, warm_ref = to.warm_start_encoding(enc_ref, gio.t(g["ws_encoding_db"]), gio.t(g["ws_solution_db"]), t_hor)
+    gio.assert_parity(np_(enc), enc_ref.numpy(), gio.RTOL_ROLLOUT, "encoding batch", atol=1e-6)
+    # a near tie between two database rows may resolve differently under float32 rounding of the rotation: the distance to the
+    # chosen row must equal the minimum distance to rounding
+    dist = torch.cdist(enc_ref, gio.t(g["ws_encoding_db"]))
+    chosen = dist[torch.arange(s), match.cpu().long()]
+    assert torch.all(chosen <= dist.min(dim=1).values + 1e-4)
+    same = match.cpu().long() == match_ref
+    assert float(same.float().mean()) > 0.98
+    assert torch.equal(warm.cpu()[same], warm_ref[same])
+
+
+def check_closed_loop_encoding_warm_start(lib, device):
+    """Closed loop started from the nearest pre-computed scenario of every scene: with ONE candidate per scene (= the warm
+    start itself) the first executed control is row 0 of the database solution the oracle picks."""
+    from oracle import torch_oracle as to
+    from mantrap_b200 import mpc, scenarios
+    eng = engine.Engine.from_library(lib, device) if device == "cpu" else engine.Engine(device)
+    g = gio.load("scene_ops")
+    db = (gio.t(g["ws_encoding_db"]), gio.t(g["ws_solution_db"]))
+    scene = scenarios.synthetic_scenes(6, 4, 3, regular_sigma=True, seed=5, param_seed=6)
+    scene.ego0[:, 2:4] = 0.3
+    loop = mpc.BatchedClosedLoop(eng, scene, t_planning=5, num_candidates=1, control_limits=False, speed_limits=False)
+    out = loop.solve(1, sample=False, warm_start_db=db)
+    _, warm = to.warm_start_encoding(to.scene_encoding(scene.ego0, scene.ego_goal, scene.ado0), db[0], db[1], 5)
+    assert torch.equal(out.best_index[:, 0].cpu(), torch.zeros(6, dtype=torch.int32))
+    assert torch.equal(out.controls[:, 0].cpu(), warm[:, 0])

@@ -54,6 +54,10 @@ def test_attention():
     dc.check_attention()
 
 
+def test_warm_start_encoding():
+    dc.check_warm_start_encoding()
+
+
 def test_random_search():
     dc.check_random_search(32)
 

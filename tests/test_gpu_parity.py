@@ -105,6 +105,14 @@ def test_attention(eng):
     kc.check_attention_golden(eng.lib, DEV)
 
 
+def test_closed_loop_encoding_warm_start(eng):
+    kc.check_closed_loop_encoding_warm_start(eng.lib, DEV)
+
+
+def test_warm_start_encoding(eng):
+    kc.check_warm_start_encoding(eng.lib, DEV)
+
+
 def test_env_step(eng):
     kc.check_env_step_golden(eng.lib, DEV)
 

@@ -98,6 +98,14 @@ def test_attention(emul_lib):
     kc.check_attention_golden(emul_lib, "cpu")
 
 
+def test_closed_loop_encoding_warm_start(emul_lib):
+    kc.check_closed_loop_encoding_warm_start(emul_lib, "cpu")
+
+
+def test_warm_start_encoding(emul_lib):
+    kc.check_warm_start_encoding(emul_lib, "cpu")
+
+
 def test_env_step(emul_lib):
     kc.check_env_step_golden(emul_lib, "cpu")
 

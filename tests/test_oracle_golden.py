@@ -160,3 +160,17 @@ def test_env_step():
             ego, ado = to.env_step(ego_kind, 0.4, ego, ado, gio.t(g["step_actions"][c][k])[None], gio.t(g["step_eps"][c][k][:n])[None])
             gio.assert_parity(ego[0].numpy(), g["step_ego_states"][c][k], gio.RTOL_ROLLOUT, f"ego {c}/{k}")
             gio.assert_parity(ado[0].numpy(), g["step_ado_states"][c][k][:n], gio.RTOL_ROLLOUT, f"ados {c}/{k}")
+
+
+def test_scene_encoding_and_warm_start():
+    """TrajOptSolver.encode and warm_start("encoding") (trajopt.py:466-499, :308-331) on the 40 recorded scenes."""
+    g = gio.load("scene_ops")
+    enc_db, sol_db = gio.t(g["ws_encoding_db"]), gio.t(g["ws_solution_db"])
+    assert enc_db.shape == (100, 4) and sol_db.shape == (100, 10, 2)
+    for i in range(len(g["ws_n"])):
+        n, t_hor = int(g["ws_n"][i]), int(g["ws_T"][i])
+        enc = to.scene_encoding(gio.t(g["ws_ego"][i])[None], gio.t(g["ws_goal"][i])[None], gio.t(g["ws_ado"][i][:n])[None])
+        gio.assert_parity(enc[0].numpy(), g["ws_encoding"][i], gio.RTOL_ROLLOUT, f"encoding {i}", atol=1e-6)
+        match, warm = to.warm_start_encoding(enc, enc_db, sol_db, t_hor)
+        assert int(match[0]) == int(g["ws_match"][i])
+        assert np.array_equal(warm[0].numpy(), g["ws_warm"][i][:t_hor])
