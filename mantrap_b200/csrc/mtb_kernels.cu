@@ -38,7 +38,11 @@ struct KParams {
     float4* tape_global;             // [grid][T-1][block]   when the tape does not fit in shared memory
     unsigned* mask_global;           // [grid][T-1][block][MW]
     int rows_control, rows_speed, rows_mind, rows_ell, R;
-    size_t ws_abar_bytes, ws_tape_bytes, ws_mask_bytes;   // workspace layout: mean adjoints | tape | interaction masks
+    size_t ws_abar_bytes, ws_tape_bytes, ws_mask_bytes;   // workspace layout: mean adjoints | tape | interaction masks | means | directions
+    int means_in_smem;               // 0: mus[T][N] and the acceleration directions live in an L2-resident scratch (large T * N per thread)
+    float4* mus_global;              // [grid][E][T][N]
+    float2* dir_global;              // [grid][E][T-1][N]
+    size_t ws_mus_bytes, ws_dir_bytes;
 };
 
 // misc slots (per evaluation)
@@ -214,13 +218,18 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     float* ctl = sm + prm.off_ctl;                                // [2T] controls, later the gradient staging
     float4* ego = reinterpret_cast<float4*>(sm + prm.off_ego);    // [T+1]
     float4* egobar = reinterpret_cast<float4*>(sm + prm.off_egobar);  // [T+1] adjoint from the environment
-    float4* mus = reinterpret_cast<float4*>(sm + prm.off_mus);    // [T][N]
+    // [T][N] collapsed means: shared memory, or (when T * N per resident thread is large) a per-evaluation L2-resident scratch;
+    // written by the first particle thread of an ado and read by the group after the group barrier (CTA-scope ordering)
+    float4* mus = prm.means_in_smem ? reinterpret_cast<float4*>(sm + prm.off_mus)
+                                    : prm.mus_global + ((size_t)blockIdx.x * prm.E + e) * (size_t)(T * N);
     float* posx = sm + prm.off_pos;                               // [NP4] mean positions of the current level, SoA, padded
     float* posy = posx + prm.NP4;                                 //       with +inf (radius test, four ados per load)
     // [T][N] adjoints of the means in an L2-resident scratch: seeded by the objectives, pair terms add with red.global
     float4* abar = prm.abar_global + ((size_t)blockIdx.x * prm.E + e) * (size_t)(T * N);
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);     // [GP]
-    float2* accdir = reinterpret_cast<float2*>(sm + prm.off_dir); // [T-1][N] unit directions of the acceleration differences (GRAD)
+    // [T-1][N] unit directions of the acceleration differences (GRAD); placed with the means
+    float2* accdir = prm.means_in_smem ? reinterpret_cast<float2*>(sm + prm.off_dir)
+                                       : prm.dir_global + ((size_t)blockIdx.x * prm.E + e) * (size_t)((T - 1) * N);
     // [T][N] variances of the weighted particle velocities (probability objective); the backward pass re-uses the rows as
     // the adjoint seeds of the variances
     float2* varbuf = reinterpret_cast<float2*>(sm + prm.off_var);
@@ -953,14 +962,15 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
 
     // adjoints of the means [T][N] per evaluation: L2-resident scratch (objective seeds + vector reductions of the pair terms)
     const bool abar_l2 = need_tape;
+    bool means_in_smem = true;
     auto layout = [&](int E, bool tape_in_smem) -> size_t {
         int off = 0;
         prm.off_ctl = off;    off += round_up(2 * prm.T, 4);
         prm.off_ego = off;    off += (prm.T + 1) * 4;
         prm.off_egobar = off; off += want_grad ? prm.NW * (prm.T + 1) * 4 : 0;
-        prm.off_mus = off;    off += prm.T * prm.N * 4;
+        prm.off_mus = off;    off += means_in_smem ? prm.T * prm.N * 4 : 0;
         prm.off_pos = off;    off += 2 * prm.NP4;
-        prm.off_dir = off;    off += want_grad ? round_up((prm.T - 1) * prm.N * 2, 4) : 0;
+        prm.off_dir = off;    off += (want_grad && means_in_smem) ? round_up((prm.T - 1) * prm.N * 2, 4) : 0;
         prm.off_var = off;    off += prm.keep_var ? round_up(prm.T * prm.N * 2, 4) : 0;
         prm.off_q = off;      off += round_up(prm.GP * 2, 4);
         prm.off_misc = off;   off += kMiscFloats;
@@ -977,41 +987,74 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         const int knob = env_flag("MTB_BLOCK");             // development knob: 64 / 128 / 256 threads per block
         if (knob == 64 || knob == 128 || knob == 256) target_block = knob;
     }
-    int E = (prm.GP >= target_block) ? 1 : target_block / prm.GP;
-    const long long total_evals = (long long)pb->num_scenes * pb->num_candidates;
-    if ((long long)E > total_evals) E = (int)total_evals;
-    // the block must be a multiple of a warp: with sub-warp groups keep E a multiple of 32 / GP
-    if (prm.GP < 32) E = round_up(E, 32 / prm.GP);
-    // Tape placement: shared memory when that still leaves >= 3 resident blocks per SM (registers cap the kernel at
-    // 3 x 256 threads anyway); otherwise a per-block global scratch that stays L2-resident, which trades ~30 B of L2
-    // traffic per particle step for occupancy (measured +17 % on the config-4 shape).
+    int E = 1;
     bool tape_in_smem = true;
-    if (need_tape) {
-        const size_t with_tape = layout(E, true);
-        const int resident = (int)((size_t)lim.smem_per_sm / (with_tape + 1024));
-        // (measured on the config-4 shape with 3 resident blocks either way: L2 tape 11.6 ms, shared tape 12.3 ms -- a
-        // 76 KB block leaves no L1 for the scene / baseline loads)
-        tape_in_smem = resident >= 3 && with_tape <= (size_t)32 * 1024;
-        const int knob = env_flag("MTB_TAPE_GLOBAL");       // development knob: 1 = global, 2 = shared
-        if (knob == 1) tape_in_smem = false;
-        if (knob == 2) tape_in_smem = true;
-    }
-    size_t smem = layout(E, tape_in_smem);
-    while (smem > (size_t)lim.max_smem && E * prm.GP > 32 && E > 1) {
-        E = (prm.GP < 32) ? E - 32 / prm.GP : E - 1;
-        if (E < 1) { E = 1; break; }
+    size_t smem = 0;
+    // (E, tape placement, shared-memory bytes) for the current placement of the means; returns an error code
+    auto choose = [&]() -> int {
+        E = (prm.GP >= target_block) ? 1 : target_block / prm.GP;
+        const long long total_evals = (long long)pb->num_scenes * pb->num_candidates;
+        if ((long long)E > total_evals) E = (int)total_evals;
+        // the block must be a multiple of a warp: with sub-warp groups keep E a multiple of 32 / GP
+        if (prm.GP < 32) E = round_up(E, 32 / prm.GP);
+        // Tape placement: shared memory when that still leaves >= 3 resident blocks per SM (registers cap the kernel at
+        // 3 x 256 threads anyway); otherwise a per-block global scratch that stays L2-resident, which trades ~30 B of L2
+        // traffic per particle step for occupancy (measured +17 % on the config-4 shape).
+        tape_in_smem = true;
+        if (need_tape) {
+            const size_t with_tape = layout(E, true);
+            const int resident = (int)((size_t)lim.smem_per_sm / (with_tape + 1024));
+            // (measured on the config-4 shape with 3 resident blocks either way: L2 tape 11.6 ms, shared tape 12.3 ms -- a
+            // 76 KB block leaves no L1 for the scene / baseline loads)
+            tape_in_smem = resident >= 3 && with_tape <= (size_t)32 * 1024;
+            const int knob = env_flag("MTB_TAPE_GLOBAL");       // development knob: 1 = global, 2 = shared
+            if (knob == 1) tape_in_smem = false;
+            if (knob == 2) tape_in_smem = true;
+        }
         smem = layout(E, tape_in_smem);
-    }
-    if (prm.GP < 32 && E < 32 / prm.GP) E = 32 / prm.GP;
-    smem = layout(E, tape_in_smem);
-    if (smem > (size_t)lim.max_smem) {
-        tape_in_smem = false;
-        smem = layout(E, false);
-        while (smem > (size_t)lim.max_smem && E > 1 && prm.GP >= 32) smem = layout(--E, false);
-        if (smem > (size_t)lim.max_smem) return MTB_ERR_TOO_LARGE;
+        while (smem > (size_t)lim.max_smem && E * prm.GP > 32 && E > 1) {
+            E = (prm.GP < 32) ? E - 32 / prm.GP : E - 1;
+            if (E < 1) { E = 1; break; }
+            smem = layout(E, tape_in_smem);
+        }
+        if (prm.GP < 32 && E < 32 / prm.GP) E = 32 / prm.GP;
+        smem = layout(E, tape_in_smem);
+        if (smem > (size_t)lim.max_smem) {
+            tape_in_smem = false;
+            smem = layout(E, false);
+            while (smem > (size_t)lim.max_smem && E > 1 && prm.GP >= 32) smem = layout(--E, false);
+            if (smem > (size_t)lim.max_smem) return MTB_ERR_TOO_LARGE;
+        }
+        return 0;
+    };
+    auto resident_threads = [&]() -> int {
+        int b = (int)((size_t)lim.smem_per_sm / (smem + 1024));
+        if (b < 1) b = 1;
+        const int t = b * E * prm.GP;
+        return t < 768 ? t : 768;                             // the register budget caps residency at 3 x 256 threads
+    };
+    {
+        int err2 = choose();
+        // Means placement: shared memory unless that leaves the SM far below its register-limited residency (long horizons
+        // with tiny groups, or T * N in the thousands): then mus[T][N] + the acceleration directions move to an L2-resident
+        // scratch like the tape, if that buys >= 1.25 x resident threads. Measured on B200 (T = 50, 2^18 evaluations): N = 64, P = 1
+        // 252 -> 91 ms, N = 32, P = 1 73 -> 31 ms, N = 8, P = 1 16.0 -> 6.4 ms, N = 2, P = 1 4.8 -> 3.2 ms; never more than 5 % slower where
+        // shared memory was not the limit, and those shapes keep it.
+        const int knob = env_flag("MTB_MEANS_GLOBAL");        // development knob: 1 = global, 2 = shared
+        if (knob == 1 || (knob == 0 && (err2 != 0 || resident_threads() < 768))) {
+            const int err_smem = err2, res_smem = (err2 == 0) ? resident_threads() : 0;
+            const int e_keep = E; const bool t_keep = tape_in_smem; const size_t s_keep = smem;
+            means_in_smem = false;
+            err2 = choose();
+            if (knob != 1 && err_smem == 0 && (err2 != 0 || resident_threads() * 100 < res_smem * 125)) {
+                means_in_smem = true; E = e_keep; tape_in_smem = t_keep; smem = layout(E, tape_in_smem); (void)s_keep; err2 = 0;
+            }
+        }
+        if (err2 != 0) return err2;
     }
     prm.E = E;
     prm.tape_in_smem = tape_in_smem ? 1 : 0;
+    prm.means_in_smem = means_in_smem ? 1 : 0;
     prm.num_evals = (long long)pb->num_scenes * pb->num_candidates;
     const int evals_per_unit = (prm.GP <= 32) ? 32 / prm.GP : 1;          // unit = warp of sub-warp groups, or one group
     prm.num_items = (int)((prm.num_evals + evals_per_unit - 1) / evals_per_unit);
@@ -1035,7 +1078,9 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         prm.ws_tape_bytes = (size_t)grid * (prm.T - 1) * block * sizeof(float4);
         prm.ws_mask_bytes = need_mask ? (size_t)grid * (prm.T - 1) * block * prm.MW * sizeof(unsigned) : 0;
     }
-    workspace_bytes = prm.ws_abar_bytes + prm.ws_tape_bytes + prm.ws_mask_bytes;
+    prm.ws_mus_bytes = means_in_smem ? 0 : (size_t)grid * E * prm.T * prm.N * sizeof(float4);
+    prm.ws_dir_bytes = (means_in_smem || !want_grad || prm.T < 2) ? 0 : (size_t)grid * E * (prm.T - 1) * prm.N * sizeof(float2);
+    workspace_bytes = prm.ws_abar_bytes + prm.ws_tape_bytes + prm.ws_mask_bytes + prm.ws_mus_bytes + prm.ws_dir_bytes;
     info.grid = grid;
     info.block = block;
     info.evals_per_block = E;
@@ -1157,6 +1202,11 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
         if (prm.ws_tape_bytes > 0) {
             prm.tape_global = reinterpret_cast<float4*>(base + prm.ws_abar_bytes);
             prm.mask_global = reinterpret_cast<unsigned*>(base + prm.ws_abar_bytes + prm.ws_tape_bytes);
+        }
+        if (prm.ws_mus_bytes > 0) {
+            char* mb = base + prm.ws_abar_bytes + prm.ws_tape_bytes + prm.ws_mask_bytes;
+            prm.mus_global = reinterpret_cast<float4*>(mb);
+            prm.dir_global = reinterpret_cast<float2*>(mb + prm.ws_mus_bytes);
         }
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

@@ -281,3 +281,18 @@ def test_rejects_cpu_tensors(eng):
     scene = scenarios.synthetic_scenes(1, 3, 2)
     with pytest.raises(RuntimeError):
         eng.evaluate(scene, scenarios.candidate_controls(1, 1, 4), None, want=("total",))
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor,weights", [
+    ("sf", "double", 4, 16, 20, 3, 12, {"goal": 0.5, "acc": 1.0}),
+    ("sf", "double", 3, 40, 2, 2, 50, {"goal": 0.5, "acc": 1.0}),            # tiny groups, long horizon: the plan picks it itself
+    ("sf", "double", 1, 4, 48, 2, 40, {"goal": 0.5, "acc": 1.0, "prob": 1.0}),  # T * N = 1920 means per evaluation
+    ("pf", "single", 2, 9, 5, 5, 15, {"goal": 0.5, "pos": 1.0}),
+])
+def test_means_in_l2_scratch(eng, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor, weights):
+    """Means in the L2-resident scratch (forced by the development knob, and chosen by the plan for the long-horizon shapes)."""
+    monkeypatch.setenv("MTB_MEANS_GLOBAL", "1")
+    kc.check_batched_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)
+    kc.check_modules(eng.lib, DEV, "c4_sf_n20_p3_t12")
+    monkeypatch.delenv("MTB_MEANS_GLOBAL")
+    kc.check_batched_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)

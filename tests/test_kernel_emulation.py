@@ -124,3 +124,18 @@ def test_argmin(emul_lib):
     assert idx.tolist() == [1, 0, -1]
     assert val[:2].tolist() == [1.0, 4.0] and torch.isinf(val[2])
     assert torch.equal(best[0], controls[0, 1]) and torch.equal(best[1], controls[1, 0])
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor,weights", [
+    ("sf", "double", 2, 3, 4, 3, 6, {"goal": 0.5, "acc": 1.0}),
+    ("sf", "single", 1, 3, 12, 3, 5, {"goal": 0.5, "vel": 1.0, "pos": 1.0}),
+    ("sf", "double", 2, 3, 5, 4, 6, {"goal": 0.5, "prob": 1.0, "acc": 1.0}),
+    ("pf", "double", 2, 2, 5, 5, 7, {"goal": 0.5, "acc": 1.0}),
+])
+def test_means_in_l2_scratch(emul_lib, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor, weights):
+    """The alternative placement of the collapsed means (L2-resident scratch instead of shared memory, chosen by the launch plan
+    for long horizons / many ados) gives the same results: forced through the development knob."""
+    monkeypatch.setenv("MTB_MEANS_GLOBAL", "1")
+    kc.check_batched_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights)
+    kc.check_modules(emul_lib, "cpu", "c4_sf_n20_p3_t12")
+    kc.check_constraints(emul_lib, "cpu", "c3_sf_n10_p4_t20")
