@@ -1035,13 +1035,13 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     };
     {
         int err2 = choose();
-        // Means placement: shared memory unless that leaves the SM far below its register-limited residency (long horizons
+        // Means placement: shared memory unless that leaves fewer than 512 resident threads per SM (long horizons
         // with tiny groups, or T * N in the thousands): then mus[T][N] + the acceleration directions move to an L2-resident
         // scratch like the tape, if that buys >= 1.25 x resident threads. Measured on B200 (T = 50, 2^18 evaluations): N = 64, P = 1
-        // 252 -> 91 ms, N = 32, P = 1 73 -> 31 ms, N = 8, P = 1 16.0 -> 6.4 ms, N = 2, P = 1 4.8 -> 3.2 ms; never more than 5 % slower where
-        // shared memory was not the limit, and those shapes keep it.
+        // 252 -> 91 ms, N = 32, P = 1 73 -> 31 ms, N = 8, P = 1 16.0 -> 6.4 ms, N = 2, P = 1 4.8 -> 3.2 ms; shapes that
+        // already hold 512 threads gain nothing or lose up to 19 % from the move and keep shared memory.
         const int knob = env_flag("MTB_MEANS_GLOBAL");        // development knob: 1 = global, 2 = shared
-        if (knob == 1 || (knob == 0 && (err2 != 0 || resident_threads() < 768))) {
+        if (knob == 1 || (knob == 0 && (err2 != 0 || resident_threads() < 512))) {
             const int err_smem = err2, res_smem = (err2 == 0) ? resident_threads() : 0;
             const int e_keep = E; const bool t_keep = tape_in_smem; const size_t s_keep = smem;
             means_in_smem = false;
