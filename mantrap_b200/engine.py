@@ -22,6 +22,30 @@ OBJECTIVE_KEYS = ("goal", "acc", "vel", "pos", "prob")     # columns of `obj` / 
 NUM_OBJECTIVES = len(OBJECTIVE_KEYS)
 
 
+PACKED_COPY_MAX_FLOATS = 1 << 16
+
+
+def to_device_packed(tensors: typing.Sequence[typing.Optional[torch.Tensor]], device) -> typing.List[typing.Optional[torch.Tensor]]:
+    """fp32 contiguous copies of `tensors` (None stays None) on `device`. A small all-host set going to a GPU (the one-scene
+    batch of a solver callback: eight tensors of a few hundred bytes) is staged in ONE host buffer and moved with ONE
+    host->device copy, every tensor a 16-byte aligned view of it: per-copy driver latency, not bandwidth, is the cost there.
+    Large sets (batched scenes) are copied one by one, without the extra host pass."""
+    device = torch.device(device)
+    live = [t for t in tensors if t is not None]
+    total = sum(-(-t.numel() // 4) * 4 for t in live)
+    if device.type != "cuda" or len(live) < 2 or total > PACKED_COPY_MAX_FLOATS or any(t.device.type != "cpu" for t in live):
+        return [None if t is None else t.to(device=device, dtype=torch.float32).contiguous() for t in tensors]
+    stage = torch.empty(total, dtype=torch.float32)
+    spans, offset = [], 0
+    for t in live:
+        stage[offset:offset + t.numel()].copy_(t.reshape(-1))
+        spans.append((offset, t.numel(), t.shape))
+        offset += -(-t.numel() // 4) * 4
+    moved = stage.to(device)
+    views = iter(moved[o:o + n].view(shape) for o, n, shape in spans)
+    return [None if t is None else next(views) for t in tensors]
+
+
 @dataclasses.dataclass
 class SceneBatch:
     """S scenes with N ados and P particles per ado. All tensors float32, contiguous, on one device.
@@ -59,12 +83,11 @@ class SceneBatch:
     def device(self) -> torch.device:
         return self.ado0.device
 
+    _TENSOR_FIELDS = ("ego0", "ego_goal", "ado0", "ado_goal", "v0", "sigma", "weight", "noise")
+
     def to(self, device) -> "SceneBatch":
-        def mv(x):
-            return None if x is None else x.to(device=device, dtype=torch.float32).contiguous()
-        return dataclasses.replace(self, ego0=mv(self.ego0), ego_goal=mv(self.ego_goal), ado0=mv(self.ado0),
-                                   ado_goal=mv(self.ado_goal), v0=mv(self.v0), sigma=mv(self.sigma),
-                                   weight=mv(self.weight), noise=mv(self.noise))
+        vals = [getattr(self, f) for f in self._TENSOR_FIELDS]
+        return dataclasses.replace(self, **dict(zip(self._TENSOR_FIELDS, to_device_packed(vals, device))))
 
     def without_ego(self) -> "SceneBatch":
         return dataclasses.replace(self, ego_kind=None)

@@ -226,12 +226,14 @@ class TrajOptSolver:
         out = hit if hit is not None else {}
         if hit is None:
             res = engine.evaluate(scene, controls, spec, want=("obj", "total", "grad", "cons", "violation"))
-            obj = res["obj"][0, 0].cpu().numpy()
-            cons = res["cons"][0, 0].cpu().numpy()
+            # one device->host read for all five results (each .cpu() is a stream synchronisation of its own)
+            parts = [res[k][0, 0].reshape(-1) for k in ("obj", "cons", "grad", "total", "violation")]
+            flat = torch.cat(parts).cpu().numpy()
+            obj, cons, grad, total, violation = np.split(flat, np.cumsum([p.numel() for p in parts])[:-1])
             out.update(obj={m.name: float(obj[OBJECTIVE_KEYS.index(m.fused_key)]) for m in self.modules
                             if getattr(m, "fused_key", None) is not None},
-                       total=float(res["total"][0, 0]), grad=res["grad"][0, 0].cpu().numpy().flatten().astype(np.float64),
-                       violation=float(res["violation"][0, 0]), cons=self._split_rows(cons, ado_ids, spec))
+                       total=float(total[0]), grad=grad.astype(np.float64), violation=float(violation[0]),
+                       cons=self._split_rows(cons, ado_ids, spec))
         if want_jacobian:
             jac = engine.constraint_jacobian(scene, controls, spec)[0, 0].cpu().numpy().astype(np.float64)
             out["jac"] = self._split_rows(jac, ado_ids, spec)

@@ -94,3 +94,34 @@ def test_ipopt_solver_reports_missing_cyipopt():
     sol = solver.IPOPTSolver(env, goal=goal, t_planning=3, modules=dc.solver.IPOPTSolver.module_hard())
     with pytest.raises(ImportError):
         sol.optimize(torch.zeros(6), tag="t")
+
+
+@pytest.mark.parametrize("env_kind", ["sf", "pf"])
+@pytest.mark.parametrize("num_ados,num_particles", [(0, 5), (1, 2), (3, 5), (8, 10), (2, 17)])
+def test_particle_draw_follows_the_reference_rng_stream(env_kind, num_ados, num_particles):
+    """`draw_particle_parameters` consumes torch's global CPU generator exactly as the reference's `create_particles`
+    (particle.py:40-79: one Normal(loc, scale).sample((P,)) + .cdf per (ado, parameter)) followed by one torch.rand per
+    step (particle.py:165) does, bit for bit, including above 16 particles where torch switches its normal sampler."""
+    import torch
+    from mantrap_b200 import environment
+    cls = {"sf": environment.SocialForcesEnvironment, "pf": environment.PotentialFieldEnvironment}[env_kind]
+    env = cls(ego_position=torch.tensor([-5.0, 0.0]), ego_velocity=torch.tensor([1.0, 0.0]))
+    for i in range(num_ados):
+        env.add_ado(position=torch.tensor([float(i), 2.0]), velocity=torch.tensor([0.0, -1.0]), goal=torch.tensor([0.0, -5.0]))
+    torch.manual_seed(7)
+    got = env.draw_particle_parameters(num_particles, 9)
+    after = torch.rand(1)
+    torch.manual_seed(7)
+    k = len(env.param_defaults)
+    samples, cdfs = torch.zeros(num_ados, k, num_particles), torch.zeros(num_ados, k, num_particles)
+    for m in range(num_ados):
+        for ip, (loc, scale) in enumerate(env.param_defaults.values()):
+            dist = torch.distributions.Normal(loc, scale)
+            samples[m, ip] = dist.sample((num_particles,))
+            cdfs[m, ip] = dist.cdf(samples[m, ip])
+    weight = torch.prod(cdfs, dim=1)
+    weight = weight / torch.norm(weight, dim=0)
+    noise = torch.stack([torch.rand((num_ados, num_particles, 2)) for _ in range(9)])[None]
+    assert torch.equal(got["v0"][0], samples[:, 0]) and torch.equal(got["weight"][0], weight)
+    assert k == 1 or torch.equal(got["sigma"][0], samples[:, 1])
+    assert torch.equal(got["noise"], noise) and torch.equal(after, torch.rand(1))
