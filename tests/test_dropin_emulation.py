@@ -125,3 +125,14 @@ def test_particle_draw_follows_the_reference_rng_stream(env_kind, num_ados, num_
     assert torch.equal(got["v0"][0], samples[:, 0]) and torch.equal(got["weight"][0], weight)
     assert k == 1 or torch.equal(got["sigma"][0], samples[:, 1])
     assert torch.equal(got["noise"], noise) and torch.equal(after, torch.rand(1))
+
+
+def test_scene_copy_to_host_keeps_values_and_none():
+    """`to_device_packed` towards a non-GPU device is the plain per-tensor fp32 copy (the staged single copy is GPU-only and
+    covered by tests/test_gpu_dropin.py::test_packed_scene_copy)."""
+    import torch
+    from mantrap_b200.engine import to_device_packed
+    src = [None, torch.arange(6.0).double().view(2, 3), torch.ones(5)[::2]]
+    out = to_device_packed(src, "cpu")
+    assert out[0] is None and out[1].dtype == torch.float32 and torch.equal(out[1], src[1].float())
+    assert out[2].is_contiguous() and out[2].tolist() == [1.0, 1.0, 1.0]

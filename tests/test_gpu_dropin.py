@@ -72,3 +72,30 @@ def test_mcts():
 def test_closed_loop_mcts():
     from mantrap_b200 import solver
     dc.check_closed_loop(solver.MonteCarloTreeSearch, "sf", steps=4, num_breadth_samples=64, num_depth_samples=64, max_cpu_time=60.0)
+
+
+def test_packed_scene_copy():
+    """`SceneBatch.to` of a small host scene (one staged host->device copy): every tensor arrives bit-identical, fp32,
+    contiguous and 16-byte aligned (the kernels read states as float4), None stays None, and the large-batch path (one
+    copy per tensor) gives the same values."""
+    import torch
+    from mantrap_b200 import engine, scenarios
+    for s, n, p in ((1, 3, 5), (1, 1, 2), (3, 7, 3), (400, 20, 3)):
+        scene = scenarios.synthetic_scenes(s, n, p, env_kind="sf")
+        scene.noise = torch.rand((s, 9, n, p, 2))
+        scene.ego_goal = torch.rand((s, 2)).double()            # converted on the way
+        packed = sum(-(-t.numel() // 4) * 4 for t in (getattr(scene, f) for f in scene._TENSOR_FIELDS) if t is not None)
+        assert (packed <= engine.PACKED_COPY_MAX_FLOATS) == (s < 400)      # both paths are exercised
+        moved = scene.to("cuda:0")
+        for f in scene._TENSOR_FIELDS:
+            src, dst = getattr(scene, f), getattr(moved, f)
+            if src is None:
+                assert dst is None
+                continue
+            assert dst.device.type == "cuda" and dst.dtype == torch.float32 and dst.is_contiguous() and dst.shape == src.shape
+            assert dst.data_ptr() % 16 == 0
+            assert torch.equal(dst.cpu(), src.float())
+        again = moved.to("cuda:0")                               # already on the device: no staging, same values
+        assert torch.equal(again.ado0, moved.ado0)
+    out = engine.to_device_packed([None, torch.ones(3), None, torch.arange(5.0)], "cuda:0")
+    assert out[0] is None and out[2] is None and out[1].tolist() == [1.0] * 3 and out[3].tolist() == [0.0, 1.0, 2.0, 3.0, 4.0]
