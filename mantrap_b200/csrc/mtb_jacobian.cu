@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(MAXT, MINB) jacobian_kernel(const JParams prm)
                     const float ep = ego_tangent(ego_kind, dt, level, dg >> 1).x;
                     const float val = (dg & 1) ? 2.0f * (eg.y - mu.y) / fmaxf(sv.y, prm.md.ellipsoid_min_scale) * ep
                                                : 2.0f * (eg.x - mu.x) / fmaxf(sv.x, prm.md.ellipsoid_min_scale) * ep;
-                    jac[(size_t)(base_ell + k * T + level) * two_t + dg] = val;
+                    jac[(size_t)(base_ell + k * T + level) * two_t + dg] = sanitize(val);
                 }
             }
             if (!want_mind) return;
@@ -200,7 +200,9 @@ __global__ void __launch_bounds__(MAXT, MINB) jacobian_kernel(const JParams prm)
                     const float ex = (dg & 1) ? 0.f : ep, ey = (dg & 1) ? ep : 0.f;
                     val = (dx * (ex - md_.x) + dy * (ey - md_.y)) / nn;
                 }
-                jac[(size_t)(base_mind + k * T + level) * two_t + dg] = val;
+                // np.nan_to_num of compute_gradient_auto_grad (optimization_module.py:440-446): a tangent poisoned by a
+                // non-finite local derivative (a sampled sigma <= 0, DESIGN.md "parity domain") is reported as 0, never as NaN
+                jac[(size_t)(base_mind + k * T + level) * two_t + dg] = sanitize(val);
             }
         };
         write_rows(0, mus, mud, varl);

@@ -141,13 +141,6 @@ MTB_DEV unsigned radius_bits4(unsigned acc, float4 X, float4 Y, float px, float 
 #endif
 }
 
-MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py:446)
-    if (is_nan(x)) return 0.f;
-    if (x > FLT_MAX) return FLT_MAX;
-    if (x < -FLT_MAX) return -FLT_MAX;
-    return x;
-}
-
 MTB_DEV float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 
 // Adjoint seed of the interaction objectives on mus[k, level] (level >= 1): (d/d mu_p, d/d mu_v).

@@ -39,6 +39,12 @@ MTB_DEV void axpy(V2& y, float a, V2 x) { y.x = fmaf(a, x.x, y.x); y.y = fmaf(a,
 #endif
 MTB_DEV float dot(V2 a, V2 b) { return a.x * b.x + a.y * b.y; }
 MTB_DEV bool is_nan(float x) { return x != x; }
+MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py:446)
+    if (is_nan(x)) return 0.f;
+    if (x > FLT_MAX) return FLT_MAX;
+    if (x < -FLT_MAX) return -FLT_MAX;
+    return x;
+}
 
 // ---------------------------------------------------------------------------------------------------------
 // Social-forces repulsion  F = dV/dr,  V = v0 exp(-b/sigma),  b = 1/2 sqrt((|r| + |r - w dt|)^2 - (dt |w|)^2)

@@ -248,6 +248,33 @@ def check_jacobian_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_ca
     return worst
 
 
+def check_jacobian_sampled_sigma_nonpositive(lib, device):
+    """Outside the parity domain: a particle whose sampled sigma is <= 0 (the reference draws sigma from a Normal, so this
+    happens with small probability) has a non-finite local derivative; the reference's autograd then returns NaN and
+    `np.nan_to_num` (optimization_module.py:440-446) reports zeros. The tangent kernel must never emit a non-finite entry
+    either (an optimiser cannot use it), and scenes of the same batch without such a particle are unaffected."""
+    from oracle import torch_oracle as to
+    from mantrap_b200 import scenarios
+    s, c, n, p, t_hor = 6, 2, 5, 4, 8
+    scene_cpu = scenarios.synthetic_scenes(s, n, p, env_kind="sf", seed=41, param_seed=42, regular_sigma=True)
+    scene_cpu.sigma[1, 2, 0] = -0.04                 # one particle each in scenes 1 and 4
+    scene_cpu.sigma[4, 0, 3] = 0.0
+    controls_cpu = scenarios.candidate_controls(s, c, t_hor, seed=43, u_max=1.0)
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True, ellipsoid=True)
+    jac, values = engine.launch_jacobian(lib, scene_cpu.to(device), controls_cpu.to(device).contiguous(), spec, want_values=True)
+    if device != "cpu":
+        torch.cuda.synchronize()
+    assert bool(torch.isfinite(jac).all()) and bool(torch.isfinite(values).all())
+    jac = np_(jac)
+    n_ctl, n_spd, n_md = 2 * t_hor, 2 * (t_hor + 1), n * t_hor
+    osc = oracle_scene(scene_cpu, c)
+    for sc in (0, 2, 3, 5):                          # regular scenes: same result as without the degenerate neighbours
+        b = sc * c
+        one = to.Scene(*[(x[b:b + 1] if isinstance(x, torch.Tensor) else x) for x in osc])
+        _, j_ref = to.min_distance_jacobian(one, controls_cpu.reshape(-1, t_hor, 2)[b:b + 1])
+        gio.assert_parity(jac[sc, 0, n_ctl + n_spd:n_ctl + n_spd + n_md], j_ref.numpy(), gio.RTOL_GRAD, "jac min-distance", atol=gio.ATOL + 1e-5)
+
+
 def oracle_scene(scene, num_candidates):
     """Expand a SceneBatch (CPU copy) to the oracle's per-evaluation batch layout [S*C, ...]."""
     from oracle import torch_oracle as to

@@ -321,3 +321,7 @@ def test_means_placement_is_bit_identical(eng, monkeypatch, s, c, n, p, t_hor):
         ga, gb = torch.nan_to_num(res[knob]["grad"]).reshape(s * c, -1), torch.nan_to_num(res["2"]["grad"]).reshape(s * c, -1)
         rel = (ga - gb).abs().amax(dim=1) / (gb.abs().amax(dim=1) + 1e-12)
         assert float(rel.median()) < 1e-5 and float(rel.quantile(0.95)) < 1e-3, (knob, float(rel.median()), float(rel.max()))
+
+
+def test_jacobian_sampled_sigma_nonpositive(eng):
+    kc.check_jacobian_sampled_sigma_nonpositive(eng.lib, DEV)

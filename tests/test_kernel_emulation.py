@@ -139,3 +139,7 @@ def test_means_in_l2_scratch(emul_lib, monkeypatch, env_kind, ego_kind, s, c, n,
     kc.check_batched_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights)
     kc.check_modules(emul_lib, "cpu", "c4_sf_n20_p3_t12")
     kc.check_constraints(emul_lib, "cpu", "c3_sf_n10_p4_t20")
+
+
+def test_jacobian_sampled_sigma_nonpositive(emul_lib):
+    kc.check_jacobian_sampled_sigma_nonpositive(emul_lib, "cpu")
