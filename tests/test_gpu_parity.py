@@ -69,6 +69,9 @@ def test_jacobian_golden(eng, name):
     ("pf", "double", 1, 3, 5, 5, 15),
     ("pf", "single", 2, 2, 7, 2, 9),
     ("kalman", "double", 1, 2, 5, 1, 15),
+    ("sf", "double", 1, 1, 1, 2, 1),            # T = 1: no particle step, one ado
+    ("pf", "single", 2, 2, 1, 2, 1),
+    ("sf", "double", 1, 1, 34, 2, 3),           # N > 32: two interaction mask words
 ])
 def test_jacobian_vs_oracle(eng, env_kind, ego_kind, s, c, n, p, t_hor):
     kc.check_jacobian_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor)

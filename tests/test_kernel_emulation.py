@@ -65,6 +65,9 @@ def test_jacobian_golden(emul_lib, name):
     ("sf", "single", 1, 2, 5, 2, 5),
     ("pf", "double", 1, 2, 5, 3, 7),
     ("kalman", "double", 1, 1, 3, 1, 5),
+    ("sf", "double", 1, 1, 1, 2, 1),            # T = 1: no particle step, one ado
+    ("pf", "single", 2, 2, 1, 2, 1),
+    ("sf", "double", 1, 1, 34, 2, 3),           # N > 32: two interaction mask words
 ])
 def test_jacobian_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor):
     kc.check_jacobian_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor)
