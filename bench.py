@@ -126,17 +126,22 @@ def workload_config(args, world):
 
 
 class ClockSampler:
-    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    """Samples SM clocks and throttle reasons with nvidia-smi DURING the timed region. nvidia-smi needs a few hundred
+    milliseconds to start (more on a busy 8-GPU box), which is as long as a short timed region: the process is therefore started
+    before the warm-up steps and streams one row every 50 ms; `mark_start` / `mark_stop` bracket the timed region on the host
+    clock and only rows that arrived inside the bracket are reported (`window`: "timed"). If none did (pathological), the rows
+    closest to the bracket are used and `window` says "nearest"."""
     QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
+        self.t0 = self.t1 = None
 
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "50", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:
@@ -145,7 +150,13 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.monotonic(), [x.strip() for x in line.split(",")]))
+
+    def mark_start(self):
+        self.t0 = time.monotonic()
+
+    def mark_stop(self):
+        self.t1 = time.monotonic()
 
     def __exit__(self, *exc):
         if self.proc is not None:
@@ -153,15 +164,24 @@ class ClockSampler:
             self.thread.join(timeout=2)
 
     def summary(self):
-        sm = sorted(float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit())
+        rows = [(ts, r) for ts, r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        t0 = self.t0 if self.t0 is not None else float("-inf")
+        t1 = self.t1 if self.t1 is not None else float("inf")
+        inside = [r for ts, r in rows if t0 <= ts <= t1]
+        window = "timed"
+        if not inside and rows:
+            window = "nearest"
+            mid = 0.5 * (max(t0, rows[0][0]) + min(t1, rows[-1][0]))
+            inside = [r for _, r in sorted(rows, key=lambda x: abs(x[0] - mid))[:3]]
+        sm = sorted(float(r[0]) for r in inside)
         reasons = set()
-        for r in self.rows:
-            if len(r) >= 7:
-                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
-                    if val.lower().startswith("active"):
-                        reasons.add(name)
-        smax = max((float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()), default=None)
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
+        for r in inside:
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        smax = max((float(r[1]) for r in inside if r[1].replace(".", "").isdigit()), default=None)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm),
+                "window": window}
 
 
 def measure_peaks(eng, torch):
@@ -297,17 +317,19 @@ def main():
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    for _ in range(args.warmup):
-        step()
-    barrier()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank) as clocks:          # started before the warm-up: see the class docstring
+        for _ in range(args.warmup):
+            step()
+        barrier()
+        clocks.mark_start()
         start.record()
         for k in range(args.steps):
             step(ev[k])
         stop.record()
         barrier()
+        clocks.mark_stop()
     ms_total = start.elapsed_time(stop)
     kernel_ms = sum(a.elapsed_time(b) for a, b in ev) / args.steps
     t_ms = torch.tensor([ms_total], dtype=torch.float64, device=dev)

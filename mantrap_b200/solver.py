@@ -17,6 +17,7 @@ solver/base/search.py:11-108; RandomSearch solver/baselines/random_search.py:9-3
 launch + device argmin instead of one candidate per Python iteration). `SLSQPSolver` drives the same four callbacks
 with scipy and is NOT IPOPT; it exists for end-to-end checks of the callbacks.
 """
+import dataclasses
 import time
 import typing
 
@@ -24,7 +25,7 @@ import numpy as np
 import torch
 
 from . import constants, modules as mods, runtime
-from .engine import OBJECTIVE_KEYS, ModuleSpec
+from .engine import OBJECTIVE_KEYS, ModuleSpec, SceneBatch, to_device_packed
 
 
 class TrajOptSolver:
@@ -212,7 +213,7 @@ class TrajOptSolver:
         if hit is not None and (not want_jacobian or "jac" in hit):
             return hit
         engine = runtime.default_engine()
-        controls = torch.from_numpy(np.asarray(z, dtype=np.float32)).view(1, 1, -1, 2).to(engine.device).contiguous()
+        controls = torch.from_numpy(np.asarray(z, dtype=np.float32)).view(1, 1, -1, 2)
         rollout = any(m.needs_rollout for m in self.modules)
         env = self.env
         if rollout:
@@ -221,7 +222,10 @@ class TrajOptSolver:
         else:
             scene = self.modules[0]._scene().to("cpu")
         scene.ego_goal = self.goal.view(1, 2).clone()
-        scene = scene.to(engine.device)
+        # scene and controls travel together: one staged host->device copy per callback (engine.to_device_packed)
+        fields = SceneBatch._TENSOR_FIELDS
+        moved = to_device_packed([getattr(scene, f) for f in fields] + [controls], engine.device)
+        scene, controls = dataclasses.replace(scene, **dict(zip(fields, moved[:-1]))), moved[-1]
         spec = self._fused_spec(ado_ids)
         out = hit if hit is not None else {}
         if hit is None:
