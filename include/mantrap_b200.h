@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define MTB_ABI_VERSION 5
+#define MTB_ABI_VERSION 6
 
 /* environment kinds: mantrap/environment/social_forces.py, simplified/potential_field.py, simplified/kalman.py */
 #define MTB_ENV_SOCIAL_FORCES 0
@@ -144,7 +144,9 @@ typedef struct mtb_outputs {
 typedef struct mtb_launch_info {
     int32_t grid, block, evals_per_block, group_size;
     int32_t smem_bytes, tape_in_smem;
-    int32_t num_items, blocks_per_sm;
+    int32_t num_items, blocks_per_sm;      /* blocks_per_sm = resident blocks of the launched instantiation (registers and shared memory) */
+    int32_t variant_maxt, variant_minb;    /* __launch_bounds__ of the instantiation */
+    int32_t kernel_kind, evals_per_thread; /* 0 = evaluate_kernel (one evaluation per group of threads) */
 } mtb_launch_info;
 
 int mtb_abi_version(void);

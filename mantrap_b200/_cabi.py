@@ -12,7 +12,7 @@ import torch
 ENV_SOCIAL_FORCES, ENV_POTENTIAL_FIELD, ENV_KALMAN = 0, 1, 2
 EGO_DOUBLE_INTEGRATOR, EGO_SINGLE_INTEGRATOR, EGO_NONE = 0, 1, 2
 MAX_ADOS, MAX_HORIZON = 64, 64
-ABI_VERSION = 5
+ABI_VERSION = 6
 ATTENTION_EUCLIDEAN, ATTENTION_CLOSEST = 0, 1
 
 _f, _i, _p = ctypes.c_float, ctypes.c_int32, ctypes.c_void_p
@@ -45,7 +45,8 @@ class MtbOutputs(ctypes.Structure):
 
 class MtbLaunchInfo(ctypes.Structure):
     _fields_ = [("grid", _i), ("block", _i), ("evals_per_block", _i), ("group_size", _i), ("smem_bytes", _i),
-                ("tape_in_smem", _i), ("num_items", _i), ("blocks_per_sm", _i)]
+                ("tape_in_smem", _i), ("num_items", _i), ("blocks_per_sm", _i), ("variant_maxt", _i), ("variant_minb", _i),
+                ("kernel_kind", _i), ("evals_per_thread", _i)]
 
 
 EXPORTED_SYMBOLS = ("mtb_abi_version", "mtb_error_string", "mtb_num_constraint_rows", "mtb_workspace_bytes",

@@ -6,6 +6,9 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 LIB_PATH = os.path.join(HERE, "libmantrap_b200.so")
+# test-only variant with the launch-geometry development knobs (-DMTB_DEV_KNOBS): the production library never reads the
+# environment; two placement tests load this one through Engine.from_library
+DEV_LIB_PATH = os.path.join(HERE, "libmantrap_b200_dev.so")
 SOURCES = [os.path.join(HERE, "csrc", name) for name in ("mtb_kernels.cu", "mtb_jacobian.cu", "mtb_ego.cu", "mtb_scene.cu", "mtb_probe.cu")]
 DEPS = SOURCES + [os.path.join(HERE, "csrc", "mtb_math.cuh"), os.path.join(HERE, "csrc", "mtb_common.cuh"), os.path.join(ROOT, "include", "mantrap_b200.h")]
 # --use_fast_math: MUFU rsqrt / rcp / ex2 instead of the IEEE division / sqrt / expf sequences (each ~10 instructions
@@ -23,12 +26,12 @@ def nvcc() -> str:
     return path
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    extra = os.environ.get("MTB_NVCC_EXTRA", "").split()      # development knob (e.g. --use_fast_math experiments)
-    if not force and not extra and os.path.exists(LIB_PATH) and \
-            all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in DEPS):
-        return LIB_PATH
-    cmd = [nvcc(), *NVCC_FLAGS, *extra, "-I", os.path.join(ROOT, "include"), "-I", os.path.join(HERE, "csrc"), "-o", LIB_PATH, *SOURCES]
+def build(force: bool = False, verbose: bool = False, dev_knobs: bool = False) -> str:
+    out = DEV_LIB_PATH if dev_knobs else LIB_PATH
+    extra = ["-DMTB_DEV_KNOBS"] if dev_knobs else []
+    if not force and os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in DEPS):
+        return out
+    cmd = [nvcc(), *NVCC_FLAGS, *extra, "-I", os.path.join(ROOT, "include"), "-I", os.path.join(HERE, "csrc"), "-o", out, *SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
@@ -37,7 +40,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError(f"nvcc failed:\n{proc.stdout}\n{proc.stderr}")
     if verbose:
         print(proc.stderr)
-    return LIB_PATH
+    return out
 
 
 if __name__ == "__main__":

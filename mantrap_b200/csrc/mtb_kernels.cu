@@ -15,9 +15,14 @@
 #include "mtb_common.cuh"
 #include "mtb_math.cuh"
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 namespace mtb {
 
 constexpr int kDefaultBlock = 256;
+static std::mutex& inst_mutex() { static std::mutex m; return m; }
 
 struct KParams {
     mtb_problem pb;
@@ -910,11 +915,34 @@ __global__ void argmin_kernel(const float* __restrict__ total, const float* __re
 // ---------------------------------------------------------------------------------------------------------
 // host side: launch geometry
 // ---------------------------------------------------------------------------------------------------------
-// development knobs (read once per call; unset in production)
+// Development knobs (launch geometry overrides read from the environment) exist only in the -DMTB_DEV_KNOBS variant of the
+// library that two placement tests build; the production library never looks at the environment.
+#ifdef MTB_DEV_KNOBS
 static int env_flag(const char* name) {
     const char* v = std::getenv(name);
     return (v != nullptr && v[0] != '\0') ? std::atoi(v) : 0;
 }
+#else
+static constexpr int env_flag(const char*) { return 0; }
+#endif
+
+// Launch-bounds variant of evaluate_kernel for a block size and the number of blocks shared memory would admit.
+struct Variant {
+    int maxt, minb;
+};
+static Variant pick_variant(int block, int blocks_by_smem) {
+    if (block > kDefaultBlock) return {kMaxThreads, 1};
+    const int force = env_flag("MTB_MINB");
+    if (force == 4) return {kDefaultBlock, 4};
+    if (force == 3 || (force == 0 && blocks_by_smem >= 3)) return {kDefaultBlock, 3};
+    return {kDefaultBlock, 2};
+}
+// launch + residency query of one instantiation (filled in below the kernel)
+struct InstOps {
+    int (*launch)(const KParams&, const mtb_launch_info&, cudaStream_t);
+    int (*resident_blocks)(int block, size_t smem);   // blocks of this instantiation one SM holds (registers AND shared memory); 0 = unknown
+};
+static const InstOps* select_inst(int env, bool grad, Variant v);
 
 static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs* out, bool want_grad, KParams& prm,
                 mtb_launch_info& info, size_t& workspace_bytes) {
@@ -1061,6 +1089,16 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const int by_threads = 2048 / block;
     if (blocks_per_sm > by_threads) blocks_per_sm = by_threads < 1 ? 1 : by_threads;
     if (blocks_per_sm > 32) blocks_per_sm = 32;
+    // The grid is persistent: exactly one resident wave. Shared memory alone over-estimates the residency of the
+    // register-limited instantiations (80 registers x 256 threads: 3 blocks, not the 7 shared memory would admit), which
+    // left a ragged third wave; ask the runtime for the instantiation that will be launched (cached per geometry).
+    const Variant variant = pick_variant(block, blocks_per_sm);
+    info.variant_maxt = variant.maxt;
+    info.variant_minb = variant.minb;
+    {
+        const int by_regs = select_inst(pb->env_kind, want_grad, variant)->resident_blocks(block, smem);
+        if (by_regs >= 1 && by_regs < blocks_per_sm) blocks_per_sm = by_regs;
+    }
     int grid = lim.sms * blocks_per_sm;
     const int units_per_block = (prm.GP <= 32) ? block / 32 : E;
     const int max_grid = (prm.num_items + units_per_block - 1) / units_per_block;
@@ -1086,38 +1124,73 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
 }
 
 template <int ENV, bool GRAD, int MAXT, int MINB>
-static int launch_evaluate_t(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
+struct Inst {
+    // dynamic shared memory the instantiation has been opted in for (cudaFuncSetAttribute once per growth, not per launch)
+    static int& smem_opt_in() { static int v = 0; return v; }
+    static int ensure_smem(int smem_bytes) {
 #ifndef MTB_HOST_EMUL
-    cudaError_t err = cudaFuncSetAttribute(evaluate_kernel<ENV, GRAD, MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, info.smem_bytes);
-    if (err != cudaSuccess) return (int)err;
+        std::lock_guard<std::mutex> lock(inst_mutex());
+        if (smem_bytes > smem_opt_in()) {
+            const cudaError_t err = cudaFuncSetAttribute(evaluate_kernel<ENV, GRAD, MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+            if (err != cudaSuccess) return (int)err;
+            smem_opt_in() = smem_bytes;
+        }
 #endif
-    MTB_LAUNCH((evaluate_kernel<ENV, GRAD, MAXT, MINB>), info.grid, info.block, (size_t)info.smem_bytes, stream, prm);
+        (void)smem_bytes;
+        return 0;
+    }
+    static int launch(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
+        const int err = ensure_smem(info.smem_bytes);
+        if (err != 0) return err;
+        MTB_LAUNCH((evaluate_kernel<ENV, GRAD, MAXT, MINB>), info.grid, info.block, (size_t)info.smem_bytes, stream, prm);
 #ifndef MTB_HOST_EMUL
-    return (int)cudaGetLastError();
+        return (int)cudaGetLastError();
 #else
-    return 0;
+        return 0;
 #endif
-}
+    }
+    static int resident_blocks(int block, size_t smem) {
+#ifndef MTB_HOST_EMUL
+        static std::map<std::pair<int, size_t>, int> cache;
+        if (ensure_smem((int)smem) != 0) { (void)cudaGetLastError(); return 0; }
+        std::lock_guard<std::mutex> lock(inst_mutex());
+        const auto key = std::make_pair(block, smem);
+        const auto it = cache.find(key);
+        if (it != cache.end()) return it->second;
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, evaluate_kernel<ENV, GRAD, MAXT, MINB>, block, smem) != cudaSuccess) {
+            (void)cudaGetLastError();                           // no device (build container): fall back to the launch bounds
+            return 0;
+        }
+        cache[key] = n;
+        return n;
+#else
+        (void)block; (void)smem;
+        return 0;
+#endif
+    }
+    static const InstOps* ops() {
+        static const InstOps o = {&Inst::launch, &Inst::resident_blocks};
+        return &o;
+    }
+};
 
 template <int ENV, bool GRAD>
-static int launch_evaluate(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
-    if (info.block > kDefaultBlock) return launch_evaluate_t<ENV, GRAD, kMaxThreads, 1>(prm, info, stream);
-    const int force = env_flag("MTB_MINB");
-#ifdef MTB_EXPERIMENT
-    if (ENV == MTB_ENV_SOCIAL_FORCES && info.block <= 64) {
-        if (force == 16) return launch_evaluate_t<ENV, GRAD, 64, 16>(prm, info, stream);
-        if (force == 14) return launch_evaluate_t<ENV, GRAD, 64, 14>(prm, info, stream);
-        return launch_evaluate_t<ENV, GRAD, 64, 12>(prm, info, stream);
-    }
-    if (ENV == MTB_ENV_SOCIAL_FORCES && info.block <= 128) {
-        if (force == 8) return launch_evaluate_t<ENV, GRAD, 128, 8>(prm, info, stream);
-        if (force == 7) return launch_evaluate_t<ENV, GRAD, 128, 7>(prm, info, stream);
-        return launch_evaluate_t<ENV, GRAD, 128, 6>(prm, info, stream);
-    }
+static const InstOps* select_variant(Variant v) {
+    if (v.maxt > kDefaultBlock) return Inst<ENV, GRAD, kMaxThreads, 1>::ops();
+#ifdef MTB_DEV_KNOBS
+    if (v.minb == 4) return Inst<ENV, GRAD, kDefaultBlock, 4>::ops();
 #endif
-    if (force == 4) return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 4>(prm, info, stream);
-    if (force == 3 || (force == 0 && info.blocks_per_sm >= 3)) return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 3>(prm, info, stream);
-    return launch_evaluate_t<ENV, GRAD, kDefaultBlock, 2>(prm, info, stream);
+    if (v.minb == 3) return Inst<ENV, GRAD, kDefaultBlock, 3>::ops();
+    return Inst<ENV, GRAD, kDefaultBlock, 2>::ops();
+}
+
+static const InstOps* select_inst(int env, bool grad, Variant v) {
+    switch (env) {
+        case MTB_ENV_SOCIAL_FORCES: return grad ? select_variant<MTB_ENV_SOCIAL_FORCES, true>(v) : select_variant<MTB_ENV_SOCIAL_FORCES, false>(v);
+        case MTB_ENV_POTENTIAL_FIELD: return grad ? select_variant<MTB_ENV_POTENTIAL_FIELD, true>(v) : select_variant<MTB_ENV_POTENTIAL_FIELD, false>(v);
+        default: return grad ? select_variant<MTB_ENV_KALMAN, true>(v) : select_variant<MTB_ENV_KALMAN, false>(v);
+    }
 }
 
 }  // namespace mtb
@@ -1203,17 +1276,8 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
         }
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    switch (problem->env_kind) {
-        case MTB_ENV_SOCIAL_FORCES:
-            return want_grad ? mtb::launch_evaluate<MTB_ENV_SOCIAL_FORCES, true>(prm, info, st)
-                             : mtb::launch_evaluate<MTB_ENV_SOCIAL_FORCES, false>(prm, info, st);
-        case MTB_ENV_POTENTIAL_FIELD:
-            return want_grad ? mtb::launch_evaluate<MTB_ENV_POTENTIAL_FIELD, true>(prm, info, st)
-                             : mtb::launch_evaluate<MTB_ENV_POTENTIAL_FIELD, false>(prm, info, st);
-        default:
-            return want_grad ? mtb::launch_evaluate<MTB_ENV_KALMAN, true>(prm, info, st)
-                             : mtb::launch_evaluate<MTB_ENV_KALMAN, false>(prm, info, st);
-    }
+    const mtb::Variant variant = {info.variant_maxt, info.variant_minb};
+    return mtb::select_inst(problem->env_kind, want_grad, variant)->launch(prm, info, st);
 }
 
 int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, int32_t num_candidates, float feas_tol,

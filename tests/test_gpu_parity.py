@@ -21,6 +21,14 @@ def eng():
     return engine.Engine(DEV)
 
 
+@pytest.fixture(scope="module")
+def eng_dev():
+    """Engine over the -DMTB_DEV_KNOBS variant of the CUDA library (placement overrides from the environment)."""
+    import ctypes
+    from mantrap_b200 import _cabi, build
+    return engine.Engine.from_library(_cabi.bind(ctypes.CDLL(build.build(dev_knobs=True))), DEV)
+
+
 @pytest.mark.parametrize("name", gio.case_names())
 def test_rollout_golden(eng, name):
     kc.check_rollout(eng.lib, DEV, name)
@@ -291,32 +299,32 @@ def test_rejects_cpu_tensors(eng):
     ("pf", "single", 2, 9, 5, 5, 15, {"goal": 0.5, "pos": 1.0}),
     ("sf", "double", 2, 8, 10, 4, 20, {"goal": 0.5, "prob": 1.0, "acc": 1.0}),
 ])
-def test_means_in_l2_scratch(eng, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor, weights):
+def test_means_in_l2_scratch(eng_dev, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor, weights):
     """Means in the L2-resident scratch (forced by the development knob) against the oracle and the goldens."""
     monkeypatch.setenv("MTB_MEANS_GLOBAL", "1")
-    kc.check_batched_vs_oracle(eng.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)
-    kc.check_modules(eng.lib, DEV, "c4_sf_n20_p3_t12")
-    kc.check_constraints(eng.lib, DEV, "c3_sf_n10_p4_t20")
+    kc.check_batched_vs_oracle(eng_dev.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)
+    kc.check_modules(eng_dev.lib, DEV, "c4_sf_n20_p3_t12")
+    kc.check_constraints(eng_dev.lib, DEV, "c3_sf_n10_p4_t20")
 
 
 @pytest.mark.parametrize("s,c,n,p,t_hor", [(64, 40, 2, 2, 50), (8, 16, 48, 2, 40), (16, 8, 64, 1, 50), (32, 32, 8, 1, 50)])
-def test_means_placement_is_bit_identical(eng, monkeypatch, s, c, n, p, t_hor):
+def test_means_placement_is_bit_identical(eng_dev, monkeypatch, s, c, n, p, t_hor):
     """The long-horizon / many-ado shapes for which the launch plan moves the means to the L2 scratch: both placements run the
     same arithmetic, so every forward output is bit-identical and the gradients agree to the rounding of the L2 float
     reductions (whose arrival order differs between launches)."""
     scene = scenarios.synthetic_scenes(s, n, p, regular_sigma=True).to(DEV)
     controls = scenarios.candidate_controls(s, c, t_hor, u_max=1.0).to(DEV)
-    mus_wo = eng.rollout_wo_ego(scene, t_hor)["mus"].contiguous()
+    mus_wo = eng_dev.rollout_wo_ego(scene, t_hor)["mus"].contiguous()
     spec = engine.ModuleSpec(weights={"goal": 0.5, "acc": 1.0, "prob": 1.0}, mus_wo=mus_wo, control_limits=True, speed_limits=True,
                              min_distance=True, ellipsoid=True)
     want = ("obj", "total", "grad", "cons", "violation", "mus", "sigmas")
     res = {}
     for knob in ("2", "1", "0"):
         monkeypatch.setenv("MTB_MEANS_GLOBAL", knob)
-        out = eng.evaluate(scene, controls, spec, want=want)
+        out = eng_dev.evaluate(scene, controls, spec, want=want)
         torch.cuda.synchronize()
         res[knob] = {k: out[k].clone() for k in want}
-    assert eng.launch_info(scene, controls, True)["blocks_per_sm"] >= 1
+    assert eng_dev.launch_info(scene, controls, True)["blocks_per_sm"] >= 1
     for knob in ("1", "0"):
         for key in ("obj", "total", "cons", "violation", "mus", "sigmas"):
             a, b = res[knob][key], res["2"][key]          # (P = 1: the variance of one particle is NaN in both, Appendix B)
