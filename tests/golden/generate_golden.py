@@ -46,9 +46,15 @@ def random_ados(n, seed, spacing=2.2, speed=1.25, box=8.0):
 
 CASES = {
     # BASELINE config 1: test_solver-style scene extended to three ados, goal + acceleration modules.
+    # Seeds of the two headline fixtures were screened (search_cases.py) so that the reference's interaction gradient is
+    # NON-trivial: min(sigma) > 0.05, raw_acc < 1, |grad_acc|max > 1e-4 (asserted in generate()). The round-1 seeds, which
+    # draw a sigma <= 0 (autograd NaN -> nan_to_num -> zero gradient), stay as the `*_sigma_neg` edge cases.
     "c1_sf_n3_t10": dict(env="sf", ego_kind="double", ego_pos=(-5, 2), ego_vel=(0, 0), ego_goal=(1, 1), dt=0.4,
-                         T=10, P=5, seed=101, seed_wo=101, useed=1, uscale=2.0, modules=("goal", "acc"),
+                         T=10, P=5, seed=107, seed_wo=107, useed=1, uscale=2.0, modules=("goal", "acc"), require=("acc",),
                          ados=_ados([[3, 2, 0, 0, -4, 2], [0, -2, 0, 0, 0, 4], [-1, 4.5, 0, 0, -1, -4]])),
+    "c1_sf_n3_t10_sigma_neg": dict(env="sf", ego_kind="double", ego_pos=(-5, 2), ego_vel=(0, 0), ego_goal=(1, 1), dt=0.4,
+                                   T=10, P=5, seed=101, seed_wo=101, useed=1, uscale=2.0, modules=("goal", "acc"),
+                                   ados=_ados([[3, 2, 0, 0, -4, 2], [0, -2, 0, 0, 0, 4], [-1, 4.5, 0, 0, -1, -4]])),
     # same scene with moving pedestrians and the ego passing close by: all three interaction variants.
     "sf_n3_t10_moving": dict(env="sf", ego_kind="double", ego_pos=(-4, 1), ego_vel=(1.0, 0), ego_goal=(4, 1),
                              dt=0.4, T=10, P=5, seed=202, seed_wo=202, useed=2, uscale=1.0,
@@ -63,7 +69,7 @@ CASES = {
     # BASELINE config 3: ten ados, four particles ("modes"), T = 20, position module + min-distance rows.
     "c3_sf_n10_p4_t20": dict(env="sf", ego_kind="double", ego_pos=(-6, 0), ego_vel=(1.0, 0.2), ego_goal=(6, 1),
                              dt=0.4, T=20, P=4, seed=404, seed_wo=404, useed=4, uscale=0.6,
-                             modules=("goal", "pos", "acc", "min_distance"), ados=random_ados(10, 44)),
+                             modules=("goal", "pos", "acc", "min_distance"), require=("acc",), ados=random_ados(10, 44)),
     # single-integrator ego, six ados.
     "sf_single_n6_t12": dict(env="sf", ego_kind="single", ego_pos=(-5, -1), ego_vel=(0, 0), ego_goal=(5, 2),
                              dt=0.4, T=12, P=5, seed=505, seed_wo=505, useed=5, uscale=1.5,
@@ -80,8 +86,26 @@ CASES = {
                                        [-0.4, 1.1, 0.5, -0.5, 3, -3]])),
     # ETH-shaped (config 4): 20 pedestrians, three particles, T = 12.
     "c4_sf_n20_p3_t12": dict(env="sf", ego_kind="double", ego_pos=(-7, -6), ego_vel=(0.8, 0.6), ego_goal=(7, 6),
-                             dt=0.4, T=12, P=3, seed=808, seed_wo=808, useed=8, uscale=1.0,
+                             dt=0.4, T=12, P=3, seed=800, seed_wo=800, useed=8, uscale=1.0, require=("acc",),
                              modules=("goal", "acc"), ados=random_ados(20, 88, spacing=1.5, box=9.0)),
+    "c4_sf_n20_p3_t12_sigma_neg": dict(env="sf", ego_kind="double", ego_pos=(-7, -6), ego_vel=(0.8, 0.6), ego_goal=(7, 6),
+                                       dt=0.4, T=12, P=3, seed=808, seed_wo=808, useed=8, uscale=1.0,
+                                       modules=("goal", "acc"), ados=random_ados(20, 88, spacing=1.5, box=9.0)),
+    # Probability-objective fixtures: moving pedestrians (the particle weights spread the weighted
+    # velocities, so the variances are ~1e-2 instead of 1e-15), short horizons and an ego a few metres away keep the raw
+    # cost inside the +-120 clamp, i.e. the adjoint through means AND variances is compared with the reference's autograd.
+    "sf_prob_n4_t6": dict(env="sf", ego_kind="double", ego_pos=(-4.5, -3.0), ego_vel=(0.8, 0.4), ego_goal=(5, 3), dt=0.4,
+                          T=6, P=5, seed=1105, seed_wo=1105, useed=11, uscale=1.0, modules=("goal", "acc", "vel"), require=("acc", "prob"),
+                          ados=_ados([[1.5, 2.0, -1.0, -0.3, -6, 0], [-1.0, 3.5, 0.6, -0.9, 2, -5],
+                                      [3.0, -1.5, -0.7, 0.8, -2, 5], [0.0, -4.5, 0.9, 0.5, 6, 1]])),
+    "sf_prob_single_n6_t8": dict(env="sf", ego_kind="single", ego_pos=(-6.0, 0.5), ego_vel=(0, 0), ego_goal=(6, 0), dt=0.4,
+                                 T=8, P=4, seed=1102, seed_wo=1102, useed=12, uscale=1.2, modules=("goal", "acc", "pos"), require=("acc", "prob"),
+                                 ados=_ados([[-1.0, 3.0, 0.9, -0.6, -5, -4], [2.0, 2.5, -0.8, -0.7, 6, -2], [0.5, -3.0, 0.7, 0.9, -5, 2],
+                                             [3.5, -1.0, -1.0, 0.4, 3, 6], [-3.0, -2.5, 1.0, 0.5, -4, 5], [5.0, 3.5, -0.9, -0.8, 6, -3]])),
+    "pf_prob_n4_t6": dict(env="pf", ego_kind="double", ego_pos=(7.0, 6.5), ego_vel=(-0.2, -0.1), ego_goal=(-5, -4), dt=0.4,
+                          T=6, P=5, seed=1305, seed_wo=1305, useed=13, uscale=1.0, modules=("goal", "acc", "vel"), require=("acc", "prob"),
+                          ados=_ados([[-0.5, 0.0, 0.8, 0.7, 0, 0], [0.5, -1.0, 0.6, 0.8, 0, 0], [-1.0, 1.0, 0.9, 0.6, 0, 0],
+                                      [1.0, 0.5, 0.7, 0.7, 0, 0]])),
     "kalman_n5_t15": dict(env="kalman", ego_kind="double", ego_pos=(-3, 0), ego_vel=(0.5, 0), ego_goal=(5, 0),
                           dt=0.4, T=15, P=5, seed=909, seed_wo=909, useed=9, uscale=1.0, modules=("goal", "acc"),
                           ados=random_ados(5, 99)),
@@ -208,8 +232,18 @@ def generate(name, case):
         out["con_min_distance"] = rh.to_np(g).astype(np.float64)
         out["jac_min_distance"] = np.asarray(module.compute_gradient_auto_grad(g, grad_wrt=u), dtype=np.float64)
 
+    # A "main" fixture must pin a NON-trivial reference gradient of the modules it names in `require` (unsaturated cost,
+    # no sampled sigma <= 0): refuse to write one that would compare zeros with zeros.
+    for key in case.get("require", ()):
+        limit = 120.0 if key == "prob" else {"acc": 1.0, "vel": 1.0, "pos": 3.0}[key]
+        gmax = float(np.abs(out[f"grad_{key}"]).max())
+        assert abs(float(out[f"raw_{key}"])) < limit, (name, key, "saturated", float(out[f"raw_{key}"]))
+        assert gmax > 1e-4, (name, key, "reference gradient is (almost) zero", gmax)
+        if case["env"] == "sf":
+            assert float(min(out["sigma"].min(), out["sigma_wo"].min())) > 0.05, (name, "sampled sigma <= 0.05")
     np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **out)
-    print(f"{name}: " + ", ".join(f"{k}={out[k]:.6g}" for k in out if k.startswith(("obj_", "raw_"))))
+    print(f"{name}: " + ", ".join(f"{k}={out[k]:.6g}" for k in out if k.startswith(("obj_", "raw_"))) + " | " +
+          ", ".join(f"|{k}|max={np.abs(out[k]).max():.3g}" for k in out if k.startswith("grad_") and not k.endswith("_sub2")))
 
 
 def generate_agent_kats():

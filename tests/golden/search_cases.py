@@ -33,7 +33,7 @@ def screen(case, seed, seed_wo):
     v0w, sigmaw, ww, noisew = to.draw_params(case["env"], n, p, t_hor - 1)
     ego0 = torch.tensor([[*case["ego_pos"], *case["ego_vel"]]], dtype=torch.float32)
     ego_goal = torch.tensor([case["ego_goal"]], dtype=torch.float32)
-    mus_wo, _ = to.rollout(case["env"], ado0, goal, v0w[None], sigmaw[None], ww[None], noisew[None], None, case["dt"])
+    mus_wo, _ = to.rollout(case["env"], ado0, goal, v0w[None], sigmaw[None], ww[None], noisew[None], t_hor, case["dt"])
     scene = to.Scene(case["env"], case["ego_kind"], case["dt"], ego0, ego_goal, ado0, goal, v0[None], sigma[None], w[None], noise[None])
     out = {"sigma_min": float(min(sigma.min(), sigmaw.min())) if case["env"] == "sf" else 1.0}
     for key in ("acc", "vel", "pos", "prob"):
