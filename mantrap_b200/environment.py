@@ -27,6 +27,44 @@ from .autograd import ParticleRollout
 from .engine import SceneBatch
 
 
+def draw_particle_parameters(ado_ids: typing.List[str], param_defaults: typing.Dict[str, typing.Tuple[float, float]],
+                             num_particles: int, num_noise_steps: int, **param_dicts) -> typing.Dict[str, torch.Tensor]:
+    """(v0, sigma, weight) [1,N,P] and noise [1,T-1,N,P,2] with the reference's RNG consumption (particle.py:40-79,
+    :141, :165). `param_dicts` may override the per-ado (mean, std) like `v0_dict` / `sigma_dict` do."""
+    n = len(ado_ids)
+    names = list(param_defaults.keys())
+    # Normal(loc, scale).sample((P,)) per (ado, parameter) in the reference's order. torch's sampler is
+    # `empty(P).normal_(0, 1).mul_(scale).add_(loc)` (distributions/normal.py:77-82 -> normal_out_impl), so one randn(P)
+    # per (ado, parameter) consumes the generator identically and ONE mul/add and ONE cdf expression (normal.py:104-110)
+    # over all draws give the same bits, without 2 N distribution objects per callback (this draw was the largest host
+    # cost of a solver callback). The draws cannot be merged into one call: >= 16 elements switch torch to a different
+    # (vectorised Box-Muller) sampler.
+    if n > 0:
+        locs, scales = [], []
+        for ado_id in ado_ids:
+            for key in names:
+                override = param_dicts.get(f"{key}_dict")
+                loc, scale = override[ado_id] if override is not None else param_defaults[key]
+                locs.append(float(loc))
+                scales.append(float(scale))
+        loc_t = torch.tensor(locs, dtype=torch.float32).view(n, len(names), 1)
+        scale_t = torch.tensor(scales, dtype=torch.float32).view(n, len(names), 1)
+        unit = torch.stack([torch.randn(num_particles) for _ in range(n * len(names))]).view(n, len(names), num_particles)
+        samples = unit.mul_(scale_t).add_(loc_t)
+        cdfs = 0.5 * (1 + torch.erf((samples - loc_t) * scale_t.reciprocal() / math.sqrt(2)))
+    else:
+        samples = cdfs = torch.zeros((0, len(names), num_particles))
+    weight = torch.prod(cdfs, dim=1)
+    weight = weight / torch.norm(weight, dim=0)               # over the ADO axis (reference quirk, particle.py:141)
+    out = {"v0": samples[None, :, 0].contiguous(), "weight": weight[None].contiguous(),
+           "sigma": (samples[None, :, 1] if len(names) > 1 else torch.ones((1, n, num_particles))).contiguous()}
+    if num_noise_steps > 0:
+        # one torch.rand per step in the reference (particle.py:165); the CPU uniform sampler is serial, so one call of
+        # [T-1, N, P, 2] is the same stream
+        out["noise"] = torch.rand((1, num_noise_steps, n, num_particles, 2))
+    return out
+
+
 class GraphBasedEnvironment:
     env_kind: str = None
 
@@ -285,40 +323,7 @@ class ParticleEnvironment(GraphBasedEnvironment):
     param_defaults: typing.Dict[str, typing.Tuple[float, float]] = {}
 
     def draw_particle_parameters(self, num_particles: int, num_noise_steps: int, **param_dicts):
-        """(v0, sigma, weight) [1,N,P] and noise [1,T-1,N,P,2] with the reference's RNG consumption (particle.py:40-79,
-        :141, :165). `param_dicts` may override the per-ado (mean, std) like `v0_dict` / `sigma_dict` do."""
-        n = self.num_ados
-        names = list(self.param_defaults.keys())
-        # Normal(loc, scale).sample((P,)) per (ado, parameter) in the reference's order. torch's sampler is
-        # `empty(P).normal_(0, 1).mul_(scale).add_(loc)` (distributions/normal.py:77-82 -> normal_out_impl), so one randn(P)
-        # per (ado, parameter) consumes the generator identically and ONE mul/add and ONE cdf expression (normal.py:104-110)
-        # over all draws give the same bits, without 2 N distribution objects per callback (this draw was the largest host
-        # cost of a solver callback). The draws cannot be merged into one call: >= 16 elements switch torch to a different
-        # (vectorised Box-Muller) sampler.
-        if n > 0:
-            locs, scales = [], []
-            for ado_id in self.ado_ids:
-                for key in names:
-                    override = param_dicts.get(f"{key}_dict")
-                    loc, scale = override[ado_id] if override is not None else self.param_defaults[key]
-                    locs.append(float(loc))
-                    scales.append(float(scale))
-            loc_t = torch.tensor(locs, dtype=torch.float32).view(n, len(names), 1)
-            scale_t = torch.tensor(scales, dtype=torch.float32).view(n, len(names), 1)
-            unit = torch.stack([torch.randn(num_particles) for _ in range(n * len(names))]).view(n, len(names), num_particles)
-            samples = unit.mul_(scale_t).add_(loc_t)
-            cdfs = 0.5 * (1 + torch.erf((samples - loc_t) * scale_t.reciprocal() / math.sqrt(2)))
-        else:
-            samples = cdfs = torch.zeros((0, len(names), num_particles))
-        weight = torch.prod(cdfs, dim=1)
-        weight = weight / torch.norm(weight, dim=0)               # over the ADO axis (reference quirk, particle.py:141)
-        out = {"v0": samples[None, :, 0].contiguous(), "weight": weight[None].contiguous(),
-               "sigma": (samples[None, :, 1] if len(names) > 1 else torch.ones((1, n, num_particles))).contiguous()}
-        if num_noise_steps > 0:
-            # one torch.rand per step in the reference (particle.py:165); the CPU uniform sampler is serial, so one call of
-            # [T-1, N, P, 2] is the same stream
-            out["noise"] = torch.rand((1, num_noise_steps, n, num_particles, 2))
-        return out
+        return draw_particle_parameters(self.ado_ids, self.param_defaults, num_particles, num_noise_steps, **param_dicts)
 
     def _compute_distributions(self, ego_trajectory, num_particles: int = constants.ENV_NUM_PARTICLES,
                                vel_dist: bool = True, t_horizon: int = None, **kwargs):
