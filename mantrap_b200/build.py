@@ -16,7 +16,10 @@ DEPS = SOURCES + [os.path.join(HERE, "csrc", "mtb_math.cuh"), os.path.join(HERE,
 # define parity (x != x tests, inf - inf) are unaffected by it.
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
               "--use_fast_math",
-              "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]
+              "-Xcompiler", "-fPIC", "-Xcompiler", "-fno-gnu-unique", "-shared", "-cudart", "static"]
+# -fno-gnu-unique: function-local statics of templates would otherwise get STB_GNU_UNIQUE binding, which the dynamic loader
+# resolves process-wide even for RTLD_LOCAL libraries -- a process that also loads the test-only emulation build of the same
+# sources (tests/host_emul) would then share launch tables between the two libraries.
 
 
 def nvcc() -> str:

@@ -40,6 +40,7 @@ namespace mtb {
 constexpr int kMaxThreads = 1024;
 
 static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+static inline size_t round_up16(size_t x) { return (x + 15) / 16 * 16; }
 
 struct DeviceLimits {
     int sms;

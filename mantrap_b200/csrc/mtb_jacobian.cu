@@ -325,7 +325,8 @@ __global__ void __launch_bounds__(MAXT, MINB) jacobian_kernel(const JParams prm)
                 float sx = 0.f, sy = 0.f;
                 for (int j = 0; j < P; ++j) { sx += qbuf[g + j].x; sy += qbuf[g + j].y; }
                 const float4 c = mus_t[m];
-                const float mx = sx / (float)P, my = sy / (float)P;
+                const float inv_p = 1.0f / (float)P;
+                const float mx = sx * inv_p, my = sy * inv_p;
                 mus[nxt * N + m] = make_float4(fmaf(c.z, dt, c.x), fmaf(c.w, dt, c.y), mx, my);
                 if (prm.rows_ell > 0 && ENV != MTB_ENV_KALMAN) {     // unbiased variance of the weighted velocities (particle.py:175)
                     float vx = 0.f, vy = 0.f;
@@ -334,7 +335,8 @@ __global__ void __launch_bounds__(MAXT, MINB) jacobian_kernel(const JParams prm)
                         vx = fmaf(ex, ex, vx);
                         vy = fmaf(ey, ey, vy);
                     }
-                    varl[nxt * N + m] = make_float2(vx / (float)(P - 1), vy / (float)(P - 1));
+                    const float inv_pm1 = 1.0f / (float)(P - 1);
+                    varl[nxt * N + m] = make_float2(vx * inv_pm1, vy * inv_pm1);
                 }
             }
             for (int idx = g; idx < N * D; idx += nthreads) {

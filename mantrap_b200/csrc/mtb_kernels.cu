@@ -29,6 +29,7 @@ struct KParams {
     mtb_modules md;
     mtb_outputs out;
     int T, N, P, G, GP, E, MW, NW;   // NW = warps per evaluation group (1 for sub-warp groups)
+    int EV;                          // evaluations per thread: 1 = evaluate_kernel, 2 = evaluate_pair_kernel (two candidates of a scene)
     int num_items;
     long long num_evals;
     int has_ego, want_grad, want_env_adjoint, use_tape;
@@ -401,7 +402,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
             if (active && i == 0) {                               // collapse the P particles of ado m (particle.py:171-175)
                 float sx = 0.f, sy = 0.f;
                 for (int j = 0; j < P; ++j) { sx += qbuf[g + j].x; sy += qbuf[g + j].y; }
-                const float mx = sx / (float)P, my = sy / (float)P;
+                const float inv_p = 1.0f / (float)P;
+                const float mx = sx * inv_p, my = sy * inv_p;
                 const float4 cur = mus_t[m];
                 const float npx = fmaf(cur.z, dt, cur.x), npy = fmaf(cur.w, dt, cur.y);
                 mus[(t + 1) * N + m] = make_float4(npx, npy, mx, my);
@@ -416,8 +418,9 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
                             vx = fmaf(ex, ex, vx);
                             vy = fmaf(ey, ey, vy);
                         }
-                        vx /= (float)(P - 1);
-                        vy /= (float)(P - 1);
+                        const float inv_pm1 = 1.0f / (float)(P - 1);
+                        vx *= inv_pm1;
+                        vy *= inv_pm1;
                     }
                     if (sig_out != nullptr) {
                         sig_out[(m * T + t + 1) * 2 + 0] = vx;
@@ -871,6 +874,12 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     }
 }
 
+}  // namespace mtb
+
+#include "mtb_pair_kernel.cuh"
+
+namespace mtb {
+
 // ---------------------------------------------------------------------------------------------------------
 // best feasible candidate per scene (random_search.py:28-35 keeps the best objective with violation < limit)
 // ---------------------------------------------------------------------------------------------------------
@@ -930,8 +939,9 @@ static constexpr int env_flag(const char*) { return 0; }
 struct Variant {
     int maxt, minb;
 };
-static Variant pick_variant(int block, int blocks_by_smem) {
+static Variant pick_variant(int block, int blocks_by_smem, int evals_per_thread) {
     if (block > kDefaultBlock) return {kMaxThreads, 1};
+    if (evals_per_thread == 2) return {kDefaultBlock, 2};     // pair kernel: 128 registers, two blocks of <= 256 threads
     const int force = env_flag("MTB_MINB");
     if (force == 4) return {kDefaultBlock, 4};
     if (force == 3 || (force == 0 && blocks_by_smem >= 3)) return {kDefaultBlock, 3};
@@ -942,7 +952,7 @@ struct InstOps {
     int (*launch)(const KParams&, const mtb_launch_info&, cudaStream_t);
     int (*resident_blocks)(int block, size_t smem);   // blocks of this instantiation one SM holds (registers AND shared memory); 0 = unknown
 };
-static const InstOps* select_inst(int env, bool grad, Variant v);
+static const InstOps* select_inst(int env, bool grad, Variant v, int evals_per_thread);
 
 static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs* out, bool want_grad, KParams& prm,
                 mtb_launch_info& info, size_t& workspace_bytes) {
@@ -959,6 +969,20 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     prm.G = prm.N * prm.P;
     prm.MW = (prm.N + 31) / 32;
     prm.NP4 = round_up(prm.N, 4);
+    // Two candidates per thread (evaluate_pair_kernel, packed FP32) whenever the candidates of a scene pair up: social-forces
+    // environment, ego present, even candidate count. Single evaluations (solver callbacks), odd counts, Kalman and the
+    // potential field run evaluate_kernel (without pair loops the packed arithmetic does not pay for the registers of a second
+    // rollout: measured 3.22 ms vs 2.88 ms on the config-2 shape; development knob MTB_PAIR=2 pairs it anyway for the tests).
+    {
+        const int pair_knob = env_flag("MTB_PAIR");
+        bool pair = (pb->env_kind == MTB_ENV_SOCIAL_FORCES || (pb->env_kind == MTB_ENV_POTENTIAL_FIELD && pair_knob == 2)) &&
+                    pb->ego_kind != MTB_EGO_NONE && (pb->num_candidates % 2) == 0 &&
+                    prm.N * prm.P <= kDefaultBlock;       // (larger groups: one block of up to 1024 threads at 64 registers, no room for two rollouts)
+        const int knob = env_flag("MTB_PAIR");              // development knob: 1 = never pair
+        if (knob == 1) pair = false;
+        prm.EV = pair ? 2 : 1;
+    }
+    int EV = prm.EV;
     prm.keep_var = (md != nullptr && ((md->w_prob != 0.f && md->mus_wo != nullptr) || (md->con_ellipsoid && pb->ego_kind != MTB_EGO_NONE))) ? 1 : 0;
     prm.has_ego = pb->ego_kind != MTB_EGO_NONE;
     prm.want_grad = want_grad ? 1 : 0;
@@ -986,17 +1010,18 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     bool means_in_smem = true;
     auto layout = [&](int E, bool tape_in_smem) -> size_t {
         int off = 0;
-        prm.off_ctl = off;    off += round_up(2 * prm.T, 4);
-        prm.off_ego = off;    off += (prm.T + 1) * 4;
-        prm.off_egobar = off; off += want_grad ? prm.NW * (prm.T + 1) * 4 : 0;
-        prm.off_mus = off;    off += means_in_smem ? prm.T * prm.N * 4 : 0;
-        prm.off_pos = off;    off += 2 * prm.NP4;
-        prm.off_dir = off;    off += (want_grad && means_in_smem) ? round_up((prm.T - 1) * prm.N * 2, 4) : 0;
-        prm.off_var = off;    off += prm.keep_var ? round_up(prm.T * prm.N * 2, 4) : 0;
-        prm.off_q = off;      off += round_up(prm.GP * 2, 4);
-        prm.off_misc = off;   off += kMiscFloats;
-        prm.off_tape = off;   off += (need_tape && tape_in_smem) ? (prm.T - 1) * prm.GP * 4 : 0;
-        prm.off_mask = off;   off += (need_mask && tape_in_smem) ? round_up((prm.T - 1) * prm.GP * prm.MW, 4) : 0;
+        // (per group; a group of the pair kernel holds the arrays of both of its candidates: EV = 2)
+        prm.off_ctl = off;    off += EV * round_up(2 * prm.T, 4);
+        prm.off_ego = off;    off += EV * (prm.T + 1) * 4;
+        prm.off_egobar = off; off += want_grad ? EV * prm.NW * (prm.T + 1) * 4 : 0;
+        prm.off_mus = off;    off += means_in_smem ? EV * prm.T * prm.N * 4 : 0;
+        prm.off_pos = off;    off += EV * 2 * prm.NP4;
+        prm.off_dir = off;    off += (want_grad && means_in_smem) ? round_up(EV * (prm.T - 1) * prm.N * 2, 4) : 0;
+        prm.off_var = off;    off += prm.keep_var ? round_up(EV * prm.T * prm.N * 2, 4) : 0;
+        prm.off_q = off;      off += round_up(EV * prm.GP * 2, 4);
+        prm.off_misc = off;   off += EV * kMiscFloats;
+        prm.off_tape = off;   off += (need_tape && tape_in_smem) ? EV * (prm.T - 1) * prm.GP * 4 : 0;
+        prm.off_mask = off;   off += (need_mask && tape_in_smem) ? round_up(EV * (prm.T - 1) * prm.GP * prm.MW, 4) : 0;
         prm.per_eval_f = off;
         const int block = E * prm.GP;
         prm.red_f = round_up(((block + 31) / 32) * 4, 4);
@@ -1014,7 +1039,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     // (E, tape placement, shared-memory bytes) for the current placement of the means; returns an error code
     auto choose = [&]() -> int {
         E = (prm.GP >= target_block) ? 1 : target_block / prm.GP;
-        const long long total_evals = (long long)pb->num_scenes * pb->num_candidates;
+        const long long total_evals = (long long)pb->num_scenes * pb->num_candidates / EV;     // work items of one group each
         if ((long long)E > total_evals) E = (int)total_evals;
         // the block must be a multiple of a warp: with sub-warp groups keep E a multiple of 32 / GP
         if (prm.GP < 32) E = round_up(E, 32 / prm.GP);
@@ -1031,6 +1056,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
             const int knob = env_flag("MTB_TAPE_GLOBAL");       // development knob: 1 = global, 2 = shared
             if (knob == 1) tape_in_smem = false;
             if (knob == 2) tape_in_smem = true;
+            if (EV == 2) tape_in_smem = false;                  // the pair kernel keeps its tape in the L2 scratch (fixed address spaces)
         }
         smem = layout(E, tape_in_smem);
         while (smem > (size_t)lim.max_smem && E * prm.GP > 32 && E > 1) {
@@ -1062,7 +1088,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         // 252 -> 91 ms, N = 32, P = 1 73 -> 31 ms, N = 8, P = 1 16.0 -> 6.4 ms, N = 2, P = 1 4.8 -> 3.2 ms; shapes that
         // already hold 512 threads gain nothing or lose up to 19 % from the move and keep shared memory.
         const int knob = env_flag("MTB_MEANS_GLOBAL");        // development knob: 1 = global, 2 = shared
-        if (knob == 1 || (knob == 0 && (err2 != 0 || resident_threads() < 512))) {
+        if (EV == 1 && (knob == 1 || (knob == 0 && (err2 != 0 || resident_threads() < 512)))) {
             const int err_smem = err2, res_smem = (err2 == 0) ? resident_threads() : 0;
             const int e_keep = E; const bool t_keep = tape_in_smem; const size_t s_keep = smem;
             means_in_smem = false;
@@ -1071,13 +1097,29 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
                 means_in_smem = true; E = e_keep; tape_in_smem = t_keep; smem = layout(E, tape_in_smem); (void)s_keep; err2 = 0;
             }
         }
+        // the pair kernel keeps the means of both candidates in shared memory: shapes that need the L2 placement run evaluate_kernel
+        if (EV == 2 && (err2 != 0 || knob == 1 || ((size_t)lim.smem_per_sm < 2 * (smem + 1024) && E * prm.GP >= 128))) {
+            EV = prm.EV = 1;
+            means_in_smem = true;
+            err2 = choose();
+            const int knob1 = env_flag("MTB_MEANS_GLOBAL");
+            if (knob1 == 1 || (knob1 == 0 && (err2 != 0 || resident_threads() < 512))) {
+                const int err_smem = err2, res_smem = (err2 == 0) ? resident_threads() : 0;
+                const int e_keep = E; const bool t_keep = tape_in_smem;
+                means_in_smem = false;
+                err2 = choose();
+                if (knob1 != 1 && err_smem == 0 && (err2 != 0 || resident_threads() * 100 < res_smem * 125)) {
+                    means_in_smem = true; E = e_keep; tape_in_smem = t_keep; smem = layout(E, tape_in_smem); err2 = 0;
+                }
+            }
+        }
         if (err2 != 0) return err2;
     }
     prm.E = E;
     prm.tape_in_smem = tape_in_smem ? 1 : 0;
     prm.means_in_smem = means_in_smem ? 1 : 0;
     prm.num_evals = (long long)pb->num_scenes * pb->num_candidates;
-    const int evals_per_unit = (prm.GP <= 32) ? 32 / prm.GP : 1;          // unit = warp of sub-warp groups, or one group
+    const int evals_per_unit = EV * ((prm.GP <= 32) ? 32 / prm.GP : 1);   // unit = warp of sub-warp groups, or one group
     prm.num_items = (int)((prm.num_evals + evals_per_unit - 1) / evals_per_unit);
     prm.use_tape = need_tape ? 1 : 0;
     prm.want_env_adjoint = (need_tape && md != nullptr &&
@@ -1092,25 +1134,25 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     // The grid is persistent: exactly one resident wave. Shared memory alone over-estimates the residency of the
     // register-limited instantiations (80 registers x 256 threads: 3 blocks, not the 7 shared memory would admit), which
     // left a ragged third wave; ask the runtime for the instantiation that will be launched (cached per geometry).
-    const Variant variant = pick_variant(block, blocks_per_sm);
+    const Variant variant = pick_variant(block, blocks_per_sm, EV);
     info.variant_maxt = variant.maxt;
     info.variant_minb = variant.minb;
     {
-        const int by_regs = select_inst(pb->env_kind, want_grad, variant)->resident_blocks(block, smem);
+        const int by_regs = select_inst(pb->env_kind, want_grad, variant, EV)->resident_blocks(block, smem);
         if (by_regs >= 1 && by_regs < blocks_per_sm) blocks_per_sm = by_regs;
     }
     int grid = lim.sms * blocks_per_sm;
     const int units_per_block = (prm.GP <= 32) ? block / 32 : E;
     const int max_grid = (prm.num_items + units_per_block - 1) / units_per_block;
     if (grid > max_grid) grid = max_grid;
-    prm.ws_abar_bytes = abar_l2 ? (size_t)grid * E * prm.T * prm.N * sizeof(float4) : 0;
+    prm.ws_abar_bytes = abar_l2 ? (size_t)grid * E * EV * prm.T * prm.N * sizeof(float4) : 0;
     prm.ws_tape_bytes = prm.ws_mask_bytes = 0;
     if (need_tape && !tape_in_smem) {
-        prm.ws_tape_bytes = (size_t)grid * (prm.T - 1) * block * sizeof(float4);
-        prm.ws_mask_bytes = need_mask ? (size_t)grid * (prm.T - 1) * block * prm.MW * sizeof(unsigned) : 0;
+        prm.ws_tape_bytes = (size_t)grid * (prm.T - 1) * block * EV * sizeof(float4);
+        prm.ws_mask_bytes = need_mask ? round_up16((size_t)grid * (prm.T - 1) * block * prm.MW * EV * sizeof(unsigned)) : 0;
     }
-    prm.ws_mus_bytes = means_in_smem ? 0 : (size_t)grid * E * prm.T * prm.N * sizeof(float4);
-    prm.ws_dir_bytes = (means_in_smem || !want_grad || prm.T < 2) ? 0 : (size_t)grid * E * (prm.T - 1) * prm.N * sizeof(float2);
+    prm.ws_mus_bytes = means_in_smem ? 0 : (size_t)grid * E * EV * prm.T * prm.N * sizeof(float4);
+    prm.ws_dir_bytes = (means_in_smem || !want_grad || prm.T < 2) ? 0 : round_up16((size_t)grid * E * EV * (prm.T - 1) * prm.N * sizeof(float2));
     workspace_bytes = prm.ws_abar_bytes + prm.ws_tape_bytes + prm.ws_mask_bytes + prm.ws_mus_bytes + prm.ws_dir_bytes;
     info.grid = grid;
     info.block = block;
@@ -1120,10 +1162,23 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     info.tape_in_smem = prm.tape_in_smem;
     info.num_items = prm.num_items;
     info.blocks_per_sm = blocks_per_sm;
+    info.kernel_kind = EV == 2 ? 1 : 0;
+    info.evals_per_thread = EV;
     return 0;
 }
 
+template <int ENV, bool GRAD, int MAXT, int MINB, int EVT>
+struct KernelOf;
 template <int ENV, bool GRAD, int MAXT, int MINB>
+struct KernelOf<ENV, GRAD, MAXT, MINB, 1> {
+    static constexpr auto fn = evaluate_kernel<ENV, GRAD, MAXT, MINB>;
+};
+template <int ENV, bool GRAD, int MAXT, int MINB>
+struct KernelOf<ENV, GRAD, MAXT, MINB, 2> {
+    static constexpr auto fn = evaluate_pair_kernel<ENV, GRAD, MAXT, MINB>;
+};
+
+template <int ENV, bool GRAD, int MAXT, int MINB, int EVT = 1>
 struct Inst {
     // dynamic shared memory the instantiation has been opted in for (cudaFuncSetAttribute once per growth, not per launch)
     static int& smem_opt_in() { static int v = 0; return v; }
@@ -1131,7 +1186,7 @@ struct Inst {
 #ifndef MTB_HOST_EMUL
         std::lock_guard<std::mutex> lock(inst_mutex());
         if (smem_bytes > smem_opt_in()) {
-            const cudaError_t err = cudaFuncSetAttribute(evaluate_kernel<ENV, GRAD, MAXT, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+            const cudaError_t err = cudaFuncSetAttribute(KernelOf<ENV, GRAD, MAXT, MINB, EVT>::fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
             if (err != cudaSuccess) return (int)err;
             smem_opt_in() = smem_bytes;
         }
@@ -1142,7 +1197,7 @@ struct Inst {
     static int launch(const KParams& prm, const mtb_launch_info& info, cudaStream_t stream) {
         const int err = ensure_smem(info.smem_bytes);
         if (err != 0) return err;
-        MTB_LAUNCH((evaluate_kernel<ENV, GRAD, MAXT, MINB>), info.grid, info.block, (size_t)info.smem_bytes, stream, prm);
+        MTB_LAUNCH((KernelOf<ENV, GRAD, MAXT, MINB, EVT>::fn), info.grid, info.block, (size_t)info.smem_bytes, stream, prm);
 #ifndef MTB_HOST_EMUL
         return (int)cudaGetLastError();
 #else
@@ -1158,7 +1213,7 @@ struct Inst {
         const auto it = cache.find(key);
         if (it != cache.end()) return it->second;
         int n = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, evaluate_kernel<ENV, GRAD, MAXT, MINB>, block, smem) != cudaSuccess) {
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, KernelOf<ENV, GRAD, MAXT, MINB, EVT>::fn, block, smem) != cudaSuccess) {
             (void)cudaGetLastError();                           // no device (build container): fall back to the launch bounds
             return 0;
         }
@@ -1185,7 +1240,17 @@ static const InstOps* select_variant(Variant v) {
     return Inst<ENV, GRAD, kDefaultBlock, 2>::ops();
 }
 
-static const InstOps* select_inst(int env, bool grad, Variant v) {
+template <int ENV, bool GRAD>
+static const InstOps* select_pair_variant(Variant v) {
+    if (v.maxt > kDefaultBlock) return Inst<ENV, GRAD, kMaxThreads, 1, 2>::ops();
+    return Inst<ENV, GRAD, kDefaultBlock, 2, 2>::ops();
+}
+
+static const InstOps* select_inst(int env, bool grad, Variant v, int evals_per_thread) {
+    if (evals_per_thread == 2) {
+        if (env == MTB_ENV_SOCIAL_FORCES) return grad ? select_pair_variant<MTB_ENV_SOCIAL_FORCES, true>(v) : select_pair_variant<MTB_ENV_SOCIAL_FORCES, false>(v);
+        return grad ? select_pair_variant<MTB_ENV_POTENTIAL_FIELD, true>(v) : select_pair_variant<MTB_ENV_POTENTIAL_FIELD, false>(v);
+    }
     switch (env) {
         case MTB_ENV_SOCIAL_FORCES: return grad ? select_variant<MTB_ENV_SOCIAL_FORCES, true>(v) : select_variant<MTB_ENV_SOCIAL_FORCES, false>(v);
         case MTB_ENV_POTENTIAL_FIELD: return grad ? select_variant<MTB_ENV_POTENTIAL_FIELD, true>(v) : select_variant<MTB_ENV_POTENTIAL_FIELD, false>(v);
@@ -1277,7 +1342,7 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const mtb::Variant variant = {info.variant_maxt, info.variant_minb};
-    return mtb::select_inst(problem->env_kind, want_grad, variant)->launch(prm, info, st);
+    return mtb::select_inst(problem->env_kind, want_grad, variant, prm.EV)->launch(prm, info, st);
 }
 
 int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, int32_t num_candidates, float feas_tol,

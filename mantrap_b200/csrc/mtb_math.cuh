@@ -37,7 +37,19 @@ MTB_DEV V2 operator-(V2 a, V2 b) { return v2(a.x - b.x, a.y - b.y); }
 MTB_DEV V2 operator*(float s, V2 a) { return v2(s * a.x, s * a.y); }
 MTB_DEV void axpy(V2& y, float a, V2 x) { y.x = fmaf(a, x.x, y.x); y.y = fmaf(a, x.y, y.y); }
 #endif
-MTB_DEV float dot(V2 a, V2 b) { return a.x * b.x + a.y * b.y; }
+// Explicitly rounded scalar operations: the scalar step models below spell out the SAME operation sequence as their
+// two-candidate versions in mtb_math2.cuh (packed FMUL2 / FFMA2 are never contracted or re-associated), so that
+// evaluate_kernel, jacobian_kernel and evaluate_pair_kernel produce bit-identical forward rollouts.
+#ifndef MTB_HOST_EMUL
+MTB_DEV float fm(float a, float b) { return __fmul_rn(a, b); }
+MTB_DEV float fa(float a, float b) { return __fadd_rn(a, b); }
+MTB_DEV float ff(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+#else
+MTB_DEV float fm(float a, float b) { return a * b; }
+MTB_DEV float fa(float a, float b) { return a + b; }
+MTB_DEV float ff(float a, float b, float c) { return fmaf(a, b, c); }
+#endif
+MTB_DEV float dot(V2 a, V2 b) { return ff(a.x, b.x, fm(a.y, b.y)); }
 MTB_DEV bool is_nan(float x) { return x != x; }
 MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py:446)
     if (is_nan(x)) return 0.f;
@@ -55,35 +67,35 @@ struct RepulsionFwd {
     bool pass_x;   // clamp passes the gradient for this component (closed interval, :122)
     bool pass_y;
     // intermediates kept for the adjoint
-    V2 s, t1, t2;
-    float inv_n1, inv_n2, a, sb, inv_sb, pot, k, inv_sigma;
+    V2 t1, t2;
+    float inv_n1, inv_n2, a, inv_sb, pot, k, inv_sigma;
 };
 
+// Four MUFU operations per pair term: rsqrt |r|^2, rsqrt |s|^2, rsqrt B (norms as x * rsqrt(x)) and one ex2.
 MTB_DEV RepulsionFwd repulsion_forward(V2 r, V2 w, float v0, float sigma, float dt, float f_max) {
     RepulsionFwd o;
-    o.s = v2(fmaf(-dt, w.x, r.x), fmaf(-dt, w.y, r.y));
-    const float n1 = sqrtf(dot(r, r));
-    const float n2 = sqrtf(dot(o.s, o.s));
-    const float n3sq = dot(w, w);
-    o.inv_n1 = 1.0f / n1;
-    o.inv_n2 = 1.0f / n2;
-    o.a = n1 + n2;
-    const float big_b = fmaf(o.a, o.a, -(dt * dt) * n3sq);
-    o.sb = sqrtf(big_b);                       // b = sb / 2
-    o.inv_sb = 1.0f / o.sb;
     o.inv_sigma = 1.0f / sigma;
-    o.pot = v0 * expf(-0.5f * o.sb * o.inv_sigma);
-    // k = dV/dn1 = dV/dn2 = -(V/sigma) * (n1+n2) / (4 b)
-    o.k = -(o.pot * o.inv_sigma) * (o.a * 0.5f * o.inv_sb);
-    o.t1 = o.inv_n1 * r;
-    o.t2 = o.inv_n2 * o.s;
+    const V2 s = v2(ff(-dt, w.x, r.x), ff(-dt, w.y, r.y));
+    const float n1sq = dot(r, r), n2sq = dot(s, s), n3sq = dot(w, w);
+    o.inv_n1 = rsqrtf(n1sq);                   // |r| = 0: rsqrt = inf, n1 = 0 * inf = NaN -> NaN force -> dead, like 0/0 in t1 = r / |r|
+    o.inv_n2 = rsqrtf(n2sq);
+    const float n1 = fm(n1sq, o.inv_n1), n2 = fm(n2sq, o.inv_n2);
+    o.a = fa(n1, n2);
+    const float big_b = ff(o.a, o.a, fm(-(dt * dt), n3sq));
+    o.inv_sb = rsqrtf(big_b);                  // b = sb / 2 with sb = sqrt(B) = B * rsqrt(B)
+    const float sb = fm(big_b, o.inv_sb);
+    o.pot = fm(v0, exp2f(fm(-0.5f * 1.4426950408889634f * o.inv_sigma, sb)));   // V = v0 exp(-sb / (2 sigma))
+    // k = dV/dn1 = dV/dn2 = -(V / sigma) * (n1 + n2) / (4 b)
+    o.k = fm(-fm(o.inv_sigma, o.pot), fm(fm(0.5f, o.a), o.inv_sb));
+    o.t1 = v2(fm(o.inv_n1, r.x), fm(o.inv_n1, r.y));
+    o.t2 = v2(fm(o.inv_n2, s.x), fm(o.inv_n2, s.y));
     // Two separate products, as autograd accumulates them: with V = inf (sampled sigma <= 0) opposite-signed
     // terms give inf - inf = NaN, which the reference turns into a zero force.
-    const float fx = o.k * o.t1.x + o.k * o.t2.x;
-    const float fy = o.k * o.t1.y + o.k * o.t2.y;
+    const float fx = ff(o.k, o.t1.x, fm(o.k, o.t2.x));
+    const float fy = ff(o.k, o.t1.y, fm(o.k, o.t2.y));
     o.dead = is_nan(fx) || is_nan(fy);
-    o.pass_x = (fx >= -f_max) && (fx <= f_max);
-    o.pass_y = (fy >= -f_max) && (fy <= f_max);
+    o.pass_x = fabsf(fx) <= f_max;
+    o.pass_y = fabsf(fy) <= f_max;
     o.force = o.dead ? v2(0.f, 0.f) : v2(fminf(fmaxf(fx, -f_max), f_max), fminf(fmaxf(fy, -f_max), f_max));
     return o;
 }
@@ -93,34 +105,37 @@ MTB_DEV void repulsion_adjoint(const RepulsionFwd& o, V2 r, V2 w, float dt, V2 f
     rbar = v2(0.f, 0.f);
     wbar = v2(0.f, 0.f);
     if (o.dead) return;
+    (void)r;
     fbar.x = o.pass_x ? fbar.x : 0.f;
     fbar.y = o.pass_y ? fbar.y : 0.f;
     // F = k t1 + k t2
     const float kbar = dot(fbar, o.t1 + o.t2);
     const V2 tbar = o.k * fbar;                                   // adjoint of t1 and of t2
     // t1 = r / n1, t2 = s / n2
-    float n1bar = -dot(tbar, o.t1) * o.inv_n1;
-    float n2bar = -dot(tbar, o.t2) * o.inv_n2;
+    float n1bar = fm(-dot(tbar, o.t1), o.inv_n1);
+    float n2bar = fm(-dot(tbar, o.t2), o.inv_n2);
     V2 sbar = o.inv_n2 * tbar;
-    rbar = o.inv_n1 * tbar;
+    V2 rb = o.inv_n1 * tbar;
     // k = V * a * q with q = -1 / (2 sigma sb)
-    const float q = -0.5f * o.inv_sigma * o.inv_sb;
-    const float potbar = kbar * o.a * q;
-    float abar = kbar * o.pot * q;
-    float sbbar = -kbar * o.k * o.inv_sb;
+    const float q = fm(-0.5f * o.inv_sigma, o.inv_sb);
+    const float potbar = fm(fm(kbar, o.a), q);
+    float abar = fm(fm(kbar, o.pot), q);
+    float sbbar = fm(-fm(kbar, o.k), o.inv_sb);
     // V = v0 exp(-sb / (2 sigma))
-    sbbar = fmaf(potbar * o.pot, -0.5f * o.inv_sigma, sbbar);
+    sbbar = ff(fm(potbar, o.pot), -0.5f * o.inv_sigma, sbbar);
     // sb = sqrt(B), B = a^2 - dt^2 |w|^2
-    const float bbar = 0.5f * sbbar * o.inv_sb;
-    abar = fmaf(2.0f * o.a, bbar, abar);
-    const float n3sqbar = -(dt * dt) * bbar;
-    n1bar += abar;
-    n2bar += abar;
-    axpy(rbar, n1bar, o.t1);                                     // n1 = |r|
+    const float bbar = fm(fm(0.5f, sbbar), o.inv_sb);
+    abar = ff(fm(2.0f, o.a), bbar, abar);
+    const float n3sqbar = fm(-(dt * dt), bbar);
+    n1bar = fa(n1bar, abar);
+    n2bar = fa(n2bar, abar);
+    axpy(rb, n1bar, o.t1);                                       // n1 = |r|
     axpy(sbar, n2bar, o.t2);                                     // n2 = |s|
-    wbar = (2.0f * n3sqbar) * w;                                 // |w|^2
-    rbar = rbar + sbar;                                          // s = r - dt w
-    axpy(wbar, -dt, sbar);
+    V2 wb = fm(2.0f, n3sqbar) * w;                               // |w|^2
+    rb = rb + sbar;                                              // s = r - dt w
+    axpy(wb, -dt, sbar);
+    rbar = rb;
+    wbar = wb;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -131,8 +146,8 @@ MTB_DEV V2 goal_force(V2 p, V2 v, V2 goal, float inv_tau, float goal_radius) {
     const float nd = sqrtf(dot(d, d));
     if (nd < goal_radius) return v2(0.f, 0.f);
     const float sp = sqrtf(dot(v, v));
-    const float inv_nd = 1.0f / nd;
-    return v2((d.x * inv_nd * sp - v.x) * inv_tau, (d.y * inv_nd * sp - v.y) * inv_tau);
+    const float c = fm(1.0f / nd, sp);
+    return v2(fm(inv_tau, ff(d.x, c, -v.x)), fm(inv_tau, ff(d.y, c, -v.y)));
 }
 
 MTB_DEV void goal_force_adjoint(V2 p, V2 v, V2 goal, float inv_tau, float goal_radius, V2 fbar, V2& pbar, V2& vbar) {
@@ -143,12 +158,13 @@ MTB_DEV void goal_force_adjoint(V2 p, V2 v, V2 goal, float inv_tau, float goal_r
     const float sp = sqrtf(dot(v, v));
     const V2 dir = inv_nd * d;
     const V2 h = inv_tau * fbar;
-    vbar = vbar - h;
     const float spbar = dot(h, dir);
     const V2 dirbar = sp * h;
-    const V2 dbar = inv_nd * (dirbar - dot(dirbar, dir) * dir);
+    const float dd = dot(dirbar, dir);
+    const V2 dbar = inv_nd * v2(ff(-dd, dir.x, dirbar.x), ff(-dd, dir.y, dirbar.y));
     pbar = pbar - dbar;
-    if (sp > 0.f) axpy(vbar, spbar / sp, v);
+    vbar = vbar - h;
+    if (sp > 0.f) axpy(vbar, fm(spbar, 1.0f / sp), v);
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -158,7 +174,8 @@ MTB_DEV V2 feasible(V2 u, float u_max) {
     const float nu = sqrtf(dot(u, u));
     const float d = fmaxf(nu, 1e-6f);
     const float cl = fminf(nu, u_max);
-    return v2(u.x / d * cl, u.y / d * cl);
+    const float inv_d = 1.0f / d;
+    return v2(fm(fm(u.x, inv_d), cl), fm(fm(u.y, inv_d), cl));
 }
 
 MTB_DEV V2 feasible_adjoint(V2 u, float u_max, V2 upbar) {
@@ -166,12 +183,12 @@ MTB_DEV V2 feasible_adjoint(V2 u, float u_max, V2 upbar) {
     const float d = fmaxf(nu, 1e-6f);
     const float cl = fminf(nu, u_max);
     const float inv_d = 1.0f / d;
-    V2 ubar = (cl * inv_d) * upbar;
+    V2 ubar = fm(cl, inv_d) * upbar;
     const float du = dot(upbar, u);
     float nubar = 0.f;
-    if (nu >= 1e-6f) nubar -= du * cl * inv_d * inv_d;           // d = |u| branch of clamp(min=1e-6)
-    if (nu <= u_max) nubar += du * inv_d;                        // cl = |u| branch of clamp(-u_max, u_max)
-    if (nu > 0.f) axpy(ubar, nubar / nu, u);
+    if (nu >= 1e-6f) nubar = -fm(fm(fm(du, cl), inv_d), inv_d);  // d = |u| branch of clamp(min=1e-6)
+    if (nu <= u_max) nubar = fa(nubar, fm(du, inv_d));           // cl = |u| branch of clamp(-u_max, u_max)
+    if (nu > 0.f) axpy(ubar, fm(nubar, 1.0f / nu), u);
     return ubar;
 }
 

@@ -13,7 +13,7 @@ DEPS = SOURCES + [os.path.join(ROOT, "mantrap_b200", "csrc", "mtb_math.cuh"), os
 def build(force: bool = False) -> str:
     if not force and os.path.exists(OUT) and all(os.path.getmtime(OUT) >= os.path.getmtime(d) for d in DEPS):
         return OUT
-    cmd = ["g++", "-std=c++20", "-O2", "-g", "-DMTB_HOST_EMUL", "-DMTB_DEV_KNOBS", "-fPIC", "-shared", "-pthread", "-ffp-contract=off",
+    cmd = ["g++", "-std=c++20", "-O2", "-g", "-DMTB_HOST_EMUL", "-DMTB_DEV_KNOBS", "-fPIC", "-shared", "-pthread", "-ffp-contract=off", "-fno-gnu-unique",
            "-I", HERE, "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "mantrap_b200", "csrc"), "-o", OUT]
     for src in SOURCES:
         cmd += ["-x", "c++", src]

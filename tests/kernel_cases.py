@@ -52,7 +52,9 @@ def prob_floor(g, mask):
     m = None if mask is None else mask.cpu().bool()
     r32 = to.evaluate(osc, controls, mus_wo, {"prob": 1.0}, ado_mask=m)
     r64 = to.evaluate(to.scene_to(osc, torch.float64), controls.double(), mus_wo.double(), {"prob": 1.0}, ado_mask=m)
-    return float((r32["total"].double() - r64["total"]).abs().max()), float((r32["grad"].double() - r64["grad"]).abs().max())
+    # |f32 - f64| is ONE realisation of the rounding noise (norms rounded once, as in torch); the kernels evaluate norms as
+    # x * rsqrt(x) (three roundings, MUFU-friendly), so their realisation is drawn from a distribution about twice as wide
+    return 2 * float((r32["total"].double() - r64["total"]).abs().max()), 2 * float((r32["grad"].double() - r64["grad"]).abs().max())
 
 
 def check_rollout(lib, device, name):
@@ -347,6 +349,66 @@ def check_batched_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_can
         to.violation(ref_cons[:, n_ctl + n_spd:], to.MIN_L2_DISTANCE, None)
     gio.assert_parity(np_(res["violation"]).reshape(b), vio, 1e-4, "violation", atol=1e-5)
     return res, ref, stats
+
+
+def check_pair_vs_single(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, weights, seed=0, noise=True,
+                         mask=False, constraints=True, given_traj=False):
+    """The two-candidates-per-thread kernel (even candidate count) against the one-evaluation-per-group kernel (the same
+    candidates evaluated one at a time, C = 1). Both spell out the same operation sequence (mtb_math.cuh / mtb_math2.cuh),
+    so the forward rollout (ego trajectory, means, variances) is BIT-IDENTICAL; objectives and gradients differ only by the
+    order of their reductions (shuffle trees, L2 float reductions)."""
+    from mantrap_b200 import scenarios
+    assert num_candidates % 2 == 0
+    scene = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=500 + seed, param_seed=600 + seed,
+                                       regular_sigma=True)
+    if noise:
+        gen = torch.Generator().manual_seed(700 + seed)
+        scene.noise = torch.rand((num_scenes, t_hor - 1, n, p, 2), generator=gen)
+    scene = scene.to(device)
+    controls = scenarios.candidate_controls(num_scenes, num_candidates, t_hor, seed=800 + seed, u_max=1.5).to(device).contiguous()
+    mus_wo = engine.launch_evaluate(lib, scene.without_ego(), None, None, want=("mus",), t_horizon=t_hor)["mus"][:, 0].contiguous()
+    ado_mask = None
+    if mask:
+        ado_mask = (torch.arange(n)[None].expand(num_scenes, n) % 2 == 0).to(torch.uint8).to(device).contiguous()
+    spec = engine.ModuleSpec(weights=weights, mus_wo=mus_wo, ado_mask=ado_mask, control_limits=constraints, speed_limits=constraints,
+                             min_distance=constraints, ellipsoid=constraints)
+    want = ["obj", "obj_raw", "total", "grad", "grad_traj", "mus", "sigmas", "violation", "ego_traj"] + (["cons"] if constraints else [])
+    ego_traj = None
+    if given_traj:
+        ego_traj = engine.launch_evaluate(lib, scene, controls, None, want=("ego_traj",))["ego_traj"].contiguous()
+    info = engine.query_launch(lib, scene, controls, True)
+    assert info["kernel_kind"] == 1 and info["evals_per_thread"] == 2, info
+    stats = torch.zeros(4, dtype=torch.int64, device=device)
+    pair = engine.launch_evaluate(lib, scene, None if given_traj else controls, spec, want=want, stats=stats, ego_traj=ego_traj)
+    stats1 = torch.zeros(4, dtype=torch.int64, device=device)
+    singles = []
+    for c in range(num_candidates):
+        ctl_c = controls[:, c:c + 1].contiguous()
+        assert engine.query_launch(lib, scene, ctl_c, True)["kernel_kind"] == 0
+        traj_c = None if ego_traj is None else ego_traj[:, c:c + 1].contiguous()
+        singles.append(engine.launch_evaluate(lib, scene, None if given_traj else ctl_c, spec, want=want, stats=stats1, ego_traj=traj_c))
+    if device != "cpu":
+        torch.cuda.synchronize()
+    assert stats[2].item() == stats1[2].item(), (stats.tolist(), stats1.tolist())    # saturated evaluations (the pair counters include padding lanes)
+    # The probability objective divides mean differences by particle VARIANCES (1e-4 .. 1e-2): it amplifies the last-bit
+    # differences of the two rollouts by 1e2 .. 1e3 (kernel_cases.prob_floor), everything else is compared tightly.
+    loose = 100.0 if "prob" in weights else 1.0
+    for key in want:
+        a = np.nan_to_num(np_(pair[key]))
+        b = np.nan_to_num(np_(torch.cat([r[key] for r in singles], dim=1)))
+        assert np.array_equal(np.isnan(np_(pair[key])), np.isnan(np_(torch.cat([r[key] for r in singles], dim=1)))), key
+        if key in ("mus", "sigmas", "ego_traj"):
+            assert np.array_equal(a, b), (key, float(np.abs(a - b).max()))
+            continue
+        if key in ("obj", "obj_raw"):
+            gio.assert_parity(a[..., :4], b[..., :4], 2e-6, f"pair vs single: {key}[goal, acc, vel, pos]", atol=2e-7)
+            gio.assert_parity(a[..., 4], b[..., 4], 2e-6 * loose, f"pair vs single: {key}[prob]", atol=2e-7)
+            continue
+        rtol = 2e-5 if key in ("grad", "grad_traj") else 2e-6
+        if key in ("grad", "grad_traj", "total"):
+            rtol *= loose
+        gio.assert_parity(a, b, rtol, f"pair vs single: {key}", atol=2e-7)
+    return pair
 
 
 def check_ellipsoid_golden(lib, device, name):

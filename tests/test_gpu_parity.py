@@ -288,6 +288,39 @@ def test_full_size_properties(eng):
     gio.assert_parity(got_grad[unsat], ref["grad"].numpy()[unsat], gio.RTOL_GRAD, "sampled grad", atol=gio.ATOL + 2 * f_grad)
 
 
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor,weights,kw", [
+    ("sf", "double", 5, 38, 4, 3, 10, {"goal": 0.5, "acc": 1.0}, {}),
+    ("sf", "double", 3, 16, 20, 3, 12, {"goal": 0.5, "acc": 1.0}, {}),                       # config-4 shape
+    ("sf", "double", 2, 6, 10, 4, 20, {"goal": 0.5, "acc": 1.0, "vel": 1.0, "pos": 1.0, "prob": 1.0}, {"mask": True}),
+    ("sf", "single", 2, 4, 12, 3, 8, {"goal": 0.5, "acc": 1.0, "prob": 1.0}, {"given_traj": True}),
+    ("pf", "double", 4, 12, 5, 5, 15, {"goal": 0.5, "acc": 1.0, "prob": 1.0}, {}),
+    ("sf", "double", 2, 4, 40, 2, 6, {"goal": 0.5, "acc": 1.0}, {"constraints": False}),      # N > 32: two mask words
+    ("sf", "double", 4, 6, 1, 2, 5, {"goal": 0.5, "acc": 1.0, "vel": 1.0}, {"noise": False}),  # groups of 2 lanes
+    ("sf", "double", 2, 4, 3, 5, 40, {"goal": 0.5, "acc": 1.0}, {}),                           # horizon > group: serial fold
+    ("sf", "double", 2, 2, 3, 2, 1, {"goal": 0.5}, {}),                                        # T = 1
+    ("sf", "double", 1, 4, 64, 4, 8, {"goal": 0.5, "acc": 1.0}, {"constraints": False}),      # 256-thread groups
+])
+def test_pair_kernel_vs_single_kernel(eng, eng_dev, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor, weights, kw):
+    """Two candidates per thread (packed FP32) against one evaluation per group, candidate by candidate. The production
+    library pairs social-forces batches only; the potential-field instantiation is reached through the development knob."""
+    monkeypatch.setenv("MTB_PAIR", "2")
+    kc.check_pair_vs_single((eng_dev if env_kind == "pf" else eng).lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights, **kw)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor,weights", [
+    ("sf", "double", 5, 38, 4, 3, 10, {"goal": 0.5, "acc": 1.0}),
+    ("sf", "single", 3, 18, 12, 3, 8, {"goal": 0.5, "vel": 1.0, "pos": 1.0}),
+    ("pf", "double", 4, 64, 5, 5, 15, {"goal": 0.5, "acc": 1.0, "vel": 1.0}),
+    ("sf", "double", 2, 8, 20, 3, 12, {"goal": 0.5, "acc": 1.0}),
+    ("sf", "double", 2, 4, 40, 2, 6, {"goal": 0.5, "acc": 1.0}),
+    ("sf", "double", 2, 10, 5, 4, 8, {"goal": 0.5, "prob": 1.0, "acc": 1.0}),
+])
+def test_batched_vs_oracle_pair_kernel(eng, eng_dev, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor, weights):
+    """Even candidate counts (the two-candidates-per-thread kernel) against the CPU oracle."""
+    monkeypatch.setenv("MTB_PAIR", "2")
+    kc.check_batched_vs_oracle((eng_dev if env_kind == "pf" else eng).lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)
+
+
 def test_rejects_cpu_tensors(eng):
     scene = scenarios.synthetic_scenes(1, 3, 2)
     with pytest.raises(RuntimeError):

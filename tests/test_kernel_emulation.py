@@ -55,6 +55,34 @@ def test_batched_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor, weig
     kc.check_batched_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights)
 
 
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor,weights", [
+    ("sf", "double", 3, 4, 4, 3, 6, {"goal": 0.5, "acc": 1.0}),            # sub-warp groups (16 lanes), two groups per warp
+    ("sf", "single", 2, 2, 12, 3, 5, {"goal": 0.5, "vel": 1.0, "pos": 1.0}),  # two warps per group
+    ("pf", "double", 2, 4, 5, 5, 7, {"goal": 0.5, "acc": 1.0, "vel": 1.0}),
+    ("sf", "double", 2, 2, 2, 2, 9, {"goal": 0.5, "acc": 1.0}),            # groups of 4 lanes, horizon > group: serial fold
+    ("sf", "double", 1, 6, 5, 4, 6, {"goal": 0.5, "prob": 1.0, "acc": 1.0}),  # probability objective (variance adjoint)
+    ("pf", "single", 1, 2, 3, 2, 4, {"goal": 0.5, "prob": 1.0}),
+])
+def test_batched_vs_oracle_pair_kernel(emul_lib, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor, weights):
+    """Even candidate counts run the two-candidates-per-thread kernel (potential field: only with the development knob)."""
+    monkeypatch.setenv("MTB_PAIR", "2")
+    kc.check_batched_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor,weights,kw", [
+    ("sf", "double", 2, 4, 4, 3, 6, {"goal": 0.5, "acc": 1.0}, {}),
+    ("sf", "double", 1, 2, 6, 3, 5, {"goal": 0.5, "acc": 1.0, "vel": 1.0, "pos": 1.0, "prob": 1.0}, {"mask": True}),
+    ("sf", "single", 1, 2, 12, 3, 4, {"goal": 0.5, "acc": 1.0, "prob": 1.0}, {"given_traj": True}),
+    ("pf", "double", 2, 2, 5, 4, 6, {"goal": 0.5, "acc": 1.0, "prob": 1.0}, {}),
+    ("sf", "double", 1, 2, 34, 2, 3, {"goal": 0.5, "acc": 1.0}, {"constraints": False}),      # N > 32: two mask words
+    ("sf", "double", 3, 2, 1, 2, 5, {"goal": 0.5, "acc": 1.0, "vel": 1.0}, {"noise": False}),  # one ado: groups of 2 lanes
+    ("sf", "double", 1, 2, 3, 2, 1, {"goal": 0.5}, {}),                                        # T = 1
+])
+def test_pair_kernel_vs_single_kernel(emul_lib, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor, weights, kw):
+    monkeypatch.setenv("MTB_PAIR", "2")
+    kc.check_pair_vs_single(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights, **kw)
+
+
 @pytest.mark.parametrize("name", gio.case_names())
 def test_jacobian_golden(emul_lib, name):
     kc.check_jacobian_golden(emul_lib, "cpu", name)
