@@ -354,9 +354,10 @@ def check_batched_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_can
 def check_pair_vs_single(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, weights, seed=0, noise=True,
                          mask=False, constraints=True, given_traj=False):
     """The two-candidates-per-thread kernel (even candidate count) against the one-evaluation-per-group kernel (the same
-    candidates evaluated one at a time, C = 1). Both spell out the same operation sequence (mtb_math.cuh / mtb_math2.cuh),
-    so the forward rollout (ego trajectory, means, variances) is BIT-IDENTICAL; objectives and gradients differ only by the
-    order of their reductions (shuffle trees, L2 float reductions)."""
+    candidates evaluated one at a time, C = 1). Both spell out the same operation sequence (mtb_math.cuh / mtb_math2.cuh): on
+    the host emulation (IEEE operations, no contraction) the forward rollout is BIT-IDENTICAL; under nvcc --use_fast_math the
+    compiler contracts / rewrites the packed and the scalar expression trees differently (FMUL2 + FADD2 -> FFMA2, rcp(sqrt) ->
+    rsqrt), so on the GPU the rollouts agree to a few ulp and objectives / gradients far inside the parity tolerances."""
     from mantrap_b200 import scenarios
     assert num_candidates % 2 == 0
     scene = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=500 + seed, param_seed=600 + seed,
@@ -393,21 +394,40 @@ def check_pair_vs_single(lib, device, env_kind, ego_kind, num_scenes, num_candid
     # The probability objective divides mean differences by particle VARIANCES (1e-4 .. 1e-2): it amplifies the last-bit
     # differences of the two rollouts by 1e2 .. 1e3 (kernel_cases.prob_floor), everything else is compared tightly.
     loose = 100.0 if "prob" in weights else 1.0
+    # On the GPU the two kernels' rollouts differ by a few ulp per step (see above), which dense scenes amplify like any other
+    # float32 re-ordering: add the measured float32-vs-float64 conditioning of the oracle on the same batch (as every oracle test does).
+    f_obj = f_grad = f_mus = 0.0
+    if device != "cpu":
+        osc = oracle_scene(scene.to("cpu"), num_candidates)
+        wo_rep = mus_wo.detach().cpu().repeat_interleave(num_candidates, dim=0)
+        m_rep = None if ado_mask is None else ado_mask.cpu().bool().repeat_interleave(num_candidates, dim=0)
+        from oracle import torch_oracle as to
+        ctl_flat = controls.cpu().reshape(-1, t_hor, 2)
+        r32 = to.evaluate(osc, ctl_flat, wo_rep, weights, ado_mask=m_rep)
+        r64 = to.evaluate(to.scene_to(osc, torch.float64), ctl_flat.double(), wo_rep.double(), weights, ado_mask=m_rep)
+        f_obj = 2 * float((r32["obj"].double() - r64["obj"]).abs().max())
+        f_grad = 2 * float((r32["grad"].double() - r64["grad"]).abs().max())
+        f_mus = 2 * float((r32["mus"].double() - r64["mus"]).abs().max())
     for key in want:
         a = np.nan_to_num(np_(pair[key]))
         b = np.nan_to_num(np_(torch.cat([r[key] for r in singles], dim=1)))
         assert np.array_equal(np.isnan(np_(pair[key])), np.isnan(np_(torch.cat([r[key] for r in singles], dim=1)))), key
-        if key in ("mus", "sigmas", "ego_traj"):
+        if key in ("mus", "sigmas", "ego_traj") and device == "cpu":
             assert np.array_equal(a, b), (key, float(np.abs(a - b).max()))
             continue
         if key in ("obj", "obj_raw"):
-            gio.assert_parity(a[..., :4], b[..., :4], 2e-6, f"pair vs single: {key}[goal, acc, vel, pos]", atol=2e-7)
-            gio.assert_parity(a[..., 4], b[..., 4], 2e-6 * loose, f"pair vs single: {key}[prob]", atol=2e-7)
+            scale = 120.0 if key == "obj_raw" else 1.0
+            gio.assert_parity(a[..., :4], b[..., :4], 2e-6, f"pair vs single: {key}[goal, acc, vel, pos]", atol=2e-7 + f_obj)
+            gio.assert_parity(a[..., 4], b[..., 4], 2e-6 * loose, f"pair vs single: {key}[prob]", atol=2e-7 + scale * f_obj)
             continue
         rtol = 2e-5 if key in ("grad", "grad_traj") else 2e-6
         if key in ("grad", "grad_traj", "total"):
             rtol *= loose
-        gio.assert_parity(a, b, rtol, f"pair vs single: {key}", atol=2e-7)
+        if key == "cons" and device != "cpu":
+            rtol = gio.RTOL_ROLLOUT          # ellipsoid rows are (distance / 0.1)^2 ~ 1e4: a few ulp of the means are 3e-6 of the largest row
+        floor = {"grad": f_grad, "grad_traj": 10 * f_grad, "total": f_obj, "mus": f_mus, "sigmas": f_mus, "cons": 10 * f_mus,
+                 "violation": 100 * f_mus}.get(key, 0.0)
+        gio.assert_parity(a, b, rtol, f"pair vs single: {key}", atol=2e-7 + floor)
     return pair
 
 

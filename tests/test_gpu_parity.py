@@ -197,7 +197,9 @@ def test_jacobian_full_size_properties(eng):
     controls = controls.to(DEV)
     spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True, ellipsoid=True)
     jac, values = eng.constraint_jacobian(scene, controls, spec, want_values=True)
-    cons = eng.evaluate(scene, controls, spec, want=("cons",))["cons"]
+    # one candidate per scene: evaluate_kernel, whose forward sweep is the Jacobian kernel's (same scalar step models, bit for bit;
+    # the two-candidate kernel agrees to a few ulp per step, which these dense 20-step scenes amplify: tested separately)
+    cons = eng.evaluate(scene, controls[:, :1].contiguous(), spec, want=("cons",))["cons"]
     torch.cuda.synchronize()
     n_ctl, n_spd, n_md = 2 * t_hor, 2 * (t_hor + 1), n * t_hor
     assert jac.shape == (s, c, n_ctl + n_spd + 2 * n_md, 2 * t_hor) and torch.isfinite(jac).all()
@@ -352,6 +354,7 @@ def test_means_placement_is_bit_identical(eng_dev, monkeypatch, s, c, n, p, t_ho
                              min_distance=True, ellipsoid=True)
     want = ("obj", "total", "grad", "cons", "violation", "mus", "sigmas")
     res = {}
+    monkeypatch.setenv("MTB_PAIR", "1")        # evaluate_kernel for every placement (the pair kernel keeps its means in shared memory)
     for knob in ("2", "1", "0"):
         monkeypatch.setenv("MTB_MEANS_GLOBAL", knob)
         out = eng_dev.evaluate(scene, controls, spec, want=want)
