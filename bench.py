@@ -24,7 +24,7 @@ sys.path.insert(0, ROOT)
 
 N_ADOS, N_PARTICLES, T_HORIZON, N_CANDIDATES = 20, 3, 12, 256
 WEIGHTS = {"goal": 0.5, "acc": 1.0}
-METRIC = "rollout+gradient evals/sec (scenes x candidates)"
+METRIC = "rollout+Jacobian evals/sec (scenes x candidates)"        # BASELINE.json's metric name
 UNIT = "evals/s"
 
 
@@ -88,6 +88,44 @@ def cpu_arm(seconds_target=12.0, batch=32, workers=None):
     return evals / timed, workers, sample
 
 
+# BASELINE config 5 (sweep): a 12-shape subset (t_planning, ados, particles) timed on every bench run, GPU and CPU port
+C5_SUBSET = [(10, 2, 2), (10, 8, 4), (10, 32, 2), (20, 4, 8), (20, 16, 4), (20, 64, 2), (30, 8, 8), (30, 32, 4), (40, 16, 2),
+             (50, 2, 8), (50, 8, 4), (50, 64, 2)]
+
+
+def _cpu_shape_worker(args):
+    """CPU oracle (one core) on one sweep shape: evaluations per second of rollout + objectives + autograd gradient."""
+    t_hor, n, p, budget = args
+    import torch
+    torch.set_num_threads(1)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oracle import torch_oracle as to
+    from mantrap_b200 import scenarios
+    import kernel_cases as kc
+    batch = 8
+    scene = scenarios.synthetic_scenes(batch, n, p, seed=11, param_seed=12, regular_sigma=True)
+    controls = scenarios.candidate_controls(batch, 1, t_hor, seed=13)[:, 0]
+    osc = kc.oracle_scene(scene, 1)
+    mus_wo, _ = to.rollout("sf", osc.ado0, osc.goal, osc.v0, osc.sigma, osc.weights, None, t_hor, scene.dt)
+    to.evaluate(osc, controls, mus_wo, WEIGHTS)
+    done, t0 = 0, time.perf_counter()
+    while True:
+        to.evaluate(osc, controls, mus_wo, WEIGHTS)
+        done += batch
+        elapsed = time.perf_counter() - t0
+        if elapsed >= budget:
+            return done / elapsed
+
+
+def cpu_c5_subset(budget=2.0):
+    """{shape: evals/s on ONE core} of the CPU oracle for the sweep subset (one process per shape, in parallel)."""
+    import multiprocessing as mp
+    ctx = mp.get_context("fork")
+    with ctx.Pool(min(len(C5_SUBSET), os.cpu_count() or 1)) as pool:
+        rates = pool.map(_cpu_shape_worker, [(t, n, p, budget) for t, n, p in C5_SUBSET])
+    return dict(zip(C5_SUBSET, rates))
+
+
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -105,7 +143,7 @@ def reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": (time.perf_counter() - t0) * 1e3 / max(1, args.steps),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, 1),
+        "config": workload_config(args, max(1, args.gpus)),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference algorithm = oracle/torch_oracle.py (the Python reference cannot travel to the GPU box; "
@@ -118,7 +156,9 @@ def reference_arm(args):
 def workload_config(args, world):
     return {"workload": f"BASELINE config 4 (ETH-shaped): SocialForces N={N_ADOS} ados x P={N_PARTICLES} particles, "
                         f"t_planning={T_HORIZON}, dt=0.4, double-integrator ego, goal+interaction-acceleration objective, "
-                        f"{args.scenes_per_gpu} scenes/GPU x {args.candidates} candidates",
+                        f"{args.scenes_per_gpu} scenes/GPU x {args.candidates} candidates; one eval = forward rollout + objectives + "
+                        "control-limit / speed-limit rows + gradient w.r.t. the 2T controls (config 4 has no Jacobian rows: its "
+                        "constraints have constant Jacobians; the Jacobian kernel is timed on config 3 under `secondary`)",
             "scenes_per_gpu": args.scenes_per_gpu, "candidates": args.candidates, "global_evals_per_step":
                 args.scenes_per_gpu * args.candidates * world, "parallelism": f"scene-sharded x{world}",
             "cache": "inputs+outputs per step (controls 96 B + gradient 96 B + 12 B per eval) exceed the 126 MB L2; "
@@ -205,32 +245,146 @@ def measure_peaks(eng, torch):
     return res
 
 
-def secondary_measurements(eng, torch, dev):
-    """Outside the timed region, N = 1 only: the two other kernels of the path on their BASELINE shapes, device-timed.
-    (a) config 3: dense constraint Jacobian (control | speed | min-distance rows) of SocialForces N=10 P=4 T=20;
-    (b) batched closed-loop MPC on the bench workload (attention -> baseline -> 256 candidates -> argmin -> step)."""
-    from mantrap_b200 import engine, mpc, scenarios
-    out = {}
-    scene = scenarios.synthetic_scenes(1024, 10, 4).to(dev)
-    controls = scenarios.candidate_controls(1024, 16, 20).to(dev)
-    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True)
-    for _ in range(2):
-        jac = eng.constraint_jacobian(scene, controls, spec)
+def _timed(torch, dev, fn, iters=5, warm=2):
+    for _ in range(warm):
+        fn()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(dev)
     a.record()
-    for _ in range(5):
-        eng.constraint_jacobian(scene, controls, spec)
+    for _ in range(iters):
+        fn()
     b.record()
     torch.cuda.synchronize(dev)
-    ms = a.elapsed_time(b) / 5
+    return a.elapsed_time(b) / iters
+
+
+def _eval_rate(eng, torch, dev, env_kind, s, c, n, p, t_hor, weights, seed=0, iters=3):
+    """Device-timed gradient evaluations per second of one shape: (evals/s, ms per launch, saturated fraction, executed pair terms / eval)."""
+    from mantrap_b200 import engine, scenarios
+    scene = scenarios.synthetic_scenes(s, n, p, env_kind=env_kind, seed=1234 + seed, param_seed=5678 + seed).to(dev)
+    controls = scenarios.candidate_controls(s, c, t_hor, seed=4321 + seed).to(dev)
+    mus_wo = eng.rollout_wo_ego(scene, t_hor)["mus"].contiguous()
+    spec = engine.ModuleSpec(weights=weights, mus_wo=mus_wo)
+    stats = torch.zeros(4, dtype=torch.int64, device=dev)
+    out = eng.evaluate(scene, controls, spec, want=("total", "grad"), stats=stats)
+    torch.cuda.synchronize(dev)
+    st = stats.tolist()
+    ms = _timed(torch, dev, lambda: eng.evaluate(scene, controls, spec, want=("total", "grad"), out=out), iters=iters, warm=1)
+    return s * c / ms * 1e3, ms, st[2] / (s * c), (st[0] + st[1]) / (s * c)
+
+
+def config1_measurements(torch):
+    """BASELINE config 1 through the drop-in solver API (one process, one GPU): the four IPOPT callbacks, one IPOPT iteration
+    (all four at one z), end-to-end solves with scipy's SLSQP over the same callbacks (labelled NOT IPOPT) and, where the
+    third-party `cyipopt` is importable at run time, real IPOPT solves."""
+    import numpy as np
+    import mantrap_b200 as mantrap
+    env = mantrap.environment.SocialForcesEnvironment(ego_position=torch.tensor([-5.0, 2.0]), ego_velocity=torch.zeros(2),
+                                                      ego_type=mantrap.agents.DoubleIntegratorDTAgent, dt=0.4)
+    for pos, goal in (((3.0, 2.0), (-4.0, 2.0)), ((0.0, -2.0), (0.0, 4.0)), ((-1.0, 4.5), (-1.0, -4.0))):
+        env.add_ado(position=torch.tensor(pos), velocity=torch.zeros(2), goal=torch.tensor(goal))
+    goal = torch.tensor([1.0, 1.0])
+    modules = [mantrap.modules.GoalNormModule, mantrap.modules.InteractionAccelerationModule, mantrap.modules.ControlLimitModule,
+               mantrap.modules.MinDistanceModule]
+    solver = mantrap.solver.IPOPTSolver(env, goal=goal, t_planning=10, modules=modules)
+    rng = np.random.RandomState(0)
+    zs = [rng.uniform(-1, 1, 20) for _ in range(120)]
+    out = {"workload": "SocialForces, double-integrator ego + 3 pedestrians x 5 particles, t_planning = 10, goal + interaction-"
+                       "acceleration objective, control-limit + min-distance rows; wall clock of the Python call incl. the particle "
+                       "draw, host<->device copies and the launch; a fresh z per call (no per-z cache hit)"}
+    for name, fn in (("objective", solver.objective), ("gradient", solver.gradient), ("constraints", solver.constraints),
+                     ("jacobian", solver.jacobian)):
+        for z in zs[:20]:
+            fn(z)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for z in zs[20:]:
+            solver._cache.clear()
+            fn(z)
+        torch.cuda.synchronize()
+        out[f"{name}_calls_per_s"] = 100.0 / (time.perf_counter() - t0)
+    solver._cache.clear()
+    t0 = time.perf_counter()
+    for z in zs[20:]:
+        solver.objective(z), solver.gradient(z), solver.constraints(z), solver.jacobian(z)
+    torch.cuda.synchronize()
+    out["ipopt_iterations_per_s"] = 100.0 / (time.perf_counter() - t0)
+    out["ipopt_iteration_note"] = "objective + gradient + constraints + jacobian at one z = two launches (per-z cache)"
+    slsqp = mantrap.solver.SLSQPSolver(env, goal=goal, t_planning=10, modules=modules)
+    z0 = slsqp.warm_start()
+    slsqp.optimize(z0, tag="bench", max_iter=30)
+    n_solves = 10
+    t0 = time.perf_counter()
+    for k in range(n_solves):
+        slsqp._cache.clear()                          # no per-z cache hits across solves: every callback evaluates
+        slsqp.optimize(z0 + 0.05 * torch.as_tensor(rng.uniform(-1, 1, tuple(z0.shape)), dtype=z0.dtype), tag="bench", max_iter=30)
+    out["slsqp_solves_per_s"] = n_solves / (time.perf_counter() - t0)
+    out["slsqp_note"] = ("NOT IPOPT: scipy.optimize SLSQP (ftol 1e-4, <= 30 iterations; ~5 iterations from the hard warm start) over "
+                         "the same four callbacks and bounds, per-z cache cleared between solves")
+    try:
+        try:
+            import ipopt  # noqa: F401
+        except ImportError:
+            import cyipopt  # noqa: F401
+        ips = mantrap.solver.IPOPTSolver(env, goal=goal, t_planning=10, modules=modules)
+        ips.optimize(z0, tag="bench")
+        t0 = time.perf_counter()
+        for _ in range(3):
+            ips._cache.clear()
+            ips.optimize(z0, tag="bench")
+        out["ipopt_solves_per_s"] = 3.0 / (time.perf_counter() - t0)
+    except ImportError:
+        out["ipopt_solves_per_s"] = None
+        out["ipopt_note"] = "cyipopt (third-party, un-vendored by the reference) is not installed on this box: IPOPT solves/s unavailable"
+    return out
+
+
+def secondary_measurements(eng, torch, dev, cpu_c5=None):
+    """Outside the timed region, N = 1: the other BASELINE configs and kernels of the path, device-timed (config 1: wall clock).
+    Every gradient figure carries its `saturated_fraction` (a saturated clamp_max objective seeds no adjoint)."""
+    from mantrap_b200 import engine, mpc, scenarios
+    out = {}
+    out["config1"] = config1_measurements(torch)
+    # config 2: ONE potential-field scene x 4096 candidates (the sampling-baseline path), gradient of goal + interaction acceleration
+    rate, ms, sat, _ = _eval_rate(eng, torch, dev, "pf", 1, 4096, 5, 5, 15, WEIGHTS, iters=10)
+    out["config2"] = {"value": rate, "unit": "evals/s", "ms_per_launch": ms, "saturated_fraction": sat,
+                      "workload": "PotentialField N=5 P=5 T=15, 1 scene x 4096 candidates (latency of one batched gradient evaluation)"}
+    rate, ms, sat, _ = _eval_rate(eng, torch, dev, "pf", 64, 4096, 5, 5, 15, WEIGHTS)
+    out["config2_throughput"] = {"value": rate, "unit": "evals/s", "ms_per_launch": ms, "saturated_fraction": sat,
+                                 "workload": "PotentialField N=5 P=5 T=15, 64 scenes x 4096 candidates"}
+    # config 3: gradient with the (unsaturated) acceleration objective and with the position objective (saturates by reference quirk
+    # A.5-4: the zero-adjoint fast path), next to the dense constraint Jacobian
+    for key, weights in (("config3_gradient_acc", {"goal": 0.5, "acc": 1.0}), ("config3_gradient_pos", {"goal": 0.5, "pos": 1.0})):
+        rate, ms, sat, _ = _eval_rate(eng, torch, dev, "sf", 1024, 16, 10, 4, 20, weights)
+        out[key] = {"value": rate, "unit": "evals/s", "ms_per_launch": ms, "saturated_fraction": sat,
+                    "workload": f"SocialForces N=10 P=4 T=20, 1024 scenes x 16 candidates, objective {sorted(weights)}"}
+    scene = scenarios.synthetic_scenes(1024, 10, 4).to(dev)
+    controls = scenarios.candidate_controls(1024, 16, 20).to(dev)
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True)
+    jac = eng.constraint_jacobian(scene, controls, spec)
+    ms = _timed(torch, dev, lambda: eng.constraint_jacobian(scene, controls, spec))
     out["jacobian_config3"] = {"value": 1024 * 16 / ms * 1e3, "unit": "Jacobians/s", "rows": int(jac.shape[2]), "cols": int(jac.shape[3]),
                                "ms_per_launch": ms, "workload": "SocialForces N=10 P=4 T=20, 1024 scenes x 16 candidates, "
                                "control + speed + min-distance rows (forward-mode tangent kernel)"}
+    # config 5: sweep subset, 2^18 evaluations per shape
+    rows = []
+    for t_hor, n, p in C5_SUBSET:
+        c = 16
+        s_c5 = (1 << 18) // c
+        rate, ms, sat, pairs = _eval_rate(eng, torch, dev, "sf", s_c5, c, n, p, t_hor, WEIGHTS, iters=2)
+        steps_pp = (t_hor - 1) * n * p
+        tflops = rate * (150.0 * pairs + 150.0 * steps_pp + 5.0 * steps_pp * n) / 1e12
+        row = {"t_planning": t_hor, "ados": n, "particles": p, "evals_per_s": rate, "ms_per_launch": ms, "saturated_fraction": sat,
+               "executed_tflops": tflops}
+        if cpu_c5 is not None:
+            row["cpu_port_evals_per_s_per_core"] = cpu_c5[(t_hor, n, p)]
+        rows.append(row)
+    out["config5_subset"] = {"evals_per_shape": 1 << 18, "objective": "goal + interaction acceleration (gradient)", "shapes": rows}
     s = 2048
     loop = mpc.BatchedClosedLoop(eng, scenarios.synthetic_scenes(s, N_ADOS, N_PARTICLES, seed=41, param_seed=42), t_planning=T_HORIZON,
                                  num_candidates=N_CANDIDATES, attention="euclidean", seed=5)
     loop.solve(1)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(dev)
     a.record()
     loop.solve(3)
@@ -243,6 +397,40 @@ def secondary_measurements(eng, torch, dev):
     return out
 
 
+def secondary_multi_gpu(eng, torch, dist, dev, rank, world):
+    """N > 1: (config 2) ONE potential-field scene x 4096 candidates partitioned over the ranks + the order-preserving-key reduction
+    of the winner; (config 5) the sweep subset with 2^18 evaluations PER RANK (weak scaling). Device-timed, max over ranks."""
+    from mantrap_b200 import engine, parallel, scenarios
+    out = {}
+    scene = scenarios.synthetic_scenes(1, 5, 5, env_kind="pf", seed=77, param_seed=78).to(dev)       # the same scene on every rank
+    controls_all = scenarios.candidate_controls(1, 4096, 15, seed=79)
+    lo, hi = parallel.shard_range(4096, rank, world)
+    controls = controls_all[:, lo:hi].to(dev).contiguous()
+    mus_wo = eng.rollout_wo_ego(scene, 15)["mus"].contiguous()
+    spec = engine.ModuleSpec(weights=WEIGHTS, mus_wo=mus_wo, control_limits=True, speed_limits=True)
+    bufs = eng.evaluate(scene, controls, spec, want=("total", "grad", "violation"))
+
+    def search():
+        eng.evaluate(scene, controls, spec, want=("total", "grad", "violation"), out=bufs)
+        idx, val, best = eng.argmin(bufs["total"], bufs["violation"], controls)
+        return parallel.reduce_best_candidate_partitioned(val, idx, best, lo)
+
+    ms = torch.tensor([_timed(torch, dev, search, iters=20, warm=3)], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    out["config2_candidate_partitioned"] = {"ms_per_search": float(ms.item()), "value": 4096 / float(ms.item()) * 1e3, "unit": "evals/s",
+                                            "workload": f"PotentialField N=5 P=5 T=15, 1 scene x 4096 candidates split over {world} ranks, "
+                                                        "gradient evaluation + argmin + 64-bit-key reduction of the winner"}
+    rows = []
+    for t_hor, n, p in C5_SUBSET:
+        rate, ms1, sat, _ = _eval_rate(eng, torch, dev, "sf", (1 << 18) // 16, 16, n, p, t_hor, WEIGHTS, seed=rank, iters=2)
+        t_ms = torch.tensor([ms1], dtype=torch.float64, device=dev)
+        dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+        rows.append({"t_planning": t_hor, "ados": n, "particles": p, "evals_per_s": world * (1 << 18) / float(t_ms.item()) * 1e3,
+                     "ms_per_launch": float(t_ms.item())})
+    out["config5_subset"] = {"evals_per_shape_per_rank": 1 << 18, "shapes": rows}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -252,6 +440,7 @@ def main():
     ap.add_argument("--scenes-per-gpu", type=int, default=8192)
     ap.add_argument("--candidates", type=int, default=N_CANDIDATES)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the measurements of the other BASELINE configs")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -268,10 +457,11 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
     # CPU baseline first (fork-based pool, before CUDA is initialised in this process); rank 0 at N = 1 only.
-    cpu_baseline = None
+    cpu_baseline, cpu_c5 = None, None
     if world == 1 and not args.no_cpu_baseline:
         v, cores, sample = cpu_arm(seconds_target=12.0)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        cpu_c5 = cpu_c5_subset()
 
     import torch
     import torch.distributed as dist
@@ -373,6 +563,7 @@ def main():
         dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
     e2e_value = evals_per_step / (float(e_ms.item()) / args.steps * 1e-3)
 
+    multi = secondary_multi_gpu(eng, torch, dist, dev, rank, world) if (world > 1 and not args.no_secondary) else None
     if rank == 0:
         peaks = measure_peaks(eng, torch)
         sm_clock = None
@@ -398,7 +589,7 @@ def main():
         hbm_achieved = evals_per_launch * bytes_per_eval(t_hor, 3) / (kernel_ms * 1e-3) / 1e9
         traffic, traffic_src = None, None
         try:        # DRAM bytes per evaluation from the committed ncu --set full capture of this kernel, scaled to this launch
-            prof = json.load(open(os.path.join(ROOT, "profiles", "evaluate_kernel_ncu.json")))
+            prof = json.load(open(os.path.join(ROOT, "profiles", "evaluate_pair_kernel_ncu.json")))
             traffic = prof["dram_bytes_per_eval"] * evals_per_launch
             traffic_src = prof["source"]
         except Exception:
@@ -415,7 +606,7 @@ def main():
                          "frac": achieved / fp32_peak, "traffic": traffic, "traffic_source": traffic_src,
                          "note": "compute-bound path (FP32 CUDA cores + MUFU; no contraction, HBM ~1e-3 of peak): the bound is "
                                  "the FP32 pipe, not hbm/tensor",
-                         "kernel": "mtb::evaluate_kernel<SF, GRAD>", "kernel_ms": kernel_ms,
+                         "kernel": "mtb::evaluate_pair_kernel<SF, GRAD> (two candidates per thread, packed FP32)", "kernel_ms": kernel_ms,
                          "kernel_share_of_step": kernel_ms / ms_per_step,
                          "work_model": "executed work: 150 FLOP x executed pair terms + 150 FLOP x particle-steps + 5 FLOP x "
                                        "radius tests (DESIGN.md §6)",
@@ -432,8 +623,10 @@ def main():
             "saturated_fraction": pair_stats[2] / evals_per_launch,
             "launch": eng.launch_info(scene, controls, True),
         }
-        if world == 1:
-            line["secondary"] = secondary_measurements(eng, torch, dev)
+        if world == 1 and not args.no_secondary:
+            line["secondary"] = secondary_measurements(eng, torch, dev, cpu_c5)
+        if multi is not None:
+            line["secondary"] = multi
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
         print(json.dumps(line), flush=True)

@@ -33,12 +33,14 @@ def _world(group=None) -> typing.Tuple[int, int]:
 
 
 def pack_best(best_val: torch.Tensor, best_idx: torch.Tensor, best_controls: torch.Tensor) -> torch.Tensor:
-    """[S] value, [S] int32 index, [S,T,2] controls -> [S, 2 + 2T] float32 rows (index stored exactly: < 2^24)."""
-    return torch.cat((best_val[:, None], best_idx.to(torch.float32)[:, None], best_controls.reshape(best_controls.shape[0], -1)), dim=1)
+    """[S] value, [S] int32 index, [S,T,2] controls -> [S, 2 + 2T] float32 rows. The index column carries the int32 BITS
+    (a bit-cast view, exact for every index; a float conversion would round global candidate indices >= 2^24)."""
+    idx_bits = best_idx.to(torch.int32).contiguous().view(torch.float32)
+    return torch.cat((best_val[:, None], idx_bits[:, None], best_controls.reshape(best_controls.shape[0], -1)), dim=1)
 
 
 def unpack_best(packed: torch.Tensor, t_horizon: int):
-    return packed[:, 0].contiguous(), packed[:, 1].to(torch.int32), packed[:, 2:].reshape(-1, t_horizon, 2).contiguous()
+    return packed[:, 0].contiguous(), packed[:, 1].contiguous().view(torch.int32), packed[:, 2:].reshape(-1, t_horizon, 2).contiguous()
 
 
 def gather_best_scene_partitioned(best_val: torch.Tensor, best_idx: torch.Tensor, best_controls: torch.Tensor,
@@ -151,6 +153,7 @@ def sharded_closed_loop(engine, scene, time_steps: int, candidates: typing.Seque
         return out
     # one flat float32 row per scene: ego trajectory | ado trajectories | controls | objective | index | steps
     n_loc = hi - lo
+    assert int(out.best_index.max()) < 2 ** 24 and time_steps < 2 ** 24, "float32 transport rows hold integers exactly below 2^24"
     rows = torch.cat([out.ego_trajectory.reshape(n_loc, -1), out.ado_trajectories.reshape(n_loc, -1), out.controls.reshape(n_loc, -1),
                       out.objective, out.best_index.to(torch.float32), out.steps.to(torch.float32)[:, None]], dim=1)
     sizes = [shard_range(s_total, r, world) for r in range(world)]
