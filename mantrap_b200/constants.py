@@ -46,5 +46,9 @@ TAG_OPTIMIZATION = "optimization"                # :16
 TAG_WARM_START = "warm_start"                    # :17
 WARM_START_HARD = "hard"                         # :72
 WARM_START_ENCODING = "encoding"                 # :72
+WARM_START_SOFT = "soft"                         # :73 (needs HJReachabilityModule: not on this path)
+WARM_START_POTENTIAL = "potential"               # :74
 WARM_START_ZEROS = "zeros"                       # :76
+WARM_START_PRE_COMPUTATION_NUM = 100             # :77
+WARM_START_PRE_COMPUTATION_HORIZON = 10          # :78
 WARM_START_PRE_COMPUTATION_FILE = ("encoding.pt", "solution.pt")   # :79 (third_party/warm_start/ of the reference)

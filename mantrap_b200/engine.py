@@ -308,7 +308,7 @@ class Engine:
         self.lib = _lib.load()
         self.device = torch.device(device)
         self.launches = 0
-        self._workspace = None
+        self._workspace = {}                              # kernel scratch per CUDA stream
 
     @classmethod
     def from_library(cls, lib: ctypes.CDLL, device: typing.Union[str, torch.device]) -> "Engine":
@@ -316,7 +316,7 @@ class Engine:
         the host emulation of the kernel source (tests/host_emul) to exercise the host classes without a GPU; nothing
         in the package calls it."""
         self = cls.__new__(cls)
-        self.lib, self.device, self.launches, self._workspace = lib, torch.device(device), 0, None
+        self.lib, self.device, self.launches, self._workspace = lib, torch.device(device), 0, {}
         return self
 
     def _check(self, *tensors):
@@ -378,19 +378,30 @@ class Engine:
 
     def evaluate(self, scene: SceneBatch, controls: typing.Optional[torch.Tensor], spec: ModuleSpec = None,
                  want: typing.Sequence[str] = ("obj", "total", "grad"), out=None, stats=None, ego_traj=None):
+        """One fused launch on the CURRENT CUDA stream. The kernel's scratch (adjoint rows, tape, masks) is kept per stream: two
+        streams that evaluate on one engine (e.g. `api.HostPipeline.s_run` next to the caller's default stream) never share it,
+        and a buffer that has to grow is replaced only for its own stream, whose launches are ordered."""
         self._check(scene.ado0, controls, ego_traj)
+        stream = self._stream()
         with self._guard():
-            res = launch_evaluate(self.lib, scene, controls, spec, want, stream=self._stream(), out=out, stats=stats,
-                                  workspace=self._workspace, ego_traj=ego_traj)
-        self._workspace = res.pop("_workspace", self._workspace)
+            res = launch_evaluate(self.lib, scene, controls, spec, want, stream=stream, out=out, stats=stats,
+                                  workspace=self._workspace.get(stream), ego_traj=ego_traj)
+        ws = res.pop("_workspace", None)
+        if ws is not None:
+            self._workspace[stream] = ws
         self.launches += 1
         return res
 
     def rollout_wo_ego(self, scene: SceneBatch, t_horizon: int, want=("mus", "sigmas")):
         """Ego-free prediction (`compute_distributions_wo_ego`): mus [S,N,T,4], sigmas [S,N,T,2]."""
         self._check(scene.ado0)
+        stream = self._stream()
         with self._guard():
-            res = launch_evaluate(self.lib, scene.without_ego(), None, None, want, t_horizon=t_horizon, stream=self._stream())
+            res = launch_evaluate(self.lib, scene.without_ego(), None, None, want, t_horizon=t_horizon, stream=stream,
+                                  workspace=self._workspace.get(stream))
+        ws = res.pop("_workspace", None)
+        if ws is not None:
+            self._workspace[stream] = ws
         self.launches += 1
         return {k: v[:, 0] for k, v in res.items() if not k.startswith("_")}
 

@@ -304,11 +304,15 @@ class GoalNormModule(PureObjectiveModule):
         super().__init__(env=env, t_horizon=t_horizon, weight=weight)
         self._goal = torch.as_tensor(goal).detach().float().cpu()
         assert self._goal.shape == (2,)
-        if optimize_speed:
-            raise NotImplementedError("GoalNormModule(optimize_speed=True): the speed term (goal_norm.py:63-65) is not part "
-                                      "of the fused kernel; the reference's analytic gradient ignores it as well")
+        # The reference's speed term `speeds.dot(torch.exp(-goal_distances * 0.5))` (goal_norm.py:63-65) multiplies a [T+1] with a
+        # [T+1, 2] tensor: torch.dot raises "1D tensors expected" on the first objective call (probe-verified on the unmodified
+        # reference), and its analytic gradient ignores the term (:99-105). Same behaviour here: constructible, raises when evaluated.
+        self._optimize_speed = bool(optimize_speed)
 
     def _spec(self, ado_ids) -> ModuleSpec:
+        if self._optimize_speed:
+            raise RuntimeError("GoalNormModule(optimize_speed=True): 1D tensors expected, but got 1D and 2D tensors "
+                               "(the reference's speed term, goal_norm.py:63-65, fails in torch.dot in exactly this way)")
         return ModuleSpec(weights={"goal": self.weight})
 
     def normalize(self, x):

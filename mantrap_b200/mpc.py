@@ -7,7 +7,7 @@ reached. Here S independent scenes advance together and stay on the device betwe
     per step k:  attention mask            mtb_attention           (attention/euclidean.py, closest.py; optional)
                  ego-free baseline         mtb_evaluate, no ego     (module __init__, acc_interact.py:33-34)
                  C candidates per scene    mtb_evaluate + mtb_argmin (search.py:98-103, random_search.py:28-35); the warm
-                                           start is candidate 0, exactly what the reference's search starts from
+                                           start is kept as incumbent (candidate 0) -- a deliberate deviation, see `plan`
                  closed-loop step          mtb_env_step            (graph_based.py:82-124, warm-start shift trajopt.py:150-155)
 
 This feeds `mantrap_evaluation.evaluate`-style sweeps (metrics.py:12-63) and warm-start data generation
@@ -58,7 +58,14 @@ class BatchedClosedLoop:
 
     def plan(self, warm: torch.Tensor, candidates: torch.Tensor = None):
         """One solve for every scene: candidates [S,C,T,2] (drawn when None) with candidate 0 replaced by the warm start
-        -> (controls [S,T,2], objective [S], index [S])."""
+        -> (controls [S,T,2], objective [S], index [S]).
+
+        DELIBERATE DEVIATION from the reference's search frame: `SearchIntermediate.optimize_core`
+        (solver/base/search.py:19-81) ignores z0, starts from obj = inf and falls back to a fresh random z when nothing feasible
+        was found. A closed loop that re-plans every step from scratch throws its previous plan away, so here the shifted warm
+        start competes as candidate 0 (it can only win when it is feasible), and when NO candidate is feasible the plan is the
+        warm start again, reported with index -1 and the warm start's objective (`tests/dropin_cases.py:
+        check_plan_with_infeasible_warm_start`)."""
         eng, scene = self.engine, self.scene
         candidates = self.draw_candidates() if candidates is None else candidates.to(eng.device).clone()
         candidates[:, 0] = warm
@@ -68,7 +75,7 @@ class BatchedClosedLoop:
         res = eng.evaluate(scene, candidates.contiguous(), spec, want=("total", "violation"))
         idx, val, best = eng.argmin(res["total"], res["violation"], candidates, self.feas_tol)
         none = (idx < 0)
-        # no feasible candidate: the search returns what it started from, the warm start (search.py:70-96)
+        # no feasible candidate: keep the incumbent (the reference would draw a fresh random z here, search.py:69-70)
         best = torch.where(none[:, None, None], warm, best)
         val = torch.where(none, res["total"][:, 0], val)
         return best, val, idx

@@ -98,20 +98,31 @@ class TrajOptSolver:
     # ---- warm start --------------------------------------------------------------------------------------------
     def warm_start(self, method: str = constants.WARM_START_HARD) -> torch.Tensor:
         """"hard": the same problem with the hard modules only, started from full throttle towards the goal
-        (trajopt.py:248-306); "zeros": zero controls; "encoding": nearest pre-computed scenario (trajopt.py:308-331; needs the
-        reference's database, see `warm_start_database`). ("soft" / "potential" need modules out of scope.)"""
+        (trajopt.py:248-306); "potential": the full default formulation on a `PotentialFieldEnvironment` copy of the scene
+        (trajopt.py:266-268); "zeros": zero controls; "encoding": nearest pre-computed scenario (trajopt.py:308-331; needs a
+        database, see `warm_start_database` / `mantrap_b200.warm_start_db.pre_compute`). "soft" needs `HJReachabilityModule`,
+        whose value grid the reference does not ship."""
         if method == constants.WARM_START_HARD:
-            part = self.__class__(env=self.env, goal=self.goal, modules=self.module_hard(), t_planning=self.planning_horizon,
-                                  config_name=self.config_name, fused=self._fused, num_particles=self._num_particles)
-            _, u_max = self.env.ego.control_limits()
-            dx_goal = self.goal - self.env.ego.position
-            init = torch.stack([dx_goal / torch.norm(dx_goal).clamp(min=1e-6) * u_max] * self.planning_horizon)
-            return part.optimize(z0=init.flatten(), tag=constants.TAG_WARM_START)
+            return self._warm_start_optimization(self.env, self.module_hard())
+        if method == constants.WARM_START_POTENTIAL:
+            from .environment import PotentialFieldEnvironment
+            return self._warm_start_optimization(self.env.copy(env_type=PotentialFieldEnvironment), self.module_defaults())
+        if method == constants.WARM_START_SOFT:
+            raise ValueError("warm start 'soft' needs HJReachabilityModule (third_party/reachability/2D.mat is not shipped by the reference)")
         if method == constants.WARM_START_ZEROS:
             return torch.zeros(2 * self.planning_horizon)
         if method == constants.WARM_START_ENCODING:
             return self._warm_start_encoding()
         raise ValueError(f"Invalid warm starting-method {method} !")
+
+    def _warm_start_optimization(self, env, modules) -> torch.Tensor:
+        """The same solver class on `env` with `modules` only, started from full throttle towards the goal (trajopt.py:280-306)."""
+        part = self.__class__(env=env, goal=self.goal, modules=modules, t_planning=self.planning_horizon,
+                              config_name=self.config_name, fused=self._fused, num_particles=self._num_particles)
+        _, u_max = self.env.ego.control_limits()
+        dx_goal = self.goal - self.env.ego.position
+        init = torch.stack([dx_goal / torch.norm(dx_goal).clamp(min=1e-6) * u_max] * self.planning_horizon)
+        return part.optimize(z0=init.flatten(), tag=constants.TAG_WARM_START)
 
     # ---- encoding / pre-computed warm starts ---------------------------------------------------------------------
     def _scene_arrays(self):
@@ -213,21 +224,28 @@ class TrajOptSolver:
         if hit is not None and (not want_jacobian or "jac" in hit):
             return hit
         engine = runtime.default_engine()
-        controls = torch.from_numpy(np.asarray(z, dtype=np.float32)).view(1, 1, -1, 2)
-        rollout = any(m.needs_rollout for m in self.modules)
-        env = self.env
-        if rollout:
-            num_p = self._num_particles if env.env_kind != "kalman" else 1
-            scene = env.scene_batch(num_p, self.planning_horizon, with_noise=env.env_kind != "kalman")
-        else:
-            scene = self.modules[0]._scene().to("cpu")
-        scene.ego_goal = self.goal.view(1, 2).clone()
-        # scene and controls travel together: one staged host->device copy per callback (engine.to_device_packed)
-        fields = SceneBatch._TENSOR_FIELDS
-        moved = to_device_packed([getattr(scene, f) for f in fields] + [controls], engine.device)
-        scene, controls = dataclasses.replace(scene, **dict(zip(fields, moved[:-1]))), moved[-1]
         spec = self._fused_spec(ado_ids)
         out = hit if hit is not None else {}
+        if hit is not None:
+            # Jacobian requested for a z whose values are cached: the SAME particle draw (device scene kept with the entry), so that
+            # cons / grad / violation / jac of one z belong together ("one draw per callback set") and the global
+            # RNG does not advance on a cache hit
+            scene, controls = hit["_scene"], hit["_controls"]
+        else:
+            controls = torch.from_numpy(np.asarray(z, dtype=np.float32)).view(1, 1, -1, 2)
+            rollout = any(m.needs_rollout for m in self.modules)
+            env = self.env
+            if rollout:
+                num_p = self._num_particles if env.env_kind != "kalman" else 1
+                scene = env.scene_batch(num_p, self.planning_horizon, with_noise=env.env_kind != "kalman")
+            else:
+                scene = self.modules[0]._scene().to("cpu")
+            scene.ego_goal = self.goal.view(1, 2).clone()
+            # scene and controls travel together: one staged host->device copy per callback (engine.to_device_packed)
+            fields = SceneBatch._TENSOR_FIELDS
+            moved = to_device_packed([getattr(scene, f) for f in fields] + [controls], engine.device)
+            scene, controls = dataclasses.replace(scene, **dict(zip(fields, moved[:-1]))), moved[-1]
+            out["_scene"], out["_controls"] = scene, controls
         if hit is None:
             res = engine.evaluate(scene, controls, spec, want=("obj", "total", "grad", "cons", "violation"))
             # one device->host read for all five results (each .cpu() is a stream synchronisation of its own)

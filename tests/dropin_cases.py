@@ -416,3 +416,92 @@ def check_closed_loop(solver_cls, env_kind, steps=3, **kwargs):
     assert torch.allclose(sol.env.ego.position, env.ego.position)       # solver environment restored (trajopt.py:187-190)
     speeds = ego_traj[:, 2:4].abs().max()
     assert float(speeds) <= 2.0 + 1e-3                                  # speed limit respected along the executed path
+
+
+def check_warm_start_potential():
+    """`warm_start("potential")` (trajopt.py:266-268): the default formulation on a PotentialFieldEnvironment copy of the scene;
+    the result is a control sequence inside the variable bounds (test_solver.py:156-172)."""
+    from mantrap_b200 import constants
+    env, goal = small_scene("sf")
+    torch.manual_seed(0)
+    sol = solver.SLSQPSolver(env, goal=goal, t_planning=4, modules=[modules.GoalNormModule, modules.InteractionAccelerationModule])
+    z = sol.warm_start(method=constants.WARM_START_POTENTIAL)
+    lb, ub = sol.optimization_variable_bounds()
+    assert z.numel() == 8 and bool(torch.isfinite(z).all())
+    assert np.all(np.asarray(z.flatten()) >= np.asarray(lb) - 1e-6) and np.all(np.asarray(z.flatten()) <= np.asarray(ub) + 1e-6)
+    with np.testing.assert_raises(ValueError):
+        sol.warm_start(method=constants.WARM_START_SOFT)
+
+
+def check_goal_optimize_speed():
+    """GoalNormModule(optimize_speed=True): the reference's speed term fails in torch.dot on the first objective call
+    (goal_norm.py:63-65: a [T+1] vector dotted with a [T+1, 2] matrix); the mirror raises the same RuntimeError when evaluated."""
+    env, goal = small_scene("pf")
+    module = modules.GoalNormModule(goal=goal, env=env, optimize_speed=True, t_horizon=4)
+    traj = env.ego.unroll_trajectory(torch.ones((4, 2)) * 0.3, dt=env.dt)
+    try:
+        module.objective(traj, ado_ids=env.ado_ids, tag="t")
+    except RuntimeError as err:
+        assert "1D tensors expected" in str(err)
+    else:
+        raise AssertionError("optimize_speed=True must raise like the reference")
+    plain = modules.GoalNormModule(goal=goal, env=env, t_horizon=4)
+    assert plain.objective(traj, ado_ids=env.ado_ids, tag="t") > 0.0
+
+
+def check_warm_start_pre_compute(tmp_dir):
+    """Batched `pre_compute` (third_party/warm_start/pre_compute.py:27-58): database shapes and file format, encodings equal to
+    `TrajOptSolver.encode()` of the same scenes, solutions inside the control limits and zero after the goal was reached; the
+    written files feed `warm_start("encoding")`."""
+    from mantrap_b200 import constants, runtime, warm_start_db
+    eng = runtime.default_engine()
+    m, horizon = 6, 4
+    encodings, solutions = warm_start_db.pre_compute(eng, num_scenarios=m, solution_horizon=horizon, num_candidates=16, seed=3)
+    assert encodings.shape == (m, 4) and solutions.shape == (m, horizon, 2)
+    assert bool(torch.isfinite(encodings).all()) and bool(torch.isfinite(solutions).all())
+    assert float(solutions.abs().max()) <= constants.ROBOT_ACC_MAX + 1e-4
+    scene = warm_start_db.random_scenes(m, seed=3)
+    for i in range(m):
+        env = environment.PotentialFieldEnvironment(ego_position=scene.ego0[i, 0:2], ego_velocity=scene.ego0[i, 2:4], dt=scene.dt)
+        env.add_ado(position=scene.ado0[i, 0, 0:2], velocity=scene.ado0[i, 0, 2:4])
+        sol = solver.IPOPTSolver(env, goal=scene.ego_goal[i], t_planning=horizon, modules=[modules.GoalNormModule])
+        assert torch.allclose(sol.encode(), encodings[i], atol=1e-5)
+    warm_start_db.save(tmp_dir, encodings, solutions)
+    sol = solver.IPOPTSolver(env, goal=scene.ego_goal[m - 1], t_planning=horizon, modules=[modules.GoalNormModule], warm_start_db=tmp_dir)
+    z = sol.warm_start(method=constants.WARM_START_ENCODING)
+    assert torch.allclose(z.view(horizon, 2), solutions[m - 1])        # its own scene is its nearest entry
+
+
+def check_plan_with_infeasible_warm_start():
+    """`BatchedClosedLoop.plan` keeps the warm start as incumbent (candidate 0) -- a deliberate deviation from the reference's
+    `SearchIntermediate.optimize_core`, which ignores z0 and falls back to a fresh random z (search.py:19-81):
+    an infeasible warm start never wins while a feasible candidate exists, and when NO candidate is feasible the plan is the
+    warm start again, reported with index -1 and the warm start's objective."""
+    from mantrap_b200 import mpc, runtime, scenarios
+    eng = runtime.default_engine()
+    scene = scenarios.synthetic_scenes(3, 2, 3, env_kind="pf", seed=9, param_seed=10)
+    loop = mpc.BatchedClosedLoop(eng, scene, t_planning=4, num_candidates=6, seed=1)
+    warm_bad = torch.full((3, 4, 2), 5.0, device=eng.device)                 # |u| = 5 > ROBOT_ACC_MAX: violates the control limits
+    cands = scenarios.candidate_controls(3, 6, 4, seed=2, u_max=1.0).to(eng.device)
+    best, val, idx = loop.plan(warm_bad, cands)
+    assert bool((idx > 0).all()) and not bool(torch.isclose(best, warm_bad).all())
+    best, val, idx = loop.plan(warm_bad, cands * 10.0)                        # every candidate infeasible
+    assert bool((idx == -1).all()) and torch.equal(best, warm_bad) and bool(torch.isfinite(val).all())
+
+
+def check_jacobian_reuses_the_cached_draw():
+    """A Jacobian requested for a z whose values are already cached uses the SAME particle draw as those values and leaves the
+    global RNG untouched (one draw per z); a fresh z draws again."""
+    env, goal = small_scene("sf")
+    sol = solver.IPOPTSolver(env, goal=goal, t_planning=4, modules=[modules.GoalNormModule, modules.InteractionAccelerationModule,
+                                                                  modules.ControlLimitModule, modules.MinDistanceModule])
+    z = np.linspace(-0.5, 0.5, 8)
+    torch.manual_seed(5)
+    sol.constraints(z)
+    state = torch.get_rng_state()
+    jac_cached = sol.jacobian(z)
+    assert torch.equal(state, torch.get_rng_state())
+    sol._cache.clear()
+    torch.manual_seed(5)
+    jac_fresh = sol.jacobian(z)                      # same seed, cold cache: the identical draw -> the identical Jacobian
+    assert np.array_equal(jac_cached, jac_fresh)

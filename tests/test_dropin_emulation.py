@@ -136,3 +136,23 @@ def test_scene_copy_to_host_keeps_values_and_none():
     out = to_device_packed(src, "cpu")
     assert out[0] is None and out[1].dtype == torch.float32 and torch.equal(out[1], src[1].float())
     assert out[2].is_contiguous() and out[2].tolist() == [1.0, 1.0, 1.0]
+
+
+def test_warm_start_potential():
+    dc.check_warm_start_potential()
+
+
+def test_goal_optimize_speed():
+    dc.check_goal_optimize_speed()
+
+
+def test_warm_start_pre_compute(tmp_path):
+    dc.check_warm_start_pre_compute(str(tmp_path))
+
+
+def test_plan_with_infeasible_warm_start():
+    dc.check_plan_with_infeasible_warm_start()
+
+
+def test_jacobian_reuses_the_cached_draw():
+    dc.check_jacobian_reuses_the_cached_draw()

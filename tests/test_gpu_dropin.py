@@ -99,3 +99,23 @@ def test_packed_scene_copy():
         assert torch.equal(again.ado0, moved.ado0)
     out = engine.to_device_packed([None, torch.ones(3), None, torch.arange(5.0)], "cuda:0")
     assert out[0] is None and out[2] is None and out[1].tolist() == [1.0] * 3 and out[3].tolist() == [0.0, 1.0, 2.0, 3.0, 4.0]
+
+
+def test_warm_start_potential():
+    dc.check_warm_start_potential()
+
+
+def test_goal_optimize_speed():
+    dc.check_goal_optimize_speed()
+
+
+def test_warm_start_pre_compute(tmp_path):
+    dc.check_warm_start_pre_compute(str(tmp_path))
+
+
+def test_plan_with_infeasible_warm_start():
+    dc.check_plan_with_infeasible_warm_start()
+
+
+def test_jacobian_reuses_the_cached_draw():
+    dc.check_jacobian_reuses_the_cached_draw()
