@@ -310,6 +310,16 @@ def config1_measurements(torch):
     torch.cuda.synchronize()
     out["ipopt_iterations_per_s"] = 100.0 / (time.perf_counter() - t0)
     out["ipopt_iteration_note"] = "objective + gradient + constraints + jacobian at one z = two launches (per-z cache)"
+    # K independent callback sets per launch (K IPOPT replicas / line-search points of one scene): TrajOptSolver.evaluate_fused_batch
+    zb = np.stack(zs[20:84])
+    for _ in range(3):
+        solver.evaluate_fused_batch(zb, want_jacobian=True)
+    t0 = time.perf_counter()
+    for _ in range(20):
+        solver.evaluate_fused_batch(zb, want_jacobian=True)
+    torch.cuda.synchronize()
+    out["batched_ipopt_iterations_per_s"] = 20 * zb.shape[0] / (time.perf_counter() - t0)
+    out["batched_note"] = "64 callback sets (values + gradient + rows + dense Jacobian) per launch pair through evaluate_fused_batch"
     slsqp = mantrap.solver.SLSQPSolver(env, goal=goal, t_planning=10, modules=modules)
     z0 = slsqp.warm_start()
     slsqp.optimize(z0, tag="bench", max_iter=30)

@@ -298,6 +298,120 @@ def launch_argmin(lib: ctypes.CDLL, total: torch.Tensor, violation: typing.Optio
     return best_idx, best_val, best_controls
 
 
+class PreparedEvaluation:
+    """A solver callback as a PRE-BUILT launch (the per-callback host work of `launch_evaluate` done once): the C-ABI structs,
+    the output buffers, the kernel scratch and a device copy of the static scene (states, goals, ego-free baseline) are created
+    when the solver is set up; a call only writes what changes between callbacks -- K candidate control sequences and the fresh
+    particle draw (`create_particles`, particle.py:40-79, + the per-step noise, :165) -- into ONE pinned host block, copies it
+    with ONE host->device transfer, launches `mtb_evaluate` (and `mtb_constraint_jacobian` on request) and reads every result
+    back with ONE device->host transfer. This is what `TrajOptSolver.objective / gradient / constraints / jacobian`
+    (solver/base/trajopt.py:368-434, solver/ipopt.py:118-154) cost per IPOPT iteration.
+
+    `scene` holds the static fields on the host (ego0, ado0, ado_goal, ego_goal); `spec.mus_wo` / `spec.ado_mask` are device tensors.
+    """
+    RESULT_KEYS = ("obj", "cons", "grad", "total", "violation")
+
+    def __init__(self, engine: "Engine", scene: SceneBatch, spec: ModuleSpec, t_horizon: int, num_particles: int,
+                 num_candidates: int = 1, with_noise: bool = True):
+        self.engine, self.spec, self.t_horizon, self.k = engine, spec, t_horizon, num_candidates
+        dev, n, p = engine.device, scene.num_ados, num_particles
+        particle_env = scene.env_kind != "kalman"
+        # dynamic inputs: one block [controls | v0 | sigma | weight | noise], 16-byte aligned segments
+        shapes = [("controls", (1, num_candidates, t_horizon, 2))]
+        if particle_env:
+            shapes += [("v0", (1, n, p)), ("sigma", (1, n, p)), ("weight", (1, n, p))]
+            if with_noise and t_horizon > 1:
+                shapes.append(("noise", (1, t_horizon - 1, n, p, 2)))
+        self._spans, total = {}, 0
+        for name, shape in shapes:
+            count = int(math.prod(shape))
+            self._spans[name] = (total, count, shape)
+            total += -(-count // 4) * 4
+        pin = dev.type == "cuda"
+        self.hin = torch.zeros(total, dtype=torch.float32, pin_memory=pin)
+        self.din = torch.zeros(total, dtype=torch.float32, device=dev)
+        self._hin_np = self.hin.numpy()
+        dyn = {name: self.din[o:o + c].view(shape) for name, (o, c, shape) in self._spans.items()}
+        static = dataclasses.replace(scene, v0=None, sigma=None, weight=None, noise=None).to(dev)
+        self.scene = dataclasses.replace(static, v0=dyn.get("v0"), sigma=dyn.get("sigma"), weight=dyn.get("weight"), noise=dyn.get("noise"))
+        self.controls = dyn["controls"]
+        self._pb = _problem_struct(self.scene, self.controls, t_horizon)
+        self._md = _module_struct(self.scene, spec)
+        lib = engine.lib
+        rows = lib.mtb_num_constraint_rows(ctypes.byref(self._pb), ctypes.byref(self._md))
+        if rows < 0:
+            _cabi.check(lib, rows, "mtb_num_constraint_rows")
+        self.rows = rows
+        # results: one block [obj | cons | grad | total | violation] (+ a second one for the dense Jacobian)
+        sizes = {"obj": num_candidates * NUM_OBJECTIVES, "cons": num_candidates * rows, "grad": num_candidates * 2 * t_horizon,
+                 "total": num_candidates, "violation": num_candidates}
+        self._out_spans, total = {}, 0
+        for name in self.RESULT_KEYS:
+            self._out_spans[name] = (total, sizes[name])
+            total += -(-sizes[name] // 4) * 4
+        self.dout = torch.zeros(max(total, 4), dtype=torch.float32, device=dev)
+        self.hout = torch.zeros(max(total, 4), dtype=torch.float32, pin_memory=pin)
+        self._hout_np = self.hout.numpy()
+        self._outs = _cabi.MtbOutputs()
+        for name in self.RESULT_KEYS:
+            o, c = self._out_spans[name]
+            if c > 0:
+                setattr(self._outs, name, self.dout[o:o + c].data_ptr())
+        self.djac = torch.zeros(max(num_candidates * rows * 2 * t_horizon, 1), dtype=torch.float32, device=dev)
+        self.hjac = torch.zeros(max(num_candidates * rows * 2 * t_horizon, 1), dtype=torch.float32, pin_memory=pin)
+        need = lib.mtb_workspace_bytes(ctypes.byref(self._pb), 1)
+        self._ws = torch.empty(max(need, 16), dtype=torch.uint8, device=dev)
+        self._ws_bytes = need
+
+    def stage(self, controls, draw: typing.Optional[typing.Dict[str, torch.Tensor]]):
+        """Write this call's inputs into the pinned host block: controls [K, 2T] (numpy or tensor) and the particle draw."""
+        o, c, _ = self._spans["controls"]
+        self._hin_np[o:o + c] = controls.reshape(-1) if not isinstance(controls, torch.Tensor) else controls.reshape(-1).numpy()
+        if draw is not None:
+            for name in ("v0", "sigma", "weight", "noise"):
+                if name in self._spans and draw.get(name) is not None:
+                    o, c, _ = self._spans[name]
+                    self.hin[o:o + c].copy_(draw[name].reshape(-1))
+
+    def staged_inputs(self):
+        """Copy of the staged host block (kept with a cache entry so that a later Jacobian request re-uses the same draw)."""
+        return self._hin_np.copy()
+
+    def restore(self, staged):
+        self._hin_np[:] = staged
+
+    def run(self, want_jacobian: bool = False, want_values: bool = True) -> typing.Dict:
+        """Upload the staged inputs, launch, read back. Returns numpy arrays: obj [K,5], cons [K,R], grad [K,2T], total [K],
+        violation [K] (when `want_values`) and jac [K,R,2T] (when `want_jacobian`)."""
+        eng, lib = self.engine, self.engine.lib
+        stream = eng._stream()
+        with eng._guard():
+            self.din.copy_(self.hin, non_blocking=True)
+            if want_values:
+                code = lib.mtb_evaluate(ctypes.byref(self._pb), ctypes.byref(self._md), ctypes.byref(self._outs),
+                                        self._ws.data_ptr() if self._ws_bytes > 0 else None, self._ws_bytes, stream)
+                _cabi.check(lib, code, "mtb_evaluate")
+                self.hout.copy_(self.dout, non_blocking=True)
+                eng.launches += 1
+            if want_jacobian and self.rows > 0:
+                code = lib.mtb_constraint_jacobian(ctypes.byref(self._pb), ctypes.byref(self._md), None, self.djac.data_ptr(), None, 0, stream)
+                _cabi.check(lib, code, "mtb_constraint_jacobian")
+                self.hjac.copy_(self.djac, non_blocking=True)
+                eng.launches += 1
+            if eng.device.type == "cuda":
+                torch.cuda.current_stream(eng.device).synchronize()
+        out = {}
+        k, t2 = self.k, 2 * self.t_horizon
+        if want_values:
+            shapes = {"obj": (k, NUM_OBJECTIVES), "cons": (k, self.rows), "grad": (k, t2), "total": (k,), "violation": (k,)}
+            for name in self.RESULT_KEYS:
+                o, c = self._out_spans[name]
+                out[name] = self._hout_np[o:o + c].reshape(shapes[name]).copy()
+        if want_jacobian:
+            out["jac"] = self.hjac.numpy()[:k * self.rows * t2].reshape(k, self.rows, t2).copy() if self.rows > 0 else None
+        return out
+
+
 class Engine:
     """The product entry point of the batched hot path: binds the CUDA library (no fallback) and counts launches."""
 

@@ -17,6 +17,7 @@ Mirrors: GraphBasedEnvironment environment/base/graph_based.py:14-560, ParticleE
 SocialForcesEnvironment environment/social_forces.py:11-210, PotentialFieldEnvironment environment/simplified/
 potential_field.py:10-99, KalmanEnvironment environment/simplified/kalman.py:11-124.
 """
+import dataclasses
 import math
 import typing
 
@@ -238,17 +239,21 @@ class GraphBasedEnvironment:
                     with_noise: bool = True, **param_dicts) -> SceneBatch:
         """This scene as a `SceneBatch` of one scene on the host, with particle parameters freshly drawn from torch's
         global CPU generator in the reference's order (one `create_particles`, then one `torch.rand` per step)."""
+        params = self.draw_particle_parameters(num_particles, (t_horizon - 1) if (with_noise and t_horizon) else 0,
+                                               **param_dicts)
+        return dataclasses.replace(self.scene_static(), v0=params.get("v0"), sigma=params.get("sigma"), weight=params.get("weight"),
+                                   noise=params.get("noise"))
+
+    def scene_static(self) -> SceneBatch:
+        """The part of the scene that does not change between the callbacks of one solve (states, goals): no random numbers."""
         _, ado_states = self.states()
         goals = torch.stack([torch.as_tensor(a.params.get("goal", a.position)).float() for a in self.ados]) \
             if self.num_ados > 0 else torch.zeros((0, 2))
-        params = self.draw_particle_parameters(num_particles, (t_horizon - 1) if (with_noise and t_horizon) else 0,
-                                               **param_dicts)
         ego = self.ego
         return SceneBatch(
             env_kind=self.env_kind, ego_kind=ego.ego_kind if ego is not None else None, dt=float(self.dt),
             ego0=ego.state[None].clone() if ego is not None else None, ego_goal=None,
             ado0=ado_states[None, :, 0:4].contiguous(), ado_goal=goals[None].contiguous(),
-            v0=params.get("v0"), sigma=params.get("sigma"), weight=params.get("weight"), noise=params.get("noise"),
             axes_diag=float(((self.x_axis[1] - self.x_axis[0]) ** 2 + (self.y_axis[1] - self.y_axis[0]) ** 2) ** 0.5))
 
     def draw_particle_parameters(self, num_particles: int, num_noise_steps: int, **param_dicts

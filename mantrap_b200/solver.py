@@ -25,7 +25,7 @@ import numpy as np
 import torch
 
 from . import constants, modules as mods, runtime
-from .engine import OBJECTIVE_KEYS, ModuleSpec, SceneBatch, to_device_packed
+from .engine import PreparedEvaluation, OBJECTIVE_KEYS, ModuleSpec, SceneBatch, to_device_packed
 
 
 class TrajOptSolver:
@@ -49,7 +49,7 @@ class TrajOptSolver:
             self._module_dict[module.name] = module
         self._attention_module = attention_module(env=self.env, t_horizon=self.planning_horizon) \
             if attention_module is not None else None
-        self._log, self._cache = {}, {}
+        self._log, self._cache, self._prepared_calls = {}, {}, {}
         self._is_logging = is_logging
         assert self.num_optimization_variables() > 0
 
@@ -84,6 +84,7 @@ class TrajOptSolver:
 
     def _refresh_modules(self):
         self._cache.clear()
+        self._prepared_calls.clear()              # the static scene on the device belongs to the previous environment state
         for module in self.modules:
             module.reset_env(env=self.env)
 
@@ -216,53 +217,71 @@ class TrajOptSolver:
                 spec.weights.pop(key, None)
         return spec
 
+    def _prepared(self, ado_ids: typing.List[str], num_candidates: int = 1) -> PreparedEvaluation:
+        """The pre-built launch of this solver's callback (engine.PreparedEvaluation): static scene on the device, C-ABI structs,
+        result buffers and scratch are set up once per (environment state, ado_ids, candidate count)."""
+        key = (tuple(ado_ids), num_candidates)
+        prep = self._prepared_calls.get(key)
+        if prep is None:
+            engine, env = runtime.default_engine(), self.env
+            rollout = any(m.needs_rollout for m in self.modules)
+            if rollout:
+                scene = env.scene_static()
+                num_p = self._num_particles if env.env_kind != "kalman" else 1
+            else:                                   # ego-only modules: no random numbers, one inert Kalman ado
+                scene, num_p = self.modules[0]._scene().to("cpu"), 1
+            scene.ego_goal = self.goal.view(1, 2).clone()
+            prep = PreparedEvaluation(engine, scene, self._fused_spec(ado_ids), self.planning_horizon, num_p, num_candidates,
+                                      with_noise=rollout and env.env_kind != "kalman")
+            prep.draws = rollout and env.env_kind != "kalman"
+            prep.num_particles = num_p
+            self._prepared_calls[key] = prep
+        return prep
+
     def evaluate_fused(self, z: np.ndarray, ado_ids: typing.List[str], want_jacobian: bool = False) -> typing.Dict:
         """One launch for everything the callbacks need at this z (cached). Keys: obj {module: value}, total, grad [2T],
-        cons {module: rows}, violation, optionally jac {module: [rows, 2T]}."""
+        cons {module: rows}, violation, optionally jac {module: [rows, 2T]}. Per call only z and the fresh particle draw travel to
+        the device (one pinned block, one copy) and one block of results comes back (engine.PreparedEvaluation)."""
         key = (np.asarray(z, dtype=np.float64).tobytes(), tuple(ado_ids))
         hit = self._cache.get(key)
         if hit is not None and (not want_jacobian or "jac" in hit):
             return hit
-        engine = runtime.default_engine()
-        spec = self._fused_spec(ado_ids)
-        out = hit if hit is not None else {}
-        if hit is not None:
-            # Jacobian requested for a z whose values are cached: the SAME particle draw (device scene kept with the entry), so that
+        prep = self._prepared(ado_ids)
+        spec = prep.spec
+        if hit is None:
+            draw = self.env.draw_particle_parameters(prep.num_particles, self.planning_horizon - 1) if prep.draws else None
+            prep.stage(np.asarray(z, dtype=np.float32), draw)
+            res = prep.run(want_jacobian=want_jacobian)
+            obj, cons = res["obj"][0], res["cons"][0]
+            out = dict(obj={m.name: float(obj[OBJECTIVE_KEYS.index(m.fused_key)]) for m in self.modules
+                            if getattr(m, "fused_key", None) is not None},
+                       total=float(res["total"][0]), grad=res["grad"][0].astype(np.float64), violation=float(res["violation"][0]),
+                       cons=self._split_rows(cons, ado_ids, spec), _staged=prep.staged_inputs())
+        else:
+            # Jacobian requested for a z whose values are cached: the SAME particle draw (staged inputs kept with the entry), so that
             # cons / grad / violation / jac of one z belong together ("one draw per callback set", DESIGN.md §5 (iii)) and the global
             # RNG does not advance on a cache hit
-            scene, controls = hit["_scene"], hit["_controls"]
-        else:
-            controls = torch.from_numpy(np.asarray(z, dtype=np.float32)).view(1, 1, -1, 2)
-            rollout = any(m.needs_rollout for m in self.modules)
-            env = self.env
-            if rollout:
-                num_p = self._num_particles if env.env_kind != "kalman" else 1
-                scene = env.scene_batch(num_p, self.planning_horizon, with_noise=env.env_kind != "kalman")
-            else:
-                scene = self.modules[0]._scene().to("cpu")
-            scene.ego_goal = self.goal.view(1, 2).clone()
-            # scene and controls travel together: one staged host->device copy per callback (engine.to_device_packed)
-            fields = SceneBatch._TENSOR_FIELDS
-            moved = to_device_packed([getattr(scene, f) for f in fields] + [controls], engine.device)
-            scene, controls = dataclasses.replace(scene, **dict(zip(fields, moved[:-1]))), moved[-1]
-            out["_scene"], out["_controls"] = scene, controls
-        if hit is None:
-            res = engine.evaluate(scene, controls, spec, want=("obj", "total", "grad", "cons", "violation"))
-            # one device->host read for all five results (each .cpu() is a stream synchronisation of its own)
-            parts = [res[k][0, 0].reshape(-1) for k in ("obj", "cons", "grad", "total", "violation")]
-            flat = torch.cat(parts).cpu().numpy()
-            obj, cons, grad, total, violation = np.split(flat, np.cumsum([p.numel() for p in parts])[:-1])
-            out.update(obj={m.name: float(obj[OBJECTIVE_KEYS.index(m.fused_key)]) for m in self.modules
-                            if getattr(m, "fused_key", None) is not None},
-                       total=float(total[0]), grad=grad.astype(np.float64), violation=float(violation[0]),
-                       cons=self._split_rows(cons, ado_ids, spec))
+            out = hit
+            prep.restore(hit["_staged"])
+            res = prep.run(want_jacobian=True, want_values=False)
         if want_jacobian:
-            jac = engine.constraint_jacobian(scene, controls, spec)[0, 0].cpu().numpy().astype(np.float64)
-            out["jac"] = self._split_rows(jac, ado_ids, spec)
+            out["jac"] = self._split_rows(res["jac"][0].astype(np.float64), ado_ids, spec) if res["jac"] is not None else {}
         if len(self._cache) > 64:
             self._cache.clear()
         self._cache[key] = out
         return out
+
+    def evaluate_fused_batch(self, z: np.ndarray, ado_ids: typing.List[str] = None, want_jacobian: bool = False) -> typing.Dict:
+        """K independent callback sets in ONE launch (SURVEY §8e "replicas only": K IPOPT replicas, line-search points or restarts
+        of the same scene): z [K, 2T] -> total [K], grad [K, 2T], cons [K, R] (kernel row order), violation [K] and, on request, the
+        dense Jacobians jac [K, R, 2T]. All K share one particle draw (they are candidates of one scene)."""
+        ado_ids = ado_ids if ado_ids is not None else self.env.ado_ids
+        assert self._fusable(), "evaluate_fused_batch needs the built-in (fused) modules"
+        z = np.asarray(z, dtype=np.float32)
+        prep = self._prepared(ado_ids, z.shape[0])
+        draw = self.env.draw_particle_parameters(prep.num_particles, self.planning_horizon - 1) if prep.draws else None
+        prep.stage(z, draw)
+        return prep.run(want_jacobian=want_jacobian)
 
     def _split_rows(self, rows: np.ndarray, ado_ids, spec: ModuleSpec) -> typing.Dict[str, np.ndarray]:
         """Kernel row order (control | speed | min-distance | ellipsoid) -> per module, min-distance restricted to

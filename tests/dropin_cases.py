@@ -505,3 +505,26 @@ def check_jacobian_reuses_the_cached_draw():
     torch.manual_seed(5)
     jac_fresh = sol.jacobian(z)                      # same seed, cold cache: the identical draw -> the identical Jacobian
     assert np.array_equal(jac_cached, jac_fresh)
+
+
+def check_evaluate_fused_batch():
+    """K callback sets in one launch (`evaluate_fused_batch`) = K single callbacks under the same seed (one draw per scene)."""
+    env, goal = small_scene("sf")
+    sol = solver.IPOPTSolver(env, goal=goal, t_planning=4, modules=[modules.GoalNormModule, modules.InteractionAccelerationModule,
+                                                                  modules.ControlLimitModule, modules.MinDistanceModule])
+    rng = np.random.RandomState(3)
+    zs = rng.uniform(-1, 1, (5, 8))
+    torch.manual_seed(11)
+    batch = sol.evaluate_fused_batch(zs, want_jacobian=True)
+    assert batch["total"].shape == (5,) and batch["grad"].shape == (5, 8) and batch["jac"].shape[0] == 5
+    for k in range(5):
+        sol._cache.clear()
+        torch.manual_seed(11)
+        one = sol.evaluate_fused(zs[k], sol.env.ado_ids, want_jacobian=True)
+        assert abs(one["total"] - float(batch["total"][k])) <= 1e-6 * max(1.0, abs(one["total"]))
+        gio.assert_parity(batch["grad"][k], one["grad"], 1e-5, "batched gradient", atol=1e-7)
+        assert abs(one["violation"] - float(batch["violation"][k])) <= 1e-6
+        rows = np.concatenate([one["cons"][name] for name in ("control_limits", "min_distance")])
+        gio.assert_parity(batch["cons"][k], rows, 1e-6, "batched rows")
+        jac = np.concatenate([one["jac"][name] for name in ("control_limits", "min_distance")])
+        gio.assert_parity(batch["jac"][k], jac, 1e-5, "batched Jacobian", atol=1e-7)

@@ -156,3 +156,7 @@ def test_plan_with_infeasible_warm_start():
 
 def test_jacobian_reuses_the_cached_draw():
     dc.check_jacobian_reuses_the_cached_draw()
+
+
+def test_evaluate_fused_batch():
+    dc.check_evaluate_fused_batch()

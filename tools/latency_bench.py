@@ -41,6 +41,21 @@ if __name__ == "__main__":
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) / 200
         print(f"config 1 callback {name}: {dt * 1e6:.0f} us per call ({1.0 / dt:.0f} calls/s), one process, one GPU", flush=True)
+    # where the time of one callback goes: particle draw (host, the reference's RNG stream) | staging into the pinned block |
+    # upload + launch + read-back + synchronise
+    prep = solver._prepared(solver.env.ado_ids)
+    t_draw = t_stage = t_run = 0.0
+    for z in zs[20:]:
+        t0 = time.perf_counter()
+        draw = solver.env.draw_particle_parameters(prep.num_particles, solver.planning_horizon - 1)
+        t1 = time.perf_counter()
+        prep.stage(np.asarray(z, dtype=np.float32), draw)
+        t2 = time.perf_counter()
+        prep.run()
+        t3 = time.perf_counter()
+        t_draw, t_stage, t_run = t_draw + t1 - t0, t_stage + t2 - t1, t_run + t3 - t2
+    print(f"config 1 callback breakdown: particle draw {t_draw / 200 * 1e6:.0f} us | staging {t_stage / 200 * 1e6:.0f} us | "
+          f"H2D + launch + D2H + sync {t_run / 200 * 1e6:.0f} us", flush=True)
     # all four callbacks at the same z (what one IPOPT iteration does): one launch + one Jacobian launch, cached per z
     t0 = time.perf_counter()
     for z in zs[20:]:
@@ -48,3 +63,12 @@ if __name__ == "__main__":
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / 200
     print(f"config 1 one IPOPT iteration (objective + gradient + constraints + jacobian at one z): {dt * 1e6:.0f} us", flush=True)
+    zb = np.stack(zs[20:84])
+    solver.evaluate_fused_batch(zb, want_jacobian=True)
+    t0 = time.perf_counter()
+    for _ in range(20):
+        solver.evaluate_fused_batch(zb, want_jacobian=True)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / 20
+    print(f"config 1 batched callbacks: 64 callback sets (values + gradient + rows + Jacobian) in {dt * 1e6:.0f} us "
+          f"({dt / 64 * 1e6:.1f} us per set)", flush=True)
