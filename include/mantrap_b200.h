@@ -146,7 +146,8 @@ typedef struct mtb_launch_info {
     int32_t smem_bytes, tape_in_smem;
     int32_t num_items, blocks_per_sm;      /* blocks_per_sm = resident blocks of the launched instantiation (registers and shared memory) */
     int32_t variant_maxt, variant_minb;    /* __launch_bounds__ of the instantiation */
-    int32_t kernel_kind, evals_per_thread; /* 0 = evaluate_kernel (one evaluation per group of threads) */
+    int32_t kernel_kind, evals_per_thread; /* 0 = evaluate_kernel (one evaluation per group of threads), 1 = evaluate_pair_kernel (two
+                                            * candidates per thread), 2 = its lean instantiation (batched search calls) */
 } mtb_launch_info;
 
 int mtb_abi_version(void);

@@ -1138,7 +1138,15 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     info.variant_maxt = variant.maxt;
     info.variant_minb = variant.minb;
     {
-        const int by_regs = select_inst(pb->env_kind, want_grad, variant, EV)->resident_blocks(block, smem);
+        // LEAN instantiation of the pair kernel: nothing but controls -> (goal, acc) objectives, control / speed rows, gradient
+        const bool lean = EV == 2 && pb->env_kind == MTB_ENV_SOCIAL_FORCES && pb->noise == nullptr && pb->ego_traj == nullptr &&
+                          prm.keep_var == 0 && prm.rows_mind == 0 && prm.rows_ell == 0 &&
+                          (md == nullptr || (md->w_vel == 0.f && md->w_pos == 0.f && md->w_prob == 0.f && md->ado_mask == nullptr &&
+                                             md->seed_mus == nullptr && md->seed_sigmas == nullptr)) &&
+                          (out == nullptr || (out->obj_raw == nullptr && out->grad_traj == nullptr && out->ego_traj == nullptr &&
+                                              out->mus == nullptr && out->sigmas == nullptr && out->stats == nullptr));
+        info.kernel_kind = EV == 2 ? (lean ? 2 : 1) : 0;
+        const int by_regs = select_inst(pb->env_kind, want_grad, variant, EV == 2 ? (lean ? 3 : 2) : 1)->resident_blocks(block, smem);
         if (by_regs >= 1 && by_regs < blocks_per_sm) blocks_per_sm = by_regs;
     }
     int grid = lim.sms * blocks_per_sm;
@@ -1162,7 +1170,6 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     info.tape_in_smem = prm.tape_in_smem;
     info.num_items = prm.num_items;
     info.blocks_per_sm = blocks_per_sm;
-    info.kernel_kind = EV == 2 ? 1 : 0;
     info.evals_per_thread = EV;
     return 0;
 }
@@ -1175,7 +1182,11 @@ struct KernelOf<ENV, GRAD, MAXT, MINB, 1> {
 };
 template <int ENV, bool GRAD, int MAXT, int MINB>
 struct KernelOf<ENV, GRAD, MAXT, MINB, 2> {
-    static constexpr auto fn = evaluate_pair_kernel<ENV, GRAD, MAXT, MINB>;
+    static constexpr auto fn = evaluate_pair_kernel<ENV, GRAD, MAXT, MINB, false>;
+};
+template <int ENV, bool GRAD, int MAXT, int MINB>
+struct KernelOf<ENV, GRAD, MAXT, MINB, 3> {                 // pair kernel, LEAN instantiation (batched search calls)
+    static constexpr auto fn = evaluate_pair_kernel<ENV, GRAD, MAXT, MINB, true>;
 };
 
 template <int ENV, bool GRAD, int MAXT, int MINB, int EVT = 1>
@@ -1241,15 +1252,16 @@ static const InstOps* select_variant(Variant v) {
 }
 
 template <int ENV, bool GRAD>
-static const InstOps* select_pair_variant(Variant v) {
-    if (v.maxt > kDefaultBlock) return Inst<ENV, GRAD, kMaxThreads, 1, 2>::ops();
+static const InstOps* select_pair_variant(Variant v, bool lean) {
+    if (lean) return Inst<ENV, GRAD, kDefaultBlock, 2, 3>::ops();
     return Inst<ENV, GRAD, kDefaultBlock, 2, 2>::ops();
 }
 
 static const InstOps* select_inst(int env, bool grad, Variant v, int evals_per_thread) {
-    if (evals_per_thread == 2) {
-        if (env == MTB_ENV_SOCIAL_FORCES) return grad ? select_pair_variant<MTB_ENV_SOCIAL_FORCES, true>(v) : select_pair_variant<MTB_ENV_SOCIAL_FORCES, false>(v);
-        return grad ? select_pair_variant<MTB_ENV_POTENTIAL_FIELD, true>(v) : select_pair_variant<MTB_ENV_POTENTIAL_FIELD, false>(v);
+    if (evals_per_thread >= 2) {                            // 2: pair kernel, 3: its LEAN instantiation (social forces only)
+        const bool lean = evals_per_thread == 3;
+        if (env == MTB_ENV_SOCIAL_FORCES) return grad ? select_pair_variant<MTB_ENV_SOCIAL_FORCES, true>(v, lean) : select_pair_variant<MTB_ENV_SOCIAL_FORCES, false>(v, lean);
+        return grad ? select_pair_variant<MTB_ENV_POTENTIAL_FIELD, true>(v, false) : select_pair_variant<MTB_ENV_POTENTIAL_FIELD, false>(v, false);
     }
     switch (env) {
         case MTB_ENV_SOCIAL_FORCES: return grad ? select_variant<MTB_ENV_SOCIAL_FORCES, true>(v) : select_variant<MTB_ENV_SOCIAL_FORCES, false>(v);
@@ -1342,7 +1354,7 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const mtb::Variant variant = {info.variant_maxt, info.variant_minb};
-    return mtb::select_inst(problem->env_kind, want_grad, variant, prm.EV)->launch(prm, info, st);
+    return mtb::select_inst(problem->env_kind, want_grad, variant, prm.EV == 2 ? (info.kernel_kind == 2 ? 3 : 2) : 1)->launch(prm, info, st);
 }
 
 int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, int32_t num_candidates, float feas_tol,

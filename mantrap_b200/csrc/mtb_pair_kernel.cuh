@@ -83,7 +83,12 @@ MTB_DEV float4 objective_seed_pair(const KParams& prm, const float* misc, const 
     return sd;
 }
 
-template <int ENV, bool GRAD, int MAXT, int MINB>
+// LEAN: the instantiation of the batched search workloads (BASELINE configs 2 / 4 / 5): controls in, goal + interaction-acceleration
+// objective, control / speed rows, totals / violation / gradient out -- no velocity noise, no caller seeds, no given trajectory, no
+// attention mask, no variance-based modules, no rollout outputs, no counters. The general instantiation carries all of that as
+// run-time branches; compiling it out shortens the kernel by a third (instruction-cache misses were 0.7 of 7 stall cycles per
+// issued instruction) and frees registers. The launcher picks LEAN whenever the call qualifies (plan()).
+template <int ENV, bool GRAD, int MAXT, int MINB, bool LEAN = false>
 __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams prm) {
     MTB_SHARED_FLOAT4(smem4);
     float* smem = reinterpret_cast<float*>(smem4);
@@ -113,7 +118,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
     const int dir_stride = (T - 1) * N;
     float2* accdir = reinterpret_cast<float2*>(sm + prm.off_dir);  // [2][T-1][N]
     float2* varbuf = reinterpret_cast<float2*>(sm + prm.off_var); // [2][T][N]
-    const bool keep_var = prm.keep_var != 0;
+    const bool keep_var = !LEAN && prm.keep_var != 0;
+    const float* noise = LEAN ? nullptr : prm.pb.noise;
     float* misc = sm + prm.off_misc;                              // [2][kMiscFloats]
 
     // Backward tape in the per-block L2-resident scratch, addressed per thread: plane 2 t holds the particle position of both
@@ -139,7 +145,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
         const int s = (int)(ev0 / (size_t)prm.pb.num_candidates);
 
         // ------------------------------------------------------------------ controls -> ego trajectories
-        const bool traj_given = prm.pb.ego_traj != nullptr;
+        const bool traj_given = !LEAN && prm.pb.ego_traj != nullptr;
         if (!traj_given) {
             const float* u_g = prm.pb.controls + ev0 * (size_t)(2 * T);
             for (int idx = g; idx < 4 * T; idx += GP) {
@@ -207,7 +213,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
             }
         }
         const float inv_sig = 1.0f / psig;
-        float* sig_out = (prm.out.sigmas != nullptr && pair_valid) ? prm.out.sigmas + ev0 * (size_t)N * T * 2 : nullptr;   // [2][N][T][2]
+        float* sig_out = (!LEAN && prm.out.sigmas != nullptr && pair_valid) ? prm.out.sigmas + ev0 * (size_t)N * T * 2 : nullptr;   // [2][N][T][2]
         if (sig_out != nullptr && active && i == 0) {
             for (int c = 0; c < 2; ++c) {
                 sig_out[(c * N * T + m * T) * 2 + 0] = prm.pb.var_initial;
@@ -238,7 +244,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                         }
                         if ((m >> 5) == wd) { bits_a &= ~(1u << (m & 31)); bits_b &= ~(1u << (m & 31)); }   // never the own ado
                         if (GRAD && prm.use_tape) maskbuf[t * mask_stride + wd] = make_uint2(bits_a, bits_b);
-                        n_pairs += __popc(bits_a) + __popc(bits_b);
+                        if (!LEAN) n_pairs += __popc(bits_a) + __popc(bits_b);
                         unsigned bits = bits_a | bits_b;          // the two neighbour sets are almost always identical
                         while (bits) {
                             const int kb = __ffs((int)bits) - 1;
@@ -253,13 +259,13 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     {
                         const Repulsion2 o = repulsion_forward2(p - row_p(eg), v - row_v(eg), pv0, inv_sig, dt, u_ped);
                         u = u - o.force;
-                        n_ego += 2;
+                        if (!LEAN) n_ego += 2;
                     }
                 } else {                                          // potential field
                     u = v;
                     const W2 delta = row_p(eg) - p;
                     u = u + sel(pf_gate2(v, delta, prm.pb.pf_theta_max), pf_impact2(delta, pv0), wzero());
-                    n_ego += 2;
+                    if (!LEAN) n_ego += 2;
                 }
                 if (GRAD && prm.use_tape) {
                     tape[(2 * t) * tape_stride] = make_float4(p.x.a, p.x.b, p.y.a, p.y.b);
@@ -270,8 +276,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                 const P2 dt2 = splat(dt);
                 p = w2(fma2(dt2, up.x, p.x), fma2(dt2, up.y, p.y));
                 W2 vel = v;
-                if (prm.pb.noise != nullptr) {
-                    const float* nz = prm.pb.noise + ((((size_t)s * (T - 1) + t) * N + m) * P + i) * 2;
+                if (noise != nullptr) {
+                    const float* nz = noise + ((((size_t)s * (T - 1) + t) * N + m) * P + i) * 2;
                     const P2 pn = splat(prm.pb.particle_noise);
                     vel.x = fma2(splat(__ldg(nz)), pn, vel.x);
                     vel.y = fma2(splat(__ldg(nz + 1)), pn, vel.y);
@@ -325,8 +331,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
 
         // ================================================================== objectives + constraints (per candidate)
         const float* wo_scene = (prm.md.mus_wo != nullptr) ? prm.md.mus_wo + (size_t)s * N * T * 4 : nullptr;
-        const uint8_t* amask = (prm.md.ado_mask != nullptr) ? prm.md.ado_mask + (size_t)s * N : nullptr;
-        const bool want_interact = wo_scene != nullptr && (prm.md.w_acc != 0.f || prm.md.w_vel != 0.f || prm.md.w_pos != 0.f);
+        const uint8_t* amask = (!LEAN && prm.md.ado_mask != nullptr) ? prm.md.ado_mask + (size_t)s * N : nullptr;
+        const bool want_interact = wo_scene != nullptr && (prm.md.w_acc != 0.f || (!LEAN && (prm.md.w_vel != 0.f || prm.md.w_pos != 0.f)));
         const bool want_prob = wo_scene != nullptr && keep_var && prm.md.w_prob != 0.f;
         float gx = 0.f, gy = 0.f;
         if (prm.md.w_goal != 0.f) { gx = __ldg(prm.md.ego_goal + (size_t)s * 2); gy = __ldg(prm.md.ego_goal + (size_t)s * 2 + 1); }
@@ -360,11 +366,11 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                         part.b += nn;
                         if (GRAD) accdir_c[t * N + k] = (nn > 0.f) ? make_float2(ax / nn, ay / nn) : make_float2(0.f, 0.f);   // norm'(0) = 0
                     }
-                    if (prm.md.w_vel != 0.f) {
+                    if (!LEAN && prm.md.w_vel != 0.f) {
                         const float dx = cur.z - wcur.z, dy = cur.w - wcur.w;
                         part.c += sqrtf(dx * dx + dy * dy);
                     }
-                    if (prm.md.w_pos != 0.f) part.d += fabsf(cur.x - wcur.z) + fabsf(cur.y - wcur.w);
+                    if (!LEAN && prm.md.w_pos != 0.f) part.d += fabsf(cur.x - wcur.z) + fabsf(cur.y - wcur.w);
                 }
             }
             part = group_reduce4(part, GP, e, red);
@@ -416,7 +422,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     }
                     base += prm.rows_speed;
                 }
-                if (prm.rows_mind > 0) {
+                if (!LEAN && prm.rows_mind > 0) {
                     for (int idx = g; idx < TN; idx += GP) {
                         const int k = idx / T, t = idx - k * T;
                         const float4 mu = cand_row(mus, t * N + k, c);
@@ -428,7 +434,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     }
                     base += prm.rows_mind;
                 }
-                if (prm.rows_ell > 0) {                           // ellipsoid_interact.py:47-57, every ado of the scene
+                if (!LEAN && prm.rows_ell > 0) {                  // ellipsoid_interact.py:47-57, every ado of the scene
                     for (int idx = g; idx < TN; idx += GP) {
                         const int k = idx / T, t = idx - k * T;
                         const float4 mu = cand_row(mus, t * N + k, c);
@@ -474,7 +480,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                         float* o = prm.out.obj + ev * MTB_NUM_OBJECTIVES;
                         o[0] = o_goal; o[1] = o_acc; o[2] = o_vel; o[3] = o_pos; o[4] = o_prob;
                     }
-                    if (prm.out.obj_raw != nullptr) {
+                    if (!LEAN && prm.out.obj_raw != nullptr) {
                         float* o = prm.out.obj_raw + ev * MTB_NUM_OBJECTIVES;
                         o[0] = raw_goal; o[1] = raw_acc; o[2] = raw_vel; o[3] = raw_pos; o[4] = raw_prob;
                     }
@@ -487,20 +493,20 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                         const float vd = (fabsf(vio.d) < eps) ? 0.f : vio.d;
                         prm.out.violation[ev] = ((va + vb) + vc) + vd;
                     }
-                    if (prm.out.stats != nullptr && ((want_interact &&
+                    if (!LEAN && prm.out.stats != nullptr && ((want_interact &&
                         (raw_acc > prm.md.max_acc || raw_vel > prm.md.max_vel || raw_pos > prm.md.max_pos)) || (want_prob && cprob == 0.f)))
                         atomicAdd(prm.out.stats + 2, 1ull);
                 }
             }
             // optional rollout outputs
-            if (pair_valid && prm.out.mus != nullptr) {
+            if (!LEAN && pair_valid && prm.out.mus != nullptr) {
                 float4* mo = reinterpret_cast<float4*>(prm.out.mus + ev * (size_t)N * T * 4);
                 for (int idx = g; idx < TN; idx += GP) {
                     const int k = idx / T, t = idx - k * T;
                     mo[idx] = cand_row(mus, t * N + k, c);
                 }
             }
-            if (pair_valid && prm.out.ego_traj != nullptr) {
+            if (!LEAN && pair_valid && prm.out.ego_traj != nullptr) {
                 float4* eo = reinterpret_cast<float4*>(prm.out.ego_traj + ev * (size_t)(T + 1) * 4);
                 for (int t = g; t <= T; t += GP) eo[t] = cand_row(ego, t, c);
             }
@@ -509,8 +515,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
 
         // ================================================================== backward (adjoint) pass
         if (GRAD) {
-            const float* seed_mus_ev = (prm.md.seed_mus != nullptr) ? prm.md.seed_mus + ev0 * (size_t)N * T * 4 : nullptr;       // [2][N][T][4]
-            const float* seed_sig_ev = (prm.md.seed_sigmas != nullptr) ? prm.md.seed_sigmas + ev0 * (size_t)N * T * 2 : nullptr;
+            const float* seed_mus_ev = (!LEAN && prm.md.seed_mus != nullptr) ? prm.md.seed_mus + ev0 * (size_t)N * T * 4 : nullptr;       // [2][N][T][4]
+            const float* seed_sig_ev = (!LEAN && prm.md.seed_sigmas != nullptr) ? prm.md.seed_sigmas + ev0 * (size_t)N * T * 2 : nullptr;
             const bool seeded = seed_mus_ev != nullptr || seed_sig_ev != nullptr;
             const bool prob_a = keep_var && misc[kCoefProb] != 0.f, prob_b = keep_var && misc[kMiscFloats + kCoefProb] != 0.f;
             const bool adj_a = prm.want_env_adjoint != 0 && (misc[kNeedAdjoint] != 0.f || seeded);
@@ -531,7 +537,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                 float2* var_c = varbuf + c * TN;
                 const float* seed_c = seed_mus_ev != nullptr ? seed_mus_ev + (size_t)c * TN * 4 : nullptr;
                 const bool prob_seed = c ? prob_b : prob_a;
-                const bool acc_only = seed_c == nullptr && misc_c[kCoefVel] == 0.f && misc_c[kCoefPos] == 0.f &&
+                const bool acc_only = LEAN || seed_c == nullptr && misc_c[kCoefVel] == 0.f && misc_c[kCoefPos] == 0.f &&
                                       misc_c[kCoefProb] == 0.f && wo_scene != nullptr && prm.md.w_acc != 0.f;
                 if (acc_only) {
                     const float cacc = misc_c[kCoefAcc];
@@ -609,8 +615,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     if (var_seed) {
                         // var[m,t+1] = sum_i (q_i - mean q)^2 / (P-1): d var / d v'_i = 2 w_i (q_i - mean) / (P-1)   (particle.py:175)
                         W2 vel = feasible2(ut, u_ped);
-                        if (prm.pb.noise != nullptr) {
-                            const float* nz = prm.pb.noise + ((((size_t)s * (T - 1) + t) * N + m) * P + i) * 2;
+                        if (noise != nullptr) {
+                            const float* nz = noise + ((((size_t)s * (T - 1) + t) * N + m) * P + i) * 2;
                             const P2 pn = splat(prm.pb.particle_noise);
                             vel.x = fma2(splat(__ldg(nz)), pn, vel.x);
                             vel.y = fma2(splat(__ldg(nz + 1)), pn, vel.y);
@@ -782,7 +788,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     go[idx] = ctl[c * CT + idx - c * 2 * T];
                 }
             }
-            if (pair_valid && prm.out.grad_traj != nullptr) {     // gradient w.r.t. the ego trajectory rows (raw, see evaluate_kernel)
+            if (!LEAN && pair_valid && prm.out.grad_traj != nullptr) {     // gradient w.r.t. the ego trajectory rows (raw, see evaluate_kernel)
 #pragma unroll 1
                 for (int c = 0; c < 2; ++c) {
                     float4* gt = reinterpret_cast<float4*>(prm.out.grad_traj + (ev0 + c) * (size_t)(T + 1) * 4);
@@ -802,7 +808,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
         group_sync(GP, e);
     }
 
-    if (prm.out.stats != nullptr) {
+    if (!LEAN && prm.out.stats != nullptr) {
         atomicAdd(prm.out.stats + 0, (unsigned long long)n_pairs);
         atomicAdd(prm.out.stats + 1, (unsigned long long)n_ego);
     }

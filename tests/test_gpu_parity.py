@@ -323,6 +323,11 @@ def test_batched_vs_oracle_pair_kernel(eng, eng_dev, monkeypatch, env_kind, ego_
     kc.check_batched_vs_oracle((eng_dev if env_kind == "pf" else eng).lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, weights)
 
 
+@pytest.mark.parametrize("s,c,n,p,t_hor", [(64, 256, 20, 3, 12), (5, 38, 4, 3, 10), (3, 6, 40, 2, 6), (8, 4, 3, 5, 40)])
+def test_lean_vs_general_pair_kernel(eng, s, c, n, p, t_hor):
+    kc.check_lean_vs_general(eng.lib, DEV, s, c, n, p, t_hor)
+
+
 def test_rejects_cpu_tensors(eng):
     scene = scenarios.synthetic_scenes(1, 3, 2)
     with pytest.raises(RuntimeError):

@@ -83,6 +83,11 @@ def test_pair_kernel_vs_single_kernel(emul_lib, monkeypatch, env_kind, ego_kind,
     kc.check_pair_vs_single(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, weights, **kw)
 
 
+@pytest.mark.parametrize("s,c,n,p,t_hor", [(2, 4, 4, 3, 6), (1, 2, 12, 3, 5), (3, 2, 2, 2, 9)])
+def test_lean_vs_general_pair_kernel(emul_lib, s, c, n, p, t_hor):
+    kc.check_lean_vs_general(emul_lib, "cpu", s, c, n, p, t_hor)
+
+
 @pytest.mark.parametrize("name", gio.case_names())
 def test_jacobian_golden(emul_lib, name):
     kc.check_jacobian_golden(emul_lib, "cpu", name)
