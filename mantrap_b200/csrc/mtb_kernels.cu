@@ -1140,7 +1140,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     {
         // LEAN instantiation of the pair kernel: nothing but controls -> (goal, acc) objectives, control / speed rows, gradient
         const bool lean = EV == 2 && pb->env_kind == MTB_ENV_SOCIAL_FORCES && pb->noise == nullptr && pb->ego_traj == nullptr &&
-                          prm.keep_var == 0 && prm.rows_mind == 0 && prm.rows_ell == 0 &&
+                          prm.keep_var == 0 && prm.rows_mind == 0 && prm.rows_ell == 0 && prm.MW == 1 &&
                           (md == nullptr || (md->w_vel == 0.f && md->w_pos == 0.f && md->w_prob == 0.f && md->ado_mask == nullptr &&
                                              md->seed_mus == nullptr && md->seed_sigmas == nullptr)) &&
                           (out == nullptr || (out->obj_raw == nullptr && out->grad_traj == nullptr && out->ego_traj == nullptr &&

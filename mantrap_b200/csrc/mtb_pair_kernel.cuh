@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
     MTB_SHARED_FLOAT4(smem4);
     float* smem = reinterpret_cast<float*>(smem4);
 
-    const int T = prm.T, N = prm.N, P = prm.P, G = prm.G, GP = prm.GP, MW = prm.MW;
+    const int T = prm.T, N = prm.N, P = prm.P, G = prm.G, GP = prm.GP;
+    const int MW = LEAN ? 1 : prm.MW;                             // (the lean instantiation is launched for N <= 32 only: one mask word)
     const int tid = threadIdx.x;
     const int e = tid / GP;                                       // group within the block (one PAIR of evaluations)
     const int g = tid - e * GP;
@@ -224,11 +225,15 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
         group_sync(GP, e);
 
         // ================================================================== forward rollout
-        for (int t = 0; t < T - 1; ++t) {
-            const float4* mus_t = mus + 2 * t * N;
+        const float4* mus_t = mus;                                // running row pointers of the forward sweep
+        const float4* ego_ft = ego;
+        float4* tp_f = tape;
+        uint2* mp_f = maskbuf;
+        for (int t = 0; t < T - 1; ++t, mus_t += 2 * N, ego_ft += 2, tp_f += 2 * tape_stride, mp_f += mask_stride) {
             if (active) {
                 W2 u;
-                const PackedRow eg = ld_row(ego, t);
+                PackedRow eg;
+                eg.A = ego_ft[0]; eg.B = ego_ft[1];
                 if (ENV == MTB_ENV_SOCIAL_FORCES) {
                     const W2 fgoal = goal_force2(p, v, goal, inv_tau, prm.pb.sf_goal_radius);
                     W2 frep = wzero();
@@ -243,7 +248,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                             bits_b = radius_bits4(bits_b, ld4(pxa + 2 * prm.NP4 + k0), ld4(pxa + 3 * prm.NP4 + k0), p.x.b, p.y.b, prm.pair_cut2);
                         }
                         if ((m >> 5) == wd) { bits_a &= ~(1u << (m & 31)); bits_b &= ~(1u << (m & 31)); }   // never the own ado
-                        if (GRAD && prm.use_tape) maskbuf[t * mask_stride + wd] = make_uint2(bits_a, bits_b);
+                        if (GRAD && prm.use_tape) mp_f[wd] = make_uint2(bits_a, bits_b);
                         if (!LEAN) n_pairs += __popc(bits_a) + __popc(bits_b);
                         unsigned bits = bits_a | bits_b;          // the two neighbour sets are almost always identical
                         while (bits) {
@@ -268,8 +273,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     if (!LEAN) n_ego += 2;
                 }
                 if (GRAD && prm.use_tape) {
-                    tape[(2 * t) * tape_stride] = make_float4(p.x.a, p.x.b, p.y.a, p.y.b);
-                    tape[(2 * t + 1) * tape_stride] = make_float4(u.x.a, u.x.b, u.y.a, u.y.b);
+                    tp_f[0] = make_float4(p.x.a, p.x.b, p.y.a, p.y.b);
+                    tp_f[tape_stride] = make_float4(u.x.a, u.x.b, u.y.a, u.y.b);
                 }
                 const W2 up = feasible2(u, u_ped);
                 v = up;
@@ -300,7 +305,11 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                 const P2 dt2 = splat(dt);
                 const W2 cp = row_p(cur), cv = row_v(cur);
                 const W2 np = w2(fma2(cv.x, dt2, cp.x), fma2(cv.y, dt2, cp.y));
-                st_row(mus, (t + 1) * N + m, np, w2(mx, my));
+                {
+                    float4* nxt_row = const_cast<float4*>(mus_t) + 2 * (N + m);
+                    nxt_row[0] = make_float4(np.x.a, np.x.b, np.y.a, np.y.b);
+                    nxt_row[1] = make_float4(mx.a, mx.b, my.a, my.b);
+                }
                 pos[m] = np.x.a; pos[prm.NP4 + m] = np.y.a;
                 pos[2 * prm.NP4 + m] = np.x.b; pos[3 * prm.NP4 + m] = np.y.b;
                 if (sig_out != nullptr || keep_var) {
@@ -581,22 +590,32 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                 if (T >= 3) { nU = tape[(2 * (T - 3) + 1) * tape_stride]; }
             }
             const P2 dt2 = splat(dt);
-            for (int t = T - 2; t >= 0 && any_adjoint; --t) {
+            // running row pointers of the sweep (level t + 1 of the mean adjoints, tape planes and masks of step t, means and ego
+            // row of level t): decremented once per step instead of re-multiplying run-time strides at every use
+            float4* ab_t1 = abar0 + (size_t)(T - 1) * N;          // candidate a; candidate b at + TN
+            const float4* tp_t = tape + (size_t)(2 * (T - 2)) * tape_stride;
+            const uint2* mp_t = maskbuf + (size_t)(T - 2) * mask_stride;
+            const float4* mus_bt = mus + 2 * (T - 2) * N;
+            const float4* ego_bt = ego + 2 * (T - 2);
+            float4* ebt0 = egobar + (GP <= 32 ? 0 : (g >> 5)) * 2 * (T + 1) + (T - 2);     // this warp's slot of step t, candidate a
+            for (int t = T - 2; t >= 0 && any_adjoint; --t, ab_t1 -= N, tp_t -= 2 * tape_stride, mp_t -= mask_stride,
+                                                         mus_bt -= 2 * N, ego_bt -= 2, --ebt0) {
                 group_sync(GP, e);                                // level t+1 adjoints complete
                 W2 eb_p = wzero(), eb_v = wzero();                // this particle's share of the ego adjoint at t
                 if (active && adj_group) {
                     // issue the L2 loads of this step first ...
-                    const float4 ta = adj_a ? mtb_ldcg_f4(abar0 + (t + 1) * N + m) : zero4;
-                    const float4 tb = adj_b ? mtb_ldcg_f4(abar0 + TN + (t + 1) * N + m) : zero4;
-                    if (t >= 1) nP = tape[(2 * (t - 1)) * tape_stride];
-                    if (t >= 2) nnU = tape[(2 * (t - 2) + 1) * tape_stride];
+                    const float4 ta = adj_a ? mtb_ldcg_f4(ab_t1 + m) : zero4;
+                    const float4 tb = adj_b ? mtb_ldcg_f4(ab_t1 + TN + m) : zero4;
+                    if (t >= 1) nP = *(tp_t - 2 * tape_stride);
+                    if (t >= 2) nnU = *(tp_t - 3 * tape_stride);
                     const uint2 mk0 = mk_next;
-                    if (ENV == MTB_ENV_SOCIAL_FORCES && t >= 1) mk_next = maskbuf[(t - 1) * mask_stride];
+                    if (ENV == MTB_ENV_SOCIAL_FORCES && t >= 1) mk_next = *(mp_t - mask_stride);
                     // ... and hide their latency behind the part of the step that needs no adjoint: the forward re-evaluation of the ego pair
                     const W2 pt = w2(p2(cP.x, cP.y), p2(cP.z, cP.w)), ut = w2(p2(cU.x, cU.y), p2(cU.z, cU.w));
                     W2 vt = w2(splat(v_init.x), splat(v_init.y));
                     if (t > 0) vt = feasible2(w2(p2(nU.x, nU.y), p2(nU.z, nU.w)), u_ped);
-                    const PackedRow eg = ld_row(ego, t);
+                    PackedRow eg;
+                    eg.A = ego_bt[0]; eg.B = ego_bt[1];
                     const W2 r_e = pt - row_p(eg), w_e = vt - row_v(eg);
                     Repulsion2 o_e;
                     if (ENV == MTB_ENV_SOCIAL_FORCES) o_e = repulsion_forward2(r_e, w_e, pv0, inv_sig, dt, u_ped);
@@ -606,8 +625,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     const W2 totp = w2(p2(ta.x, tb.x), p2(ta.y, tb.y));
                     const W2 totv = w2(p2(ta.z, tb.z), p2(ta.w, tb.w));
                     if (i == 0 && t >= 1) {
-                        if (adj_a) mtb_red_add_f4(abar0 + t * N + m, ta.x, ta.y, dt * ta.x, dt * ta.y);
-                        if (adj_b) mtb_red_add_f4(abar0 + TN + t * N + m, tb.x, tb.y, dt * tb.x, dt * tb.y);
+                        if (adj_a) mtb_red_add_f4(ab_t1 - N + m, ta.x, ta.y, dt * ta.x, dt * ta.y);
+                        if (adj_b) mtb_red_add_f4(ab_t1 - N + TN + m, tb.x, tb.y, dt * tb.x, dt * tb.y);
                     }
                     const P2 wop = splat(w_over_p);
                     vbar.x = fma2(totv.x, wop, vbar.x);
@@ -640,7 +659,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     W2 pb = pbar;                                 // p carries through p' = p + dt u'
                     W2 vb = wzero();
                     if (ENV == MTB_ENV_SOCIAL_FORCES) {
-                        const float4* mus_t = mus + 2 * t * N;
+                        const float4* mus_t = mus_bt;
                         goal_force_adjoint2(pt, vt, goal, inv_tau, prm.pb.sf_goal_radius, ubar, pb, vb);
                         const W2 fbar = wneg(ubar);               // u = f_goal - sum F_k - F_ego
                         {
@@ -650,7 +669,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                             eb_p = eb_p - rb; eb_v = eb_v - wb;
                         }
                         for (int wd = 0; wd < MW; ++wd) {
-                            const uint2 mk = wd == 0 ? mk0 : maskbuf[t * mask_stride + wd];
+                            const uint2 mk = wd == 0 ? mk0 : mp_t[wd];
                             unsigned bits = mk.x | mk.y;
                             while (bits) {
                                 const int kb = __ffs((int)bits) - 1;
@@ -668,8 +687,8 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                                 pb = pb + rb; vb = vb + wb;
                                 // mus[:, 0] are constants; adjoint of ado k's mean at level t
                                 if (t >= 1) {
-                                    if (va) mtb_red_add_f4(abar0 + t * N + k, -rb.x.a, -rb.y.a, -wb.x.a, -wb.y.a);
-                                    if (vb_) mtb_red_add_f4(abar0 + TN + t * N + k, -rb.x.b, -rb.y.b, -wb.x.b, -wb.y.b);
+                                    if (va) mtb_red_add_f4(ab_t1 - N + k, -rb.x.a, -rb.y.a, -wb.x.a, -wb.y.a);
+                                    if (vb_) mtb_red_add_f4(ab_t1 - N + TN + k, -rb.x.b, -rb.y.b, -wb.x.b, -wb.y.b);
                                 }
                             }
                         }
@@ -692,7 +711,7 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
                     const int l = g & (W - 1);
                     for (int c = 0; c < 2; ++c) {
                         float ex = lane_of(eb_p.x, c), ey = lane_of(eb_p.y, c), fx = lane_of(eb_v.x, c), fy = lane_of(eb_v.y, c);
-                        float* ebt = reinterpret_cast<float*>(egobar + ((GP <= 32 ? 0 : (g >> 5)) * 2 + c) * (T + 1) + t);
+                        float* ebt = reinterpret_cast<float*>(ebt0 + c * (T + 1));
                         if (W >= 4) {
                             const float r = transpose_reduce4(ex, ey, fx, fy, W);
                             if ((l & ((W >> 2) - 1)) == 0) ebt[((l & (W >> 1)) ? 2 : 0) + ((l & (W >> 2)) ? 1 : 0)] = r;
