@@ -941,7 +941,12 @@ struct Variant {
 };
 static Variant pick_variant(int block, int blocks_by_smem, int evals_per_thread) {
     if (block > kDefaultBlock) return {kMaxThreads, 1};
-    if (evals_per_thread == 2) return {kDefaultBlock, 2};     // pair kernel: 128 registers, two blocks of <= 256 threads
+    if (evals_per_thread == 2) {                              // pair kernel: 128 registers, two blocks of <= 256 threads
+#ifdef MTB_DEV_KNOBS
+        if (env_flag("MTB_MINB") == 3 && block <= 192) return {192, 3};
+#endif
+        return {kDefaultBlock, 2};
+    }
     const int force = env_flag("MTB_MINB");
     if (force == 4) return {kDefaultBlock, 4};
     if (force == 3 || (force == 0 && blocks_by_smem >= 3)) return {kDefaultBlock, 3};
@@ -1028,16 +1033,17 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
         return (size_t)(prm.red_f + E * prm.per_eval_f) * sizeof(float);
     };
 
-    int target_block = kDefaultBlock;
-    {
-        const int knob = env_flag("MTB_BLOCK");             // development knob: 64 / 128 / 256 threads per block
-        if (knob == 64 || knob == 128 || knob == 256) target_block = knob;
-    }
+    // pair kernel with groups of >= 64 threads: blocks of 128 threads (two groups on the config-4 shape), four resident per SM at
+    // 128 registers -- the same 16 warps as two blocks of 256, finer-grained scheduling (measured 7.18 vs 7.29 ms per 262144
+    // evaluations); warp-sized and sub-warp groups keep 256 (T = 50, N = 8, P = 4 lost 6 % with 128)
+    const int block_knob = env_flag("MTB_BLOCK");           // development knob: 64 / 128 / 192 / 256 threads per block
     int E = 1;
     bool tape_in_smem = true;
     size_t smem = 0;
     // (E, tape placement, shared-memory bytes) for the current placement of the means; returns an error code
     auto choose = [&]() -> int {
+        int target_block = (EV == 2 && prm.GP >= 64) ? 128 : kDefaultBlock;
+        if (block_knob == 64 || block_knob == 128 || block_knob == 192 || block_knob == 256) target_block = block_knob;
         E = (prm.GP >= target_block) ? 1 : target_block / prm.GP;
         const long long total_evals = (long long)pb->num_scenes * pb->num_candidates / EV;     // work items of one group each
         if ((long long)E > total_evals) E = (int)total_evals;
@@ -1253,6 +1259,9 @@ static const InstOps* select_variant(Variant v) {
 
 template <int ENV, bool GRAD>
 static const InstOps* select_pair_variant(Variant v, bool lean) {
+#ifdef MTB_DEV_KNOBS
+    if (lean && v.maxt == 192) return Inst<ENV, GRAD, 192, 3, 3>::ops();
+#endif
     if (lean) return Inst<ENV, GRAD, kDefaultBlock, 2, 3>::ops();
     return Inst<ENV, GRAD, kDefaultBlock, 2, 2>::ops();
 }
