@@ -156,7 +156,8 @@ const char* mtb_error_string(int code);
 /* number of constraint rows R for the enabled constraint modules */
 int mtb_num_constraint_rows(const mtb_problem* problem, const mtb_modules* modules);
 
-/* bytes of device scratch mtb_evaluate needs (0 when everything fits in shared memory) */
+/* bytes of device scratch mtb_evaluate needs (adjoint rows, tape, masks when they do not fit in shared memory + 16 bytes for
+ * the ticket counter of the dynamic work distribution: always > 0) */
 size_t mtb_workspace_bytes(const mtb_problem* problem, int want_grad);
 
 /* forward rollout (+ objectives, constraints) and, when out->grad != NULL, the adjoint pass in the same kernel */

@@ -49,10 +49,11 @@ struct KParams {
     float4* mus_global;              // [grid][E][T][N]
     float2* dir_global;              // [grid][E][T-1][N]
     size_t ws_mus_bytes, ws_dir_bytes;
+    unsigned* work_counter;          // ticket counter of the dynamic work distribution (last 16 bytes of the workspace, zeroed per launch)
 };
 
 // misc slots (per evaluation)
-enum { kCoefAcc = 0, kCoefVel = 1, kCoefPos = 2, kNeedAdjoint = 3, kCoefProb = 4, kMiscFloats = 8 };
+enum { kCoefAcc = 0, kCoefVel = 1, kCoefPos = 2, kNeedAdjoint = 3, kCoefProb = 4, kTicket = 7, kMiscFloats = 8 };
 
 struct Red4 {
     float a, b, c, d;
@@ -63,6 +64,25 @@ struct Red4 {
 MTB_DEV void group_sync(int GP, int e) {
     if (GP <= 32) __syncwarp();
     else mtb_bar_sync(e, GP);
+}
+
+// Dynamic work distribution: a unit (one warp of sub-warp groups, or one group of >= 64 threads) takes its next work item from
+// a global ticket counter. Evaluations differ in cost by a factor of two and more (executed pair terms per scene, saturated
+// objectives skip the reverse sweep), so a static round-robin over a persistent grid leaves the units that drew the expensive
+// items as a tail (max over ~1200 units of a sum of ~100 item costs: +9 % on the config-4 shape); with tickets the tail is
+// one item. `slot` is the group's shared-memory word for the broadcast (groups of >= 64 threads); the last group barrier of
+// the previous item orders its reuse.
+// The ticket is TAKEN (by the unit's leader thread) at the start of the previous item and PUBLISHED to the unit at its end, so
+// the round trip of the L2 atomic (~1 us, a tenth of a small item) overlaps the item's work.
+MTB_DEV unsigned take_ticket(unsigned* counter, int GP, int g) {
+    const bool leader = (GP <= 32) ? ((threadIdx.x & 31) == 0) : (g == 0);
+    return leader ? atomicAdd(counter, 1u) : 0u;
+}
+MTB_DEV long long publish_ticket(unsigned ticket, int GP, int e, int g, float* slot) {
+    if (GP <= 32) return (long long)__shfl_sync(0xffffffffu, ticket, 0);
+    if (g == 0) *reinterpret_cast<unsigned*>(slot) = ticket;
+    group_sync(GP, e);
+    return (long long)*reinterpret_cast<const unsigned*>(slot);
 }
 
 // Sum over the GP threads of a group; result valid in every thread of the group. Must be reached by all threads of
@@ -261,8 +281,14 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm)
     const int evals_per_unit = (GP <= 32) ? (32 / GP) : 1;
     const int e_in_unit = (GP <= 32) ? ((tid & 31) / GP) : 0;
 
-    for (long long item = (long long)blockIdx.x * units_per_block + unit; item < prm.num_items;
-         item += (long long)gridDim.x * units_per_block) {
+    // (a launch without a ticket counter falls back to the static round-robin; measured on the config-5 sweep the tickets win on
+    // every shape, 3 - 8 % even for groups of 2 - 8 threads)
+    const bool dynamic = prm.work_counter != nullptr;
+    const unsigned item_stride = gridDim.x * units_per_block;
+    unsigned ticket = dynamic ? take_ticket(prm.work_counter, GP, g) : blockIdx.x * units_per_block + unit;
+    for (long long item = dynamic ? publish_ticket(ticket, GP, e, g, misc + kTicket) : (long long)ticket; item < prm.num_items;
+         item = dynamic ? publish_ticket(ticket, GP, e, g, misc + kTicket) : (long long)ticket) {
+        ticket = dynamic ? take_ticket(prm.work_counter, GP, g) : ticket + item_stride;   // the NEXT item: in flight during this one
         const long long ev_raw = item * evals_per_unit + e_in_unit;
         const bool eval_valid = ev_raw < prm.num_evals;
         const size_t ev = (size_t)(eval_valid ? ev_raw : prm.num_evals - 1);
@@ -1039,14 +1065,17 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     const int block_knob = env_flag("MTB_BLOCK");           // development knob: 64 / 128 / 192 / 256 threads per block
     int E = 1;
     bool tape_in_smem = true;
+    bool work_capped = false;                               // the batch holds fewer groups than one block would take
+    bool pair_small_blocks = false;                         // pair kernel: 128-thread blocks also for warp-sized / sub-warp groups
     size_t smem = 0;
     // (E, tape placement, shared-memory bytes) for the current placement of the means; returns an error code
     auto choose = [&]() -> int {
-        int target_block = (EV == 2 && prm.GP >= 64) ? 128 : kDefaultBlock;
+        int target_block = (EV == 2 && (prm.GP >= 64 || pair_small_blocks)) ? 128 : kDefaultBlock;
         if (block_knob == 64 || block_knob == 128 || block_knob == 192 || block_knob == 256) target_block = block_knob;
         E = (prm.GP >= target_block) ? 1 : target_block / prm.GP;
         const long long total_evals = (long long)pb->num_scenes * pb->num_candidates / EV;     // work items of one group each
-        if ((long long)E > total_evals) E = (int)total_evals;
+        work_capped = (long long)E > total_evals;
+        if (work_capped) E = (int)total_evals;
         // the block must be a multiple of a warp: with sub-warp groups keep E a multiple of 32 / GP
         if (prm.GP < 32) E = round_up(E, 32 / prm.GP);
         // Tape placement: shared memory when that still leaves >= 3 resident blocks per SM (registers cap the kernel at
@@ -1103,8 +1132,24 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
                 means_in_smem = true; E = e_keep; tape_in_smem = t_keep; smem = layout(E, tape_in_smem); (void)s_keep; err2 = 0;
             }
         }
-        // the pair kernel keeps the means of both candidates in shared memory: shapes that need the L2 placement run evaluate_kernel
-        if (EV == 2 && (err2 != 0 || knob == 1 || ((size_t)lim.smem_per_sm < 2 * (smem + 1024) && E * prm.GP >= 128))) {
+        // The pair kernel keeps the means of both candidates in shared memory and is capped at 512 resident threads per SM by its
+        // 128 registers. Shapes whose shared-memory layout leaves fewer than 384 of them resident (long horizons x many ados, or
+        // long horizons with tiny groups) run evaluate_kernel, which holds up to 768 threads and can move the means to the L2 scratch.
+        auto pair_residency = [&]() -> int {
+            int b = (int)((size_t)lim.smem_per_sm / (smem + 1024));
+            const int r = (b < 1 ? 1 : b) * E * prm.GP;
+            return r > 512 ? 512 : r;
+        };
+        int pair_resident = (EV == 2 && err2 == 0) ? pair_residency() : 0;
+        if (EV == 2 && knob != 1 && !work_capped && pair_resident < 384 && prm.GP < 64) {   // (first try smaller blocks)
+            // many small groups per 256-thread block: halve the block (half the shared memory per block, more resident blocks)
+            pair_small_blocks = true;
+            const int err_small = choose();
+            const int res_small = err_small == 0 ? pair_residency() : 0;
+            if (res_small > pair_resident) { err2 = err_small; pair_resident = res_small; }
+            else { pair_small_blocks = false; err2 = choose(); }
+        }
+        if (EV == 2 && (err2 != 0 || knob == 1 || (!work_capped && pair_resident < 384))) {
             EV = prm.EV = 1;
             means_in_smem = true;
             err2 = choose();
@@ -1167,7 +1212,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     }
     prm.ws_mus_bytes = means_in_smem ? 0 : (size_t)grid * E * EV * prm.T * prm.N * sizeof(float4);
     prm.ws_dir_bytes = (means_in_smem || !want_grad || prm.T < 2) ? 0 : round_up16((size_t)grid * E * EV * (prm.T - 1) * prm.N * sizeof(float2));
-    workspace_bytes = prm.ws_abar_bytes + prm.ws_tape_bytes + prm.ws_mask_bytes + prm.ws_mus_bytes + prm.ws_dir_bytes;
+    workspace_bytes = prm.ws_abar_bytes + prm.ws_tape_bytes + prm.ws_mask_bytes + prm.ws_mus_bytes + prm.ws_dir_bytes + 16;   // + ticket counter
     info.grid = grid;
     info.block = block;
     info.evals_per_block = E;
@@ -1360,8 +1405,17 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
             prm.mus_global = reinterpret_cast<float4*>(mb);
             prm.dir_global = reinterpret_cast<float2*>(mb + prm.ws_mus_bytes);
         }
+        prm.work_counter = reinterpret_cast<unsigned*>(base + ws - 16);
     }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+#ifndef MTB_HOST_EMUL
+    {
+        const cudaError_t err_ms = prm.work_counter != nullptr ? cudaMemsetAsync(prm.work_counter, 0, 16, st) : cudaSuccess;   // tickets start at 0
+        if (err_ms != cudaSuccess) return (int)err_ms;
+    }
+#else
+    if (prm.work_counter != nullptr) std::memset(prm.work_counter, 0, 16);
+#endif
     const mtb::Variant variant = {info.variant_maxt, info.variant_minb};
     return mtb::select_inst(problem->env_kind, want_grad, variant, prm.EV == 2 ? (info.kernel_kind == 2 ? 3 : 2) : 1)->launch(prm, info, st);
 }

@@ -138,8 +138,12 @@ __global__ void __launch_bounds__(MAXT, MINB) evaluate_pair_kernel(const KParams
     const int g_in_unit = (GP <= 32) ? ((tid & 31) / GP) : 0;
     const long long num_pairs = prm.num_evals >> 1;
 
-    for (long long item = (long long)blockIdx.x * units_per_block + unit; item < prm.num_items;
-         item += (long long)gridDim.x * units_per_block) {
+    const bool dynamic = prm.work_counter != nullptr;            // tickets, or the static round-robin for tiny groups (see evaluate_kernel)
+    const unsigned item_stride = gridDim.x * units_per_block;
+    unsigned ticket = dynamic ? take_ticket(prm.work_counter, GP, g) : blockIdx.x * units_per_block + unit;
+    for (long long item = dynamic ? publish_ticket(ticket, GP, e, g, misc + kTicket) : (long long)ticket; item < prm.num_items;
+         item = dynamic ? publish_ticket(ticket, GP, e, g, misc + kTicket) : (long long)ticket) {
+        ticket = dynamic ? take_ticket(prm.work_counter, GP, g) : ticket + item_stride;   // the NEXT item: in flight during this one
         const long long pair_raw = item * groups_per_unit + g_in_unit;
         const bool pair_valid = pair_raw < num_pairs;
         const size_t ev0 = 2 * (size_t)(pair_valid ? pair_raw : num_pairs - 1);      // evaluations ev0 (a) and ev0 + 1 (b)

@@ -117,6 +117,7 @@ static inline float atomicAdd(float* addr, float val) {
     }
 }
 static inline unsigned atomicOr(unsigned* addr, unsigned val) { return __atomic_fetch_or(addr, val, __ATOMIC_RELAXED); }
+static inline unsigned atomicAdd(unsigned* addr, unsigned val) { return __atomic_fetch_add(addr, val, __ATOMIC_RELAXED); }
 static inline unsigned long long atomicAdd(unsigned long long* addr, unsigned long long val) {
     return __atomic_fetch_add(addr, val, __ATOMIC_RELAXED);
 }

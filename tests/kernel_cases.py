@@ -354,10 +354,10 @@ def check_batched_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_can
 def check_pair_vs_single(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, weights, seed=0, noise=True,
                          mask=False, constraints=True, given_traj=False):
     """The two-candidates-per-thread kernel (even candidate count) against the one-evaluation-per-group kernel (the same
-    candidates evaluated one at a time, C = 1). Both spell out the same operation sequence (mtb_math.cuh / mtb_math2.cuh): on
-    the host emulation (IEEE operations, no contraction) the forward rollout is BIT-IDENTICAL; under nvcc --use_fast_math the
-    compiler contracts / rewrites the packed and the scalar expression trees differently (FMUL2 + FADD2 -> FFMA2, rcp(sqrt) ->
-    rsqrt), so on the GPU the rollouts agree to a few ulp and objectives / gradients far inside the parity tolerances."""
+    candidates evaluated one at a time, C = 1). Both follow the same operation sequence (mtb_math.cuh / mtb_math2.cuh) except for
+    how norms are formed (sqrt + rsqrt vs x * rsqrt(x)), and nvcc --use_fast_math contracts / rewrites the packed and the scalar
+    expression trees differently: the ego trajectories are bit-identical, the rollouts agree to a few ulp per step and objectives /
+    gradients far inside the parity tolerances."""
     from mantrap_b200 import scenarios
     assert num_candidates % 2 == 0
     scene = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=500 + seed, param_seed=600 + seed,
@@ -408,11 +408,14 @@ def check_pair_vs_single(lib, device, env_kind, ego_kind, num_scenes, num_candid
         f_obj = 2 * float((r32["obj"].double() - r64["obj"]).abs().max())
         f_grad = 2 * float((r32["grad"].double() - r64["grad"]).abs().max())
         f_mus = 2 * float((r32["mus"].double() - r64["mus"]).abs().max())
+        # per evaluation: dense scenes hold the odd evaluation whose float32 gradient is off by 1e-2 from its own float64 value
+        # (a force clamp or the interaction radius within an ulp): such an evaluation bounds nothing, the others are held tightly
+        g_eval = 4 * (r32["grad"].double() - r64["grad"]).abs().amax(dim=(1, 2)).numpy()
     for key in want:
         a = np.nan_to_num(np_(pair[key]))
         b = np.nan_to_num(np_(torch.cat([r[key] for r in singles], dim=1)))
         assert np.array_equal(np.isnan(np_(pair[key])), np.isnan(np_(torch.cat([r[key] for r in singles], dim=1)))), key
-        if key in ("mus", "sigmas", "ego_traj") and device == "cpu":
+        if key == "ego_traj":
             assert np.array_equal(a, b), (key, float(np.abs(a - b).max()))
             continue
         if key in ("obj", "obj_raw"):
@@ -427,6 +430,12 @@ def check_pair_vs_single(lib, device, env_kind, ego_kind, num_scenes, num_candid
             rtol = gio.RTOL_ROLLOUT          # ellipsoid rows are (distance / 0.1)^2 ~ 1e4: a few ulp of the means are 3e-6 of the largest row
         floor = {"grad": f_grad, "grad_traj": 10 * f_grad, "total": f_obj, "mus": f_mus, "sigmas": f_mus, "cons": 10 * f_mus,
                  "violation": 100 * f_mus}.get(key, 0.0)
+        if key == "grad" and device != "cpu":
+            ga, gb = a.reshape(-1, a.shape[-2] * a.shape[-1]), b.reshape(-1, a.shape[-2] * a.shape[-1])
+            err = np.abs(ga - gb).max(axis=1)
+            bound = max(rtol, 0.5 * gio.RTOL_GRAD) * np.abs(gb).max() + 2e-7 + g_eval       # half the parity tolerance + conditioning
+            assert np.all(err <= bound), (f"pair vs single: grad", float((err - bound).max()), int(np.argmax(err - bound)))
+            continue
         gio.assert_parity(a, b, rtol, f"pair vs single: {key}", atol=2e-7 + floor)
     return pair
 

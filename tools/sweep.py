@@ -45,7 +45,7 @@ def measure(eng, t_hor, n, p, evals, iters=3):
     return dict(T=t_hor, N=n, P=p, evals=s * c, ms=round(ms, 3), evals_per_s=round(s * c / ms * 1e3, 1),
                 pairs_per_eval=round(pairs, 1), saturated=round(saturated, 3), flop_per_eval=round(flop, 1),
                 executed_tflops=round(s * c / ms * 1e3 * flop / 1e12, 3), block=info["block"], group=info["group_size"],
-                blocks_per_sm=info["blocks_per_sm"], tape_in_smem=info["tape_in_smem"])
+                blocks_per_sm=info["blocks_per_sm"], tape_in_smem=info["tape_in_smem"], kernel_kind=info["kernel_kind"])
 
 
 if __name__ == "__main__":
@@ -53,8 +53,14 @@ if __name__ == "__main__":
     ap.add_argument("--evals", type=int, default=1 << 20)
     ap.add_argument("--out", default="gpurun_out/sweep.csv")
     ap.add_argument("--quick", action="store_true", help="corner points only")
+    ap.add_argument("--dev", action="store_true", help="use the -DMTB_DEV_KNOBS library (launch-plan overrides from the environment)")
     args = ap.parse_args()
-    eng = engine.Engine("cuda:0")
+    if args.dev:
+        import ctypes
+        from mantrap_b200 import _cabi, build
+        eng = engine.Engine.from_library(_cabi.bind(ctypes.CDLL(build.build(dev_knobs=True))), "cuda:0")
+    else:
+        eng = engine.Engine("cuda:0")
     ts, ns, ps = (10, 20, 30, 40, 50), (2, 4, 8, 16, 32, 64), (1, 2, 4, 8)
     if args.quick:
         ts, ns, ps = (10, 50), (2, 64), (2, 8)
