@@ -37,11 +37,13 @@ MTB_DEV V2 operator-(V2 a, V2 b) { return v2(a.x - b.x, a.y - b.y); }
 MTB_DEV V2 operator*(float s, V2 a) { return v2(s * a.x, s * a.y); }
 MTB_DEV void axpy(V2& y, float a, V2 x) { y.x = fmaf(a, x.x, y.x); y.y = fmaf(a, x.y, y.y); }
 #endif
-// The scalar step models below follow the operation sequence of their two-candidate versions in mtb_math2.cuh except for the norms
-// (see repulsion_forward). Under nvcc --use_fast_math the compiler contracts and rewrites the scalar and the packed expression
-// trees independently (FMUL + FADD -> FFMA, rcp(sqrt) -> rsqrt), so evaluate_kernel / jacobian_kernel (scalar, bit-identical to
-// each other) and evaluate_pair_kernel agree to a few ulp per step, which the tests bound; pinning the scalar operations with
-// __fmul_rn / __fadd_rn did not make them identical and cost the scalar kernels 3 - 7 %, so the compiler is left free here.
+// The scalar step models below spell out the SAME operation sequence as their two-candidate versions in mtb_math2.cuh. On the
+// host emulation (IEEE operations, -ffp-contract=off) evaluate_kernel, jacobian_kernel and evaluate_pair_kernel therefore produce
+// bit-identical forward rollouts, which the CPU tests assert (a sharded search returns the same bits whichever kernel a shard
+// runs). Under nvcc --use_fast_math the compiler contracts and rewrites the scalar and the packed expression trees independently
+// (FMUL + FADD -> FFMA, rcp(sqrt) -> rsqrt), so on the GPU evaluate_kernel / jacobian_kernel (bit-identical to each other) and
+// evaluate_pair_kernel agree to a few ulp per step, which the tests bound; pinning the scalar operations with __fmul_rn /
+// __fadd_rn did not make them identical and cost the scalar kernels a few percent, so the compiler is left free here.
 MTB_DEV float fm(float a, float b) { return a * b; }
 MTB_DEV float fa(float a, float b) { return a + b; }
 MTB_DEV float ff(float a, float b, float c) { return fmaf(a, b, c); }
@@ -72,16 +74,16 @@ MTB_DEV RepulsionFwd repulsion_forward(V2 r, V2 w, float v0, float sigma, float 
     o.inv_sigma = 1.0f / sigma;
     const V2 s = v2(ff(-dt, w.x, r.x), ff(-dt, w.y, r.y));
     const float n1sq = dot(r, r), n2sq = dot(s, s), n3sq = dot(w, w);
-    // Norms and their reciprocals as two INDEPENDENT MUFU operations (sqrt, rsqrt) here: the scalar kernels are bound by issue
-    // slots, not by the MUFU pipe, and x * rsqrt(x) costs them one more FMUL per norm (measured 2 - 7 % on the config-5 sweep). The
-    // two-candidate kernel (mtb_math2.cuh) makes the opposite trade: one packed FMUL2 serves both candidates, a MUFU only one.
-    o.inv_n1 = rsqrtf(n1sq);                   // |r| = 0: rsqrt = inf -> t1 = inf * 0 = NaN -> NaN force -> dead, like 0/0 in t1 = r / |r|
+    // Four MUFU operations per pair term: rsqrt |r|^2, rsqrt |s|^2, rsqrt B (norms as x * rsqrt(x)) and one ex2 -- the same
+    // sequence as the two-candidate version. (sqrt + rsqrt as two independent MUFU operations instead of rsqrt + FMUL was
+    // measured on the config-5 sweep: no gain for the scalar kernels, and it would cost the bit-identity on the host emulation.)
+    o.inv_n1 = rsqrtf(n1sq);                   // |r| = 0: rsqrt = inf, n1 = 0 * inf = NaN -> NaN force -> dead, like 0/0 in t1 = r / |r|
     o.inv_n2 = rsqrtf(n2sq);
-    const float n1 = sqrtf(n1sq), n2 = sqrtf(n2sq);
+    const float n1 = fm(n1sq, o.inv_n1), n2 = fm(n2sq, o.inv_n2);
     o.a = fa(n1, n2);
     const float big_b = ff(o.a, o.a, fm(-(dt * dt), n3sq));
-    o.inv_sb = rsqrtf(big_b);                  // b = sb / 2 with sb = sqrt(B)
-    const float sb = sqrtf(big_b);
+    o.inv_sb = rsqrtf(big_b);                  // b = sb / 2 with sb = sqrt(B) = B * rsqrt(B)
+    const float sb = fm(big_b, o.inv_sb);
     o.pot = fm(v0, exp2f(fm(-0.5f * 1.4426950408889634f * o.inv_sigma, sb)));   // V = v0 exp(-sb / (2 sigma))
     // k = dV/dn1 = dV/dn2 = -(V / sigma) * (n1 + n2) / (4 b)
     o.k = fm(-fm(o.inv_sigma, o.pot), fm(fm(0.5f, o.a), o.inv_sb));

@@ -354,10 +354,10 @@ def check_batched_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_can
 def check_pair_vs_single(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, weights, seed=0, noise=True,
                          mask=False, constraints=True, given_traj=False):
     """The two-candidates-per-thread kernel (even candidate count) against the one-evaluation-per-group kernel (the same
-    candidates evaluated one at a time, C = 1). Both follow the same operation sequence (mtb_math.cuh / mtb_math2.cuh) except for
-    how norms are formed (sqrt + rsqrt vs x * rsqrt(x)), and nvcc --use_fast_math contracts / rewrites the packed and the scalar
-    expression trees differently: the ego trajectories are bit-identical, the rollouts agree to a few ulp per step and objectives /
-    gradients far inside the parity tolerances."""
+    candidates evaluated one at a time, C = 1). Both spell out the same operation sequence (mtb_math.cuh / mtb_math2.cuh): on
+    the host emulation (IEEE operations, no contraction) the forward rollout is BIT-IDENTICAL; under nvcc --use_fast_math the
+    compiler contracts / rewrites the packed and the scalar expression trees differently (FMUL2 + FADD2 -> FFMA2, rcp(sqrt) ->
+    rsqrt), so on the GPU the rollouts agree to a few ulp and objectives / gradients far inside the parity tolerances."""
     from mantrap_b200 import scenarios
     assert num_candidates % 2 == 0
     scene = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=500 + seed, param_seed=600 + seed,
@@ -415,7 +415,7 @@ def check_pair_vs_single(lib, device, env_kind, ego_kind, num_scenes, num_candid
         a = np.nan_to_num(np_(pair[key]))
         b = np.nan_to_num(np_(torch.cat([r[key] for r in singles], dim=1)))
         assert np.array_equal(np.isnan(np_(pair[key])), np.isnan(np_(torch.cat([r[key] for r in singles], dim=1)))), key
-        if key == "ego_traj":
+        if key == "ego_traj" or (key in ("mus", "sigmas") and device == "cpu"):
             assert np.array_equal(a, b), (key, float(np.abs(a - b).max()))
             continue
         if key in ("obj", "obj_raw"):
