@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define MTB_ABI_VERSION 6
+#define MTB_ABI_VERSION 7
 
 /* environment kinds: mantrap/environment/social_forces.py, simplified/potential_field.py, simplified/kalman.py */
 #define MTB_ENV_SOCIAL_FORCES 0
@@ -54,6 +54,7 @@ extern "C" {
 #define MTB_ERR_BAD_ARGUMENT (-1)
 #define MTB_ERR_TOO_LARGE (-2)
 #define MTB_ERR_WORKSPACE (-3)
+#define MTB_ERR_STATIC_SCRATCH (-4) /* mtb_evaluate_static: the problem needs more than MTB_STATIC_SCRATCH_BYTES of scratch */
 
 /* Scene batch + candidate controls. All pointers are device pointers. */
 typedef struct mtb_problem {
@@ -163,6 +164,20 @@ size_t mtb_workspace_bytes(const mtb_problem* problem, int want_grad);
 /* forward rollout (+ objectives, constraints) and, when out->grad != NULL, the adjoint pass in the same kernel */
 int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const mtb_outputs* out,
                  void* workspace, size_t workspace_bytes, void* stream);
+
+/* mtb_evaluate for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). No counterpart in the reference. Same inputs, outputs,
+ * kernels and results as mtb_evaluate; the scratch (adjoint rows, tape, masks, means, ticket counter) is a file-scope
+ * `static __device__` array of MTB_STATIC_SCRATCH_BYTES inside the library instead of a caller workspace. Every GPU that loads
+ * the library holds that array until the process exits. The call allocates nothing (no cudaMalloc / cudaFree / allocating library
+ * routine); its first use on a device resolves the array's device address (cudaGetSymbolAddress, once per device, with that
+ * device current). A problem whose mtb_workspace_bytes exceeds MTB_STATIC_SCRATCH_BYTES is rejected with MTB_ERR_STATIC_SCRATCH
+ * and nothing is launched -- use mtb_evaluate with a workspace of your own for it.
+ * ALL calls on a device share the one array: calls that overlap on the GPU (different streams, or two host threads) race on it;
+ * issue them on one stream, or order them with events. The array keeps the previous call's contents; what must start at zero
+ * (the ticket counter) is cleared by every call on `stream` before the launch, the rest is written before it is read. */
+#define MTB_STATIC_SCRATCH_BYTES ((size_t)64 << 20)
+int mtb_evaluate_static(const mtb_problem* problem, const mtb_modules* modules, const mtb_outputs* out, void* stream);
 
 /* launch geometry mtb_evaluate would use (for benchmarks / docs) */
 int mtb_query_launch(const mtb_problem* problem, int want_grad, mtb_launch_info* info);

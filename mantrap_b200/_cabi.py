@@ -12,7 +12,9 @@ import torch
 ENV_SOCIAL_FORCES, ENV_POTENTIAL_FIELD, ENV_KALMAN = 0, 1, 2
 EGO_DOUBLE_INTEGRATOR, EGO_SINGLE_INTEGRATOR, EGO_NONE = 0, 1, 2
 MAX_ADOS, MAX_HORIZON = 64, 64
-ABI_VERSION = 6
+ABI_VERSION = 7
+STATIC_SCRATCH_BYTES = 64 << 20     # MTB_STATIC_SCRATCH_BYTES (mtb_evaluate_static)
+ERR_STATIC_SCRATCH = -4            # MTB_ERR_STATIC_SCRATCH
 ATTENTION_EUCLIDEAN, ATTENTION_CLOSEST = 0, 1
 
 _f, _i, _p = ctypes.c_float, ctypes.c_int32, ctypes.c_void_p
@@ -50,7 +52,7 @@ class MtbLaunchInfo(ctypes.Structure):
 
 
 EXPORTED_SYMBOLS = ("mtb_abi_version", "mtb_error_string", "mtb_num_constraint_rows", "mtb_workspace_bytes",
-                    "mtb_evaluate", "mtb_query_launch", "mtb_constraint_jacobian", "mtb_jacobian_workspace_bytes",
+                    "mtb_evaluate", "mtb_evaluate_static", "mtb_query_launch", "mtb_constraint_jacobian", "mtb_jacobian_workspace_bytes",
                     "mtb_argmin", "mtb_attention", "mtb_warm_start_encoding", "mtb_env_step", "mtb_probe_launch", "mtb_ego_unroll", "mtb_ego_roll", "mtb_ego_unroll_adjoint",
                     "mtb_ego_dx_du")
 
@@ -67,6 +69,8 @@ def bind(lib: ctypes.CDLL) -> ctypes.CDLL:
     lib.mtb_workspace_bytes.restype, lib.mtb_workspace_bytes.argtypes = ctypes.c_size_t, [pp, ctypes.c_int]
     lib.mtb_evaluate.restype = ctypes.c_int
     lib.mtb_evaluate.argtypes = [pp, pm, po, _p, ctypes.c_size_t, _p]
+    lib.mtb_evaluate_static.restype = ctypes.c_int
+    lib.mtb_evaluate_static.argtypes = [pp, pm, po, _p]
     lib.mtb_query_launch.restype = ctypes.c_int
     lib.mtb_query_launch.argtypes = [pp, ctypes.c_int, ctypes.POINTER(MtbLaunchInfo)]
     lib.mtb_constraint_jacobian.restype = ctypes.c_int

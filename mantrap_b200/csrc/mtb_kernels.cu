@@ -1339,6 +1339,9 @@ const char* mtb_error_string(int code) {
         case MTB_ERR_BAD_ARGUMENT: return "mantrap_b200: bad argument";
         case MTB_ERR_TOO_LARGE: return "mantrap_b200: problem exceeds the supported size (N <= 64, T <= 64, N*P <= 1024)";
         case MTB_ERR_WORKSPACE: return "mantrap_b200: workspace missing or too small";
+        case MTB_ERR_STATIC_SCRATCH:
+            return "mantrap_b200: mtb_evaluate_static: the problem needs more scratch than the static array holds "
+                   "(MTB_STATIC_SCRATCH_BYTES = 64 MiB); call mtb_evaluate with a workspace of mtb_workspace_bytes instead";
         default: break;
     }
 #ifndef MTB_HOST_EMUL
@@ -1418,6 +1421,60 @@ int mtb_evaluate(const mtb_problem* problem, const mtb_modules* modules, const m
 #endif
     const mtb::Variant variant = {info.variant_maxt, info.variant_minb};
     return mtb::select_inst(problem->env_kind, want_grad, variant, prm.EV == 2 ? (info.kernel_kind == 2 ? 3 : 2) : 1)->launch(prm, info, st);
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// mtb_evaluate without a caller workspace (no counterpart in the reference; added for
+// callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The scratch of the evaluation kernels lives in ONE file-scope device array per GPU that loads the library. In host code the
+// name `g_static_scratch` is only a stand-in for the symbol, NOT a device address: its device address is resolved once per
+// device (with that device current) with cudaGetSymbolAddress and that pointer is what the kernels get. All calls on a device
+// share the array (calls that overlap on the GPU race); it keeps the previous call's contents, so the ticket counter is
+// cleared per call (mtb_evaluate's cudaMemsetAsync on `stream`), everything else is written before it is read.
+// -------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_scratch[MTB_STATIC_SCRATCH_BYTES];
+
+namespace mtb {
+static int static_scratch_address(void** out) {
+#ifndef MTB_HOST_EMUL
+    constexpr int kMaxDevices = 64;
+    static void* address[kMaxDevices] = {};
+    int device = -1;
+    cudaError_t err = cudaGetDevice(&device);
+    if (err != cudaSuccess) return (int)err;
+    if (device < 0 || device >= kMaxDevices) return MTB_ERR_BAD_ARGUMENT;
+    std::lock_guard<std::mutex> lock(inst_mutex());
+    if (address[device] == nullptr) {
+        void* ptr = nullptr;
+        err = cudaGetSymbolAddress(&ptr, g_static_scratch);     // (set-up: once per device, with that device current)
+        if (err != cudaSuccess) return (int)err;
+        if (ptr == nullptr) return (int)cudaErrorInvalidSymbol;
+        address[device] = ptr;
+    }
+    *out = address[device];
+#else
+    *out = g_static_scratch;                                    // host emulation: "device" memory is host memory
+#endif
+    return 0;
+}
+}  // namespace mtb
+
+int mtb_evaluate_static(const mtb_problem* problem, const mtb_modules* modules, const mtb_outputs* out, void* stream) {
+    if (problem == nullptr || out == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    // the size mtb_evaluate will ask for (same plan, same arguments) -- checked against the array BEFORE anything is launched
+    {
+        const bool want_grad = out->grad != nullptr || out->grad_traj != nullptr;
+        mtb::KParams prm;
+        mtb_launch_info info;
+        size_t ws = 0;
+        const int err = mtb::plan(problem, modules, out, want_grad, prm, info, ws);
+        if (err != 0) return err;
+        if (ws > MTB_STATIC_SCRATCH_BYTES) return MTB_ERR_STATIC_SCRATCH;
+    }
+    void* scratch = nullptr;
+    const int err = mtb::static_scratch_address(&scratch);
+    if (err != 0) return err;
+    return mtb_evaluate(problem, modules, out, scratch, MTB_STATIC_SCRATCH_BYTES, stream);
 }
 
 int mtb_argmin(const float* total, const float* violation, int32_t num_scenes, int32_t num_candidates, float feas_tol,

@@ -20,6 +20,7 @@
 
 #define __global__
 #define __device__
+#define __align__(n) __attribute__((aligned(n)))
 #define __host__
 #define __forceinline__ inline
 #define __launch_bounds__(...)
