@@ -149,7 +149,7 @@ def reference_arm(args):
         "note": "reference algorithm = oracle/torch_oracle.py (the Python reference cannot travel to the GPU box; "
                 "its own per-call cost is ~0.3 evals/s/core, BASELINE.md §2)",
     }
-    print(json.dumps(line), flush=True)
+    emit_line(line)
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -441,6 +441,29 @@ def secondary_multi_gpu(eng, torch, dist, dev, rank, world):
     return out
 
 
+_JSON_FD = None
+
+
+def protect_stdout():
+    """stdout carries the ONE JSON line and nothing else: native libraries (NCCL prints its version banner with NCCL_DEBUG set,
+    whatever NCCL_DEBUG_FILE says), torch warnings and stray prints all write to file descriptor 1, so descriptor 1 is pointed
+    at stderr for the whole run and the line is written to a private duplicate of the original stdout."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -452,6 +475,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the measurements of the other BASELINE configs")
     args = ap.parse_args()
+    protect_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     if args.impl == "reference":
@@ -639,7 +663,7 @@ def main():
             line["secondary"] = multi
         if cpu_baseline is not None:
             line["cpu_baseline"] = cpu_baseline
-        print(json.dumps(line), flush=True)
+        emit_line(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

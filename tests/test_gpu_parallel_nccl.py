@@ -48,7 +48,15 @@ def _worker(rank, world, port):
         for mode in ("scenes", "candidates"):
             val, idx, best, local = parallel.sharded_search(eng, scene, controls, make_spec, 1e-3, mode=mode)
             assert torch.equal(idx, idx0), (mode, idx, idx0)
-            assert torch.equal(val, val0) and torch.equal(best, best0), mode
+            assert torch.equal(best, best0), mode
+            if mode == "scenes":
+                assert torch.equal(val, val0), mode
+            else:
+                # 19 candidates over 2 ranks = shards of 10 (even: evaluate_pair_kernel) and 9 (odd: evaluate_kernel), the whole
+                # batch (odd) runs evaluate_kernel. Under --use_fast_math the scalar and the packed expression trees are contracted
+                # differently, so on the GPU the two kernels agree to a few ulp per step (bit-identical on the host emulation,
+                # tests/test_parallel_gloo.py): same winners, values within the objective tolerance.
+                torch.testing.assert_close(val, val0, rtol=1e-5, atol=1e-6)
         # ---- sharded closed loop (5 scenes over 2 ranks), given candidates and step noise
         s, c, n, p, t_hor, steps = 5, 16, 4, 3, 6, 3
         scene = scenarios.synthetic_scenes(s, n, p, seed=31, param_seed=32, regular_sigma=True)
