@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "libmantrap_b200.so")
 # environment; two placement tests load this one through Engine.from_library
 DEV_LIB_PATH = os.path.join(HERE, "libmantrap_b200_dev.so")
 SOURCES = [os.path.join(HERE, "csrc", name) for name in ("mtb_kernels.cu", "mtb_jacobian.cu", "mtb_ego.cu", "mtb_scene.cu", "mtb_probe.cu")]
-DEPS = SOURCES + [os.path.join(HERE, "csrc", "mtb_math.cuh"), os.path.join(HERE, "csrc", "mtb_common.cuh"), os.path.join(ROOT, "include", "mantrap_b200.h")]
+DEPS = sorted(os.path.join(HERE, "csrc", name) for name in os.listdir(os.path.join(HERE, "csrc"))) + [os.path.join(ROOT, "include", "mantrap_b200.h")]
 # --use_fast_math: MUFU rsqrt / rcp / ex2 instead of the IEEE division / sqrt / expf sequences (each ~10 instructions
 # in the pair term). Parity with the reference is measured WITH this flag (tests -m gpu); NaN / inf semantics that
 # define parity (x != x tests, inf - inf) are unaffected by it.

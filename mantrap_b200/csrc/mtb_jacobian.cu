@@ -15,6 +15,10 @@
 //   ellipsoid     baselines/ellipsoid_interact.py:47-57: means and scales detached, 2 (ego_p - mu_p) / max(scale, min) d ego_p / du
 #include "mtb_common.cuh"
 #include "mtb_math.cuh"
+#include "mtb_jacobian_block.cuh"
+
+#include <map>
+#include <mutex>
 
 namespace mtb {
 
@@ -30,15 +34,6 @@ struct JParams {
     float pair_cut2;
     int off_ctl, off_ego, off_mus, off_mud, off_q, off_qd, off_var;   // float offsets into dynamic shared memory
 };
-
-// tangent of the ego state at time index t w.r.t. control j (same component): (d p, d v)   [SURVEY A.1]
-MTB_DEV float2 ego_tangent(int ego_kind, float dt, int t, int j) {
-    if (ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) {
-        const int lag = t - 1 - j;
-        return make_float2(lag > 0 ? dt * dt * (float)lag : 0.f, j < t ? dt : 0.f);
-    }
-    return make_float2(j < t ? dt : 0.f, j == t - 1 ? 1.f : 0.f);
-}
 
 template <int ENV, int D, int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB) jacobian_kernel(const JParams prm) {
@@ -442,6 +437,109 @@ static int launch_jacobian(const JParams& prm, int grid, int block, size_t smem,
     return launch_jacobian_t<ENV, 4, kMaxThreads, 1>(prm, grid, block, smem, stream);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// jacobian_block_kernel (mtb_jacobian_block.cuh): one evaluation per block, tangents in shared memory
+// ---------------------------------------------------------------------------------------------------------
+#ifdef MTB_DEV_KNOBS
+static int jac_knob() {                                     // development knob MTB_JAC: 1 = always jacobian_kernel
+    const char* v = std::getenv("MTB_JAC");
+    return (v != nullptr && v[0] != '\0') ? std::atoi(v) : 0;
+}
+#else
+static constexpr int jac_knob() { return 0; }
+#endif
+
+// 0: launch geometry filled in; 1: the shape does not fit (use jacobian_kernel); < 0: error
+static int plan_jacobian_block(const mtb_problem* pb, const mtb_modules* md, const float* jac, BParams& prm, int& block, size_t& smem) {
+    const int err = validate(pb);
+    if (err != 0) return err;
+    if (pb->ego_kind == MTB_EGO_NONE || md == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    if (jac_knob() == 1) return 1;
+    if ((reinterpret_cast<uintptr_t>(jac) & 7u) != 0) return 1;          // rows are written with 8-byte stores
+    std::memset(&prm, 0, sizeof(prm));
+    prm.pb = *pb;
+    prm.md = *md;
+    const bool kalman = pb->env_kind == MTB_ENV_KALMAN;
+    prm.T = pb->t_horizon;
+    prm.N = pb->num_ados;
+    prm.P = kalman ? 1 : pb->num_particles;
+    prm.G = prm.N * prm.P;
+    prm.MW = (prm.N + 31) / 32;
+    prm.NM1 = prm.N - 1;
+    prm.pair_cut2 = pair_cut_squared(pb->sf_interaction_radius);
+    const ConstraintRows rows = constraint_rows(pb, md);
+    prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.rows_ell = rows.ell; prm.R = rows.total;
+    if (prm.R == 0) return MTB_ERR_BAD_ARGUMENT;
+    if (prm.G > 256) return 1;
+    prm.num_evals = (long long)pb->num_scenes * pb->num_candidates;
+    const bool tangents = rows.mind > 0 && !kalman;
+    const bool pairs = tangents && pb->env_kind == MTB_ENV_SOCIAL_FORCES;
+    int off = 0;
+    prm.off_ctl = off;  off += round_up(2 * prm.T, 4);
+    prm.off_ego = off;  off += (prm.T + 1) * 4;
+    prm.off_mus = off;  off += 2 * prm.N * 4;
+    prm.off_var = off;  off += round_up(2 * prm.N * 2, 4);
+    prm.off_pw = off;   off += round_up(prm.G, 4);
+    prm.off_q = off;    off += round_up(prm.G * 2, 4);
+    prm.off_lin = off;  off += tangents ? prm.G * kLinRows * 4 : 0;
+    prm.off_nbr = off;  off += tangents ? round_up(prm.G * prm.MW, 4) : 0;
+    prm.off_pool = off; off += pairs ? prm.G * prm.NM1 * 8 : 0;
+    prm.off_tan = off;  off += tangents ? prm.G * prm.T * 8 : 0;
+    prm.off_mud = off;  off += tangents ? 2 * prm.N * prm.T * 8 : 0;
+    smem = (size_t)off * sizeof(float);
+    const DeviceLimits lim = device_limits();
+    if (smem > (size_t)lim.max_smem / 2) return 1;                       // fewer than two resident blocks per SM: not this kernel's shape
+    // threads: the particles in phase 1, (particle, live control step) items in phase 2 (G * t of them at step t), N * T row entries
+    int work = prm.G * prm.T / 2;
+    if (work < prm.G) work = prm.G;
+    if (work < 64) work = 64;
+    if (work > 256) work = 256;
+    block = round_up(work, 32);
+    return 0;
+}
+
+template <int ENV>
+static int launch_jacobian_block(const BParams& prm, int block, size_t smem, cudaStream_t stream) {
+    const DeviceLimits lim = device_limits();
+    int per_sm = (int)((size_t)lim.smem_per_sm / (smem + 1024));
+    if (per_sm > 2048 / block) per_sm = 2048 / block;
+    if (per_sm > 3 && block > 128) per_sm = 3;               // __launch_bounds__(256, 3)
+    if (per_sm < 1) per_sm = 1;
+#ifndef MTB_HOST_EMUL
+    {
+        static std::mutex mu;
+        static int smem_opt_in = 0;
+        static std::map<std::pair<int, size_t>, int> resident;
+        std::lock_guard<std::mutex> lock(mu);
+        if ((int)smem > smem_opt_in) {
+            const cudaError_t err = cudaFuncSetAttribute(jacobian_block_kernel<ENV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (err != cudaSuccess) return (int)err;
+            smem_opt_in = (int)smem;
+        }
+        const auto key = std::make_pair(block, smem);
+        const auto it = resident.find(key);
+        int n = 0;
+        if (it != resident.end()) {
+            n = it->second;
+        } else if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, jacobian_block_kernel<ENV>, block, smem) == cudaSuccess) {
+            resident[key] = n;
+        } else {
+            (void)cudaGetLastError();
+            n = 0;
+        }
+        if (n >= 1) per_sm = n;
+    }
+#endif
+    long long gl = (long long)lim.sms * per_sm;
+    if (gl > prm.num_evals) gl = prm.num_evals;
+    MTB_LAUNCH((jacobian_block_kernel<ENV>), (int)gl, block, smem, stream, prm);
+#ifndef MTB_HOST_EMUL
+    return (int)cudaGetLastError();
+#else
+    return 0;
+#endif
+}
+
 }  // namespace mtb
 
 extern "C" {
@@ -451,6 +549,24 @@ size_t mtb_jacobian_workspace_bytes(const mtb_problem*) { return 0; }   // every
 int mtb_constraint_jacobian(const mtb_problem* problem, const mtb_modules* modules, float* cons, float* jac,
                             void* /*workspace*/, size_t /*workspace_bytes*/, void* stream) {
     if (jac == nullptr) return MTB_ERR_BAD_ARGUMENT;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    {
+        // one evaluation per block with the tangents in shared memory, whenever the shape fits (mtb_jacobian_block.cuh)
+        mtb::BParams bp;
+        int bblock = 0;
+        size_t bsmem = 0;
+        const int fit = mtb::plan_jacobian_block(problem, modules, jac, bp, bblock, bsmem);
+        if (fit < 0) return fit;
+        if (fit == 0) {
+            bp.cons = cons;
+            bp.jac = jac;
+            switch (problem->env_kind) {
+                case MTB_ENV_SOCIAL_FORCES: return mtb::launch_jacobian_block<MTB_ENV_SOCIAL_FORCES>(bp, bblock, bsmem, st);
+                case MTB_ENV_POTENTIAL_FIELD: return mtb::launch_jacobian_block<MTB_ENV_POTENTIAL_FIELD>(bp, bblock, bsmem, st);
+                default: return mtb::launch_jacobian_block<MTB_ENV_KALMAN>(bp, bblock, bsmem, st);
+            }
+        }
+    }
     mtb::JParams prm;
     int grid = 0, block = 0, dirs = 0;
     size_t smem = 0;
@@ -458,7 +574,6 @@ int mtb_constraint_jacobian(const mtb_problem* problem, const mtb_modules* modul
     if (err != 0) return err;
     prm.cons = cons;
     prm.jac = jac;
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (problem->env_kind) {
         case MTB_ENV_SOCIAL_FORCES: return mtb::launch_jacobian<MTB_ENV_SOCIAL_FORCES>(prm, grid, block, smem, dirs, st);
         case MTB_ENV_POTENTIAL_FIELD: return mtb::launch_jacobian<MTB_ENV_POTENTIAL_FIELD>(prm, grid, block, smem, dirs, st);

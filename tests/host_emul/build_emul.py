@@ -6,8 +6,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 OUT = os.path.join(HERE, "libmtb_emul.so")
 SOURCES = [os.path.join(ROOT, "mantrap_b200", "csrc", f) for f in ("mtb_kernels.cu", "mtb_jacobian.cu", "mtb_ego.cu", "mtb_scene.cu")]
-DEPS = SOURCES + [os.path.join(ROOT, "mantrap_b200", "csrc", "mtb_math.cuh"), os.path.join(ROOT, "mantrap_b200", "csrc", "mtb_common.cuh"), os.path.join(HERE, "cuda_shim.h"),
-                  os.path.join(ROOT, "include", "mantrap_b200.h")]
+CSRC = os.path.join(ROOT, "mantrap_b200", "csrc")
+DEPS = sorted(os.path.join(CSRC, name) for name in os.listdir(CSRC)) + [os.path.join(HERE, "cuda_shim.h"), os.path.join(ROOT, "include", "mantrap_b200.h")]
 
 
 def build(force: bool = False) -> str:

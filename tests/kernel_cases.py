@@ -250,6 +250,51 @@ def check_jacobian_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_ca
     return worst
 
 
+def check_jacobian_block_vs_chunked(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, seed=0, setenv=None):
+    """The two Jacobian kernels on the same batch: jacobian_block_kernel (one evaluation per block, tangents in shared memory; the
+    default whenever the shape fits) against jacobian_kernel (chunks of 8 directions in registers; `MTB_JAC=1` in a library built
+    with the development knobs). Same forward arithmetic, hence identical constraint values; the Jacobians differ by the order in
+    which the pair terms are accumulated (aggregated 2x2 maps vs. per-direction sums), bounded by the oracle's own
+    float32-vs-float64 difference on the batch."""
+    from oracle import torch_oracle as to
+    from mantrap_b200 import scenarios
+    scene_cpu = scenarios.synthetic_scenes(num_scenes, n, p, env_kind=env_kind, ego_kind=ego_kind, seed=1400 + seed,
+                                           param_seed=1500 + seed, regular_sigma=True)
+    controls_cpu = scenarios.candidate_controls(num_scenes, num_candidates, t_hor, seed=1600 + seed, u_max=1.0)
+    spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True, ellipsoid=True)
+    scene, controls = scene_cpu.to(device), controls_cpu.to(device).contiguous()
+    out = {}
+    for knob in ("0", "1"):
+        setenv("MTB_JAC", knob)
+        jac, values = engine.launch_jacobian(lib, scene, controls, spec, want_values=True)
+        if device != "cpu":
+            torch.cuda.synchronize()
+        out[knob] = (np_(jac), np_(values))
+    setenv("MTB_JAC", "0")
+    assert np.isfinite(out["0"][0]).all() and np.isfinite(out["1"][0]).all()
+    if device == "cpu":
+        np.testing.assert_array_equal(out["0"][1], out["1"][1])      # min-distance values: the same forward rollout (IEEE emulation)
+    else:                                                            # nvcc --use_fast_math contracts the two kernels independently
+        gio.assert_parity(out["0"][1], out["1"][1], gio.RTOL_ROLLOUT, "min-distance values: block kernel vs chunked kernel", atol=1e-5)
+    floor = 0.0
+    if env_kind != "kalman":
+        osc = oracle_scene(scene_cpu, num_candidates)
+        for b in range(min(num_scenes * num_candidates, 4)):
+            one = to.Scene(*[(x[b:b + 1] if isinstance(x, torch.Tensor) else x) for x in osc])
+            u = controls_cpu.reshape(-1, t_hor, 2)[b:b + 1]
+            _, j_ref = to.min_distance_jacobian(one, u)
+            _, j64 = to.min_distance_jacobian(to.scene_to(one, torch.float64), u.double())
+            floor = max(floor, float((j_ref.double() - j64).abs().max()))
+    n_const = (2 * t_hor if ego_kind == "double" else t_hor) + 2 * (t_hor + 1)
+    n_md = n * t_hor
+    a, b = out["0"][0], out["1"][0]
+    np.testing.assert_array_equal(a[:, :, :n_const], b[:, :, :n_const])                        # control | speed rows: closed form
+    gio.assert_parity(a[:, :, n_const + n_md:], b[:, :, n_const + n_md:], 1e-6, "ellipsoid rows: block kernel vs chunked kernel")
+    assert env_kind == "kalman" or float(np.abs(b[:, :, n_const:n_const + n_md]).max()) > 1e-3
+    return gio.assert_parity(a[:, :, n_const:n_const + n_md], b[:, :, n_const:n_const + n_md], gio.RTOL_GRAD,
+                             "min-distance rows: block kernel vs chunked kernel", atol=gio.ATOL + 2 * floor)
+
+
 def check_jacobian_sampled_sigma_nonpositive(lib, device):
     """Outside the parity domain: a particle whose sampled sigma is <= 0 (the reference draws sigma from a Normal, so this
     happens with small probability) has a non-finite local derivative; the reference's autograd then returns NaN and

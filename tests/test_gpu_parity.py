@@ -183,6 +183,27 @@ def test_host_pipeline_matches_synchronous_api(eng):
         assert torch.allclose(got[k]["grad"], ref_out.grad, rtol=1e-4, atol=1e-6), k
 
 
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 16, 4, 10, 4, 20),         # config-3 shape
+    ("sf", "single", 4, 2, 5, 2, 5),
+    ("sf", "double", 8, 4, 20, 3, 12),          # config-4 shape
+    ("pf", "double", 4, 4, 5, 5, 15),
+    ("kalman", "double", 2, 2, 3, 1, 5),
+    ("sf", "double", 2, 2, 34, 2, 3),           # N > 32: two interaction mask words
+    ("sf", "double", 3, 2, 3, 5, 40),           # long horizon, many live control steps
+])
+def test_jacobian_block_vs_chunked(eng_dev, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor):
+    """jacobian_block_kernel (default) against jacobian_kernel (MTB_JAC=1 in the development library) on the same batch."""
+    kc.check_jacobian_block_vs_chunked(eng_dev.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, setenv=monkeypatch.setenv)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [("sf", "double", 4, 4, 10, 4, 20), ("pf", "single", 8, 2, 5, 5, 15)])
+def test_jacobian_vs_oracle_chunked_kernel(eng_dev, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor):
+    """jacobian_kernel, the fall-back for shapes whose tangents do not fit into shared memory, on its own against the oracle."""
+    monkeypatch.setenv("MTB_JAC", "1")
+    kc.check_jacobian_vs_oracle(eng_dev.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor)
+
+
 def test_jacobian_full_size_properties(eng):
     """Config-3 shape at BASELINE size (1024 scenes, SocialForces N=10 P=4 T=20, control + speed + min-distance + ellipsoid
     rows), properties that need no oracle: (1) duplicated candidates give bit-identical Jacobians wherever they land in the

@@ -108,6 +108,29 @@ def test_jacobian_vs_oracle(emul_lib, env_kind, ego_kind, s, c, n, p, t_hor):
 
 @pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
     ("sf", "double", 2, 2, 4, 3, 6),
+    ("sf", "single", 1, 2, 5, 2, 5),
+    ("sf", "double", 1, 2, 10, 4, 9),           # several live control steps per particle, neighbours in most steps
+    ("pf", "double", 1, 2, 5, 3, 7),
+    ("kalman", "double", 1, 1, 3, 1, 5),
+    ("sf", "double", 1, 1, 34, 2, 3),           # N > 32: two interaction mask words
+])
+def test_jacobian_block_vs_chunked(emul_lib, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor):
+    kc.check_jacobian_block_vs_chunked(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, setenv=monkeypatch.setenv)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 2, 2, 4, 3, 6),
+    ("pf", "double", 1, 2, 5, 3, 7),
+    ("sf", "double", 1, 1, 34, 2, 3),
+])
+def test_jacobian_vs_oracle_chunked_kernel(emul_lib, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor):
+    """jacobian_kernel (the fall-back for shapes whose tangents do not fit into shared memory) on its own against the oracle."""
+    monkeypatch.setenv("MTB_JAC", "1")
+    kc.check_jacobian_vs_oracle(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor)
+
+
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
+    ("sf", "double", 2, 2, 4, 3, 6),
     ("sf", "single", 1, 2, 12, 3, 5),
     ("pf", "double", 1, 3, 5, 5, 7),
     ("kalman", "single", 1, 1, 3, 1, 5),

@@ -60,8 +60,14 @@ if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--big", action="store_true")
     ap.add_argument("--only", default="")
+    ap.add_argument("--dev", action="store_true", help="load the -DMTB_DEV_KNOBS library (launch overrides from the environment, e.g. MTB_JAC=1)")
     args = ap.parse_args()
-    eng = engine.Engine("cuda:0")
+    if args.dev:
+        import ctypes
+        from mantrap_b200 import _cabi, build
+        eng = engine.Engine.from_library(_cabi.bind(ctypes.CDLL(build.build(dev_knobs=True))), "cuda:0")
+    else:
+        eng = engine.Engine("cuda:0")
     w = {"goal": 0.5, "acc": 1.0}
     if args.only == "c4":
         run(eng, "sf", 2048, 256, 20, 3, 12, w)
@@ -72,6 +78,8 @@ if __name__ == "__main__":
         run_jacobian(eng, "sf", 1024, 16, 10, 4, 20, ellipsoid=True)
         run_jacobian(eng, "sf", 256, 16, 20, 3, 12)
         run_jacobian(eng, "pf", 256, 64, 5, 5, 15)
+        run_jacobian(eng, "sf", 4096, 16, 3, 5, 10)
+        run_jacobian(eng, "sf", 64, 16, 20, 3, 40)
         sys.exit(0)
     run(eng, "sf", 1024, 256, 20, 3, 12, w)
     run(eng, "sf", 1024, 256, 20, 3, 12, w, grad=False)
