@@ -441,12 +441,15 @@ static int launch_jacobian(const JParams& prm, int grid, int block, size_t smem,
 // jacobian_block_kernel (mtb_jacobian_block.cuh): one evaluation per block, tangents in shared memory
 // ---------------------------------------------------------------------------------------------------------
 #ifdef MTB_DEV_KNOBS
-static int jac_knob() {                                     // development knob MTB_JAC: 1 = always jacobian_kernel
-    const char* v = std::getenv("MTB_JAC");
+static int jac_env(const char* name) {
+    const char* v = std::getenv(name);
     return (v != nullptr && v[0] != '\0') ? std::atoi(v) : 0;
 }
+static int jac_knob() { return jac_env("MTB_JAC"); }        // development knob MTB_JAC: 1 = always jacobian_kernel
+static int jac_block_knob() { return jac_env("MTB_JAC_BLOCK"); }   // development knob: threads per block of jacobian_block_kernel
 #else
 static constexpr int jac_knob() { return 0; }
+static constexpr int jac_block_knob() { return 0; }
 #endif
 
 // 0: launch geometry filled in; 1: the shape does not fit (use jacobian_kernel); < 0: error
@@ -495,6 +498,19 @@ static int plan_jacobian_block(const mtb_problem* pb, const mtb_modules* md, con
     if (work < 64) work = 64;
     if (work > 256) work = 256;
     block = round_up(work, 32);
+    // The kernel waits on its barriers most of the time (phase 1 runs on G threads only), so resident BLOCKS per SM matter more
+    // than threads per block: no more threads than let the register file (80 per thread) hold as many blocks as shared memory
+    // admits. Measured on B200, config-3 shape (54.7 KB per block, 4 blocks by shared memory): 256 threads 3.16 ms, 192 threads
+    // 2.68 ms, 128 threads 2.77 ms per 16384 Jacobians.
+    {
+        int by_smem = (int)((size_t)lim.smem_per_sm / (smem + 1024));
+        if (by_smem < 1) by_smem = 1;
+        int by_regs = (65536 / 80 / by_smem) / 32 * 32;
+        if (by_regs < round_up(prm.G, 32)) by_regs = round_up(prm.G, 32);
+        if (by_regs < 64) by_regs = 64;
+        if (block > by_regs) block = by_regs;
+    }
+    if (jac_block_knob() >= 32 && jac_block_knob() <= 256 && jac_block_knob() >= prm.G) block = round_up(jac_block_knob(), 32);
     return 0;
 }
 
@@ -503,7 +519,6 @@ static int launch_jacobian_block(const BParams& prm, int block, size_t smem, cud
     const DeviceLimits lim = device_limits();
     int per_sm = (int)((size_t)lim.smem_per_sm / (smem + 1024));
     if (per_sm > 2048 / block) per_sm = 2048 / block;
-    if (per_sm > 3 && block > 128) per_sm = 3;               // __launch_bounds__(256, 3)
     if (per_sm < 1) per_sm = 1;
 #ifndef MTB_HOST_EMUL
     {

@@ -56,6 +56,10 @@ MTB_DEV void mat_acc(P2& ux, P2& uy, float4 M, P2 ax, P2 ay) {
     uy = fma2(splat(M.w), ay, uy);
 }
 
+// x / d for 0 <= x < 2^16, 1 <= d <= 128 without the integer-division sequence: (x + 0.5) / d is at least 0.5 / d away from an
+// integer, the float product is off by < 2^16 * 2^-22, so the truncation is exact
+MTB_DEV int small_div(int x, float inv_d) { return (int)(((float)x + 0.5f) * inv_d); }
+
 constexpr int kLinRows = 5;   // per particle: Ap, Av (own state), Er, Ew (ego state), C (clamp), each a row-major 2x2
 
 template <int ENV>
@@ -200,14 +204,17 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
                     *reinterpret_cast<float2*>(jac + (size_t)(base_ell + k * T + level) * two_t + 2 * j) = make_float2(sanitize(vx), sanitize(vy));
                 }
                 if (want_mind) {
-                    const float nn = sqrtf(dx * dx + dy * dy);
-                    if (cons != nullptr && j == 0) cons[k * T + level] = nn;
                     float vx = 0.f, vy = 0.f;
-                    if (nn > 0.f && j < level) {
-                        float4 mp = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (tangents) mp = mud_l[2 * (k * T + j)];
-                        vx = (dx * (ep - mp.x) + dy * (0.f - mp.z)) / nn;
-                        vy = (dx * (0.f - mp.y) + dy * (ep - mp.w)) / nn;
+                    if (j < level || j == 0) {                        // (columns of later controls are structural zeros)
+                        const float nn = sqrtf(dx * dx + dy * dy);
+                        if (cons != nullptr && j == 0) cons[k * T + level] = nn;
+                        if (nn > 0.f && j < level) {
+                            float4 mp = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (tangents) mp = mud_l[2 * (k * T + j)];
+                            const float inv_nn = 1.0f / nn;
+                            vx = (dx * (ep - mp.x) + dy * (0.f - mp.z)) * inv_nn;
+                            vy = (dx * (0.f - mp.y) + dy * (ep - mp.w)) * inv_nn;
+                        }
                     }
                     // np.nan_to_num of compute_gradient_auto_grad (optimization_module.py:440-446): a tangent poisoned by a
                     // non-finite local derivative (a sampled sigma <= 0, DESIGN.md "parity domain") is reported as 0, never as NaN
@@ -321,8 +328,9 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
             // ---------------------------------------------------- phase 2: the map applied to the live tangents (g, j < t)
             if (live) {
                 const int cnt = G * t;
-                int g = tid / t, j = tid - g * t;
-                const int qs = NT / t, rs = NT - qs * t;
+                const float inv_t = 1.0f / (float)t;
+                int g = small_div(tid, inv_t), j = tid - g * t;
+                const int qs = small_div(NT, inv_t), rs = NT - qs * t;
                 const P2 dt2 = splat(dt);
                 for (int idx = tid; idx < cnt; idx += NT) {
                     const float2 et = ego_tangent(ego_kind, dt, t, j);   // (d ego_p, d ego_v) at time t w.r.t. control j, same component
@@ -387,8 +395,9 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
             }
             if (live) {
                 const int cnt = N * t;
-                int k = tid / t, j = tid - k * t;
-                const int qs = NT / t, rs = NT - qs * t;
+                const float inv_t = 1.0f / (float)t;
+                int k = small_div(tid, inv_t), j = tid - k * t;
+                const int qs = small_div(NT, inv_t), rs = NT - qs * t;
                 const P2 dt2 = splat(dt), inv_p2 = splat(1.0f / (float)P);
                 for (int idx = tid; idx < cnt; idx += NT) {
                     const float4 cA = mud_t[2 * (k * T + j)], cB = mud_t[2 * (k * T + j) + 1];
