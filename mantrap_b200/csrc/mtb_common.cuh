@@ -17,6 +17,21 @@
 static __device__ __forceinline__ void mtb_bar_sync(int id, int count) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
+// arrive at a named barrier without waiting (producer side of a producer / consumer hand-over inside a block): `count` is the
+// number of threads that arrive at OR wait on this barrier id in one phase
+static __device__ __forceinline__ void mtb_bar_arrive(int id, int count) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
+}
+// the same with IMMEDIATE barrier ids: ptxas reserves only the ids it sees (a register id reserves all 16 barriers of the block,
+// which caps an SM at 4 resident blocks)
+template <int ID>
+static __device__ __forceinline__ void mtb_bar_sync_id(int count) {
+    asm volatile("bar.sync %0, %1;" ::"n"(ID), "r"(count) : "memory");
+}
+template <int ID>
+static __device__ __forceinline__ void mtb_bar_arrive_id(int count) {
+    asm volatile("bar.arrive %0, %1;" ::"n"(ID), "r"(count) : "memory");
+}
 // Fire-and-forget 16-byte float accumulation in L2 (REDG.E.ADD.F32x4, sm_90+): one instruction per pair adjoint instead
 // of four shared-memory compare-and-swap loops. The target lives in an L2-resident global scratch; loads / stores of it
 // bypass L1 (ld/st.global.cg) and are ordered against the reductions by the group barriers.

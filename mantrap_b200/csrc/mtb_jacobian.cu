@@ -447,9 +447,11 @@ static int jac_env(const char* name) {
 }
 static int jac_knob() { return jac_env("MTB_JAC"); }        // development knob MTB_JAC: 1 = always jacobian_kernel
 static int jac_block_knob() { return jac_env("MTB_JAC_BLOCK"); }   // development knob: threads per block of jacobian_block_kernel
+static int jac_ring_knob() { return jac_env("MTB_JAC_RING"); }     // development knob: 1 = one ring slot
 #else
 static constexpr int jac_knob() { return 0; }
 static constexpr int jac_block_knob() { return 0; }
+static constexpr int jac_ring_knob() { return 0; }
 #endif
 
 // 0: launch geometry filled in; 1: the shape does not fit (use jacobian_kernel); < 0: error
@@ -473,44 +475,54 @@ static int plan_jacobian_block(const mtb_problem* pb, const mtb_modules* md, con
     const ConstraintRows rows = constraint_rows(pb, md);
     prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.rows_ell = rows.ell; prm.R = rows.total;
     if (prm.R == 0) return MTB_ERR_BAD_ARGUMENT;
-    if (prm.G > 256) return 1;
+    if (prm.G > 224) return 1;
     prm.num_evals = (long long)pb->num_scenes * pb->num_candidates;
     const bool tangents = rows.mind > 0 && !kalman;
     const bool pairs = tangents && pb->env_kind == MTB_ENV_SOCIAL_FORCES;
-    int off = 0;
-    prm.off_ctl = off;  off += round_up(2 * prm.T, 4);
-    prm.off_ego = off;  off += (prm.T + 1) * 4;
-    prm.off_mus = off;  off += 2 * prm.N * 4;
-    prm.off_var = off;  off += round_up(2 * prm.N * 2, 4);
-    prm.off_pw = off;   off += round_up(prm.G, 4);
-    prm.off_q = off;    off += round_up(prm.G * 2, 4);
-    prm.off_lin = off;  off += tangents ? prm.G * kLinRows * 4 : 0;
-    prm.off_nbr = off;  off += tangents ? round_up(prm.G * prm.MW, 4) : 0;
-    prm.off_pool = off; off += pairs ? prm.G * prm.NM1 * 8 : 0;
-    prm.off_tan = off;  off += tangents ? prm.G * prm.T * 8 : 0;
-    prm.off_mud = off;  off += tangents ? 2 * prm.N * prm.T * 8 : 0;
-    smem = (size_t)off * sizeof(float);
     const DeviceLimits lim = device_limits();
+    auto layout = [&](int ring) -> size_t {
+        int off = 0;
+        prm.off_ctl = off;  off += round_up(2 * prm.T, 4);
+        prm.off_ego = off;  off += (prm.T + 1) * 4;
+        prm.off_mus = off;  off += prm.T * prm.N * 4;
+        prm.off_var = off;  off += round_up(prm.T * prm.N * 2, 4);
+        prm.off_pw = off;   off += round_up(prm.G, 4);
+        prm.off_q = off;    off += round_up(prm.G * 2, 4);
+        prm.off_lin = off;  off += tangents ? ring * prm.G * kLinRows * 4 : 0;
+        prm.off_nbr = off;  off += tangents ? round_up(ring * prm.G * prm.MW, 4) : 0;
+        prm.off_pool = off; off += pairs ? ring * prm.G * prm.NM1 * 8 : 0;
+        prm.off_tan = off;  off += tangents ? prm.G * prm.T * 8 : 0;
+        prm.off_mud = off;  off += tangents ? 2 * prm.N * prm.T * 8 : 0;
+        prm.ring = ring;
+        return (size_t)off * sizeof(float);
+    };
+    auto resident = [&](size_t bytes) { return (int)((size_t)lim.smem_per_sm / (bytes + 1024)); };
+    // two ring slots (the forward warps one full step ahead) unless the second slot costs a resident block per SM
+    {
+        const size_t one = layout(1), two = layout(2);
+        const int ring = (resident(two) < resident(one) || two > (size_t)lim.max_smem / 2 || jac_ring_knob() == 1) ? 1 : 2;
+        smem = layout(ring);
+    }
     if (smem > (size_t)lim.max_smem / 2) return 1;                       // fewer than two resident blocks per SM: not this kernel's shape
-    // threads: the particles in phase 1, (particle, live control step) items in phase 2 (G * t of them at step t), N * T row entries
+    // threads: GR = round_up(G, 32) for the forward role + the tangent warps, whose work items are (particle, live control step):
+    // G * t of them at step t, N * T row entries per level
+    prm.GR = round_up(prm.G, 32);
     int work = prm.G * prm.T / 2;
-    if (work < prm.G) work = prm.G;
-    if (work < 64) work = 64;
-    if (work > 256) work = 256;
-    block = round_up(work, 32);
-    // The kernel waits on its barriers most of the time (phase 1 runs on G threads only), so resident BLOCKS per SM matter more
-    // than threads per block: no more threads than let the register file (80 per thread) hold as many blocks as shared memory
-    // admits. Measured on B200, config-3 shape (54.7 KB per block, 4 blocks by shared memory): 256 threads 3.16 ms, 192 threads
-    // 2.68 ms, 128 threads 2.77 ms per 16384 Jacobians.
+    if (work < 32) work = 32;
+    if (work > 192) work = 192;
+    block = prm.GR + round_up(work, 32);
+    if (block > 256) block = 256;
+    // The kernel waits on its barriers most of the time, so resident BLOCKS per SM matter more than threads per block: no more
+    // threads than let the register file (80 per thread) hold as many blocks as shared memory admits.
     {
         int by_smem = (int)((size_t)lim.smem_per_sm / (smem + 1024));
         if (by_smem < 1) by_smem = 1;
         int by_regs = (65536 / 80 / by_smem) / 32 * 32;
-        if (by_regs < round_up(prm.G, 32)) by_regs = round_up(prm.G, 32);
-        if (by_regs < 64) by_regs = 64;
+        if (by_regs < prm.GR + 32) by_regs = prm.GR + 32;
         if (block > by_regs) block = by_regs;
     }
-    if (jac_block_knob() >= 32 && jac_block_knob() <= 256 && jac_block_knob() >= prm.G) block = round_up(jac_block_knob(), 32);
+    if (block > 256) return 1;
+    if (jac_block_knob() >= prm.GR + 32 && jac_block_knob() <= 256) block = round_up(jac_block_knob(), 32);
     return 0;
 }
 

@@ -72,6 +72,9 @@ static inline void mtb_bar_sync(int, int) {}
 #else
 static inline void mtb_bar_sync(int id, int count) { emul::tl_block->named_barrier(id, count).arrive_and_wait(); }
 #endif
+static inline void mtb_bar_arrive(int id, int count) { (void)emul::tl_block->named_barrier(id, count).arrive(); }
+template <int ID> static inline void mtb_bar_sync_id(int count) { mtb_bar_sync(ID, count); }
+template <int ID> static inline void mtb_bar_arrive_id(int count) { mtb_bar_arrive(ID, count); }
 
 template <class T>
 static inline T emul_exchange(T v, int src_lane) {

@@ -250,7 +250,7 @@ def check_jacobian_vs_oracle(lib, device, env_kind, ego_kind, num_scenes, num_ca
     return worst
 
 
-def check_jacobian_block_vs_chunked(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, seed=0, setenv=None):
+def check_jacobian_block_vs_chunked(lib, device, env_kind, ego_kind, num_scenes, num_candidates, n, p, t_hor, seed=0, setenv=None, ring=0):
     """The two Jacobian kernels on the same batch: jacobian_block_kernel (one evaluation per block, tangents in shared memory; the
     default whenever the shape fits) against jacobian_kernel (chunks of 8 directions in registers; `MTB_JAC=1` in a library built
     with the development knobs). Same forward arithmetic, hence identical constraint values; the Jacobians differ by the order in
@@ -264,6 +264,7 @@ def check_jacobian_block_vs_chunked(lib, device, env_kind, ego_kind, num_scenes,
     spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True, ellipsoid=True)
     scene, controls = scene_cpu.to(device), controls_cpu.to(device).contiguous()
     out = {}
+    setenv("MTB_JAC_RING", str(ring))                # 1: the block kernel with ONE ring slot (forward and tangent warps alternate)
     for knob in ("0", "1"):
         setenv("MTB_JAC", knob)
         jac, values = engine.launch_jacobian(lib, scene, controls, spec, want_values=True)

@@ -197,6 +197,12 @@ def test_jacobian_block_vs_chunked(eng_dev, monkeypatch, env_kind, ego_kind, s, 
     kc.check_jacobian_block_vs_chunked(eng_dev.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, setenv=monkeypatch.setenv)
 
 
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [("sf", "double", 2, 2, 4, 3, 6), ("sf", "double", 1, 2, 10, 4, 9), ("pf", "single", 1, 2, 5, 3, 7)])
+def test_jacobian_block_one_ring_slot(eng_dev, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor):
+    """The block kernel with one ring slot (shapes where a second slot would cost a resident block per SM)."""
+    kc.check_jacobian_block_vs_chunked(eng_dev.lib, DEV, env_kind, ego_kind, s, c, n, p, t_hor, setenv=monkeypatch.setenv, ring=1)
+
+
 @pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [("sf", "double", 4, 4, 10, 4, 20), ("pf", "single", 8, 2, 5, 5, 15)])
 def test_jacobian_vs_oracle_chunked_kernel(eng_dev, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor):
     """jacobian_kernel, the fall-back for shapes whose tangents do not fit into shared memory, on its own against the oracle."""

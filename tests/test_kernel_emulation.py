@@ -118,6 +118,12 @@ def test_jacobian_block_vs_chunked(emul_lib, monkeypatch, env_kind, ego_kind, s,
     kc.check_jacobian_block_vs_chunked(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, setenv=monkeypatch.setenv)
 
 
+@pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [("sf", "double", 2, 2, 4, 3, 6), ("sf", "double", 1, 2, 10, 4, 9), ("pf", "single", 1, 2, 5, 3, 7)])
+def test_jacobian_block_one_ring_slot(emul_lib, monkeypatch, env_kind, ego_kind, s, c, n, p, t_hor):
+    """The block kernel with one ring slot (shapes where a second slot would cost a resident block per SM)."""
+    kc.check_jacobian_block_vs_chunked(emul_lib, "cpu", env_kind, ego_kind, s, c, n, p, t_hor, setenv=monkeypatch.setenv, ring=1)
+
+
 @pytest.mark.parametrize("env_kind,ego_kind,s,c,n,p,t_hor", [
     ("sf", "double", 2, 2, 4, 3, 6),
     ("pf", "double", 1, 2, 5, 3, 7),
