@@ -10,7 +10,8 @@ from mantrap_b200 import _cabi, build, engine, scenarios  # noqa: E402
 
 if __name__ == "__main__":
     s, c, n, p, t_hor = (int(x) for x in (sys.argv[1:6] if len(sys.argv) > 5 else (1024, 16, 10, 4, 20)))
-    eng = engine.Engine.from_library(_cabi.bind(ctypes.CDLL(build.build(dev_knobs=True))), "cuda:0")
+    prod = os.environ.get("MTB_AB_PROD", "") == "1"       # A/B: the production library (possibly built from another source state)
+    eng = engine.Engine.from_library(_cabi.bind(ctypes.CDLL(build.LIB_PATH if prod else build.build(dev_knobs=True))), "cuda:0")
     scene = scenarios.synthetic_scenes(s, n, p, env_kind="sf").to("cuda:0")
     controls = scenarios.candidate_controls(s, c, t_hor).to("cuda:0")
     spec = engine.ModuleSpec(control_limits=True, speed_limits=True, min_distance=True)
@@ -24,4 +25,4 @@ if __name__ == "__main__":
         b.record()
         torch.cuda.synchronize()
         times.append(a.elapsed_time(b))
-    print(os.environ.get("MTB_JAC_BLOCK", "default"), " ".join(f"{x:.2f}" for x in times), flush=True)
+    print("prod" if prod else "dev", os.environ.get("MTB_JAC_BLOCK", "default"), " ".join(f"{x:.2f}" for x in times), flush=True)
