@@ -471,7 +471,8 @@ static int plan_jacobian_block(const mtb_problem* pb, const mtb_modules* md, con
     prm.G = prm.N * prm.P;
     prm.MW = (prm.N + 31) / 32;
     prm.NM1 = prm.N - 1;
-    prm.pair_cut2 = pair_cut_squared(pb->sf_interaction_radius);
+    prm.NP4 = round_up(prm.N, 4);
+    prm.pair_cut_above = nextafterf(pair_cut_squared(pb->sf_interaction_radius), INFINITY);   // d^2 < cut_above  <=>  norm <= radius
     const ConstraintRows rows = constraint_rows(pb, md);
     prm.rows_control = rows.control; prm.rows_speed = rows.speed; prm.rows_mind = rows.mind; prm.rows_ell = rows.ell; prm.R = rows.total;
     if (prm.R == 0) return MTB_ERR_BAD_ARGUMENT;
@@ -482,6 +483,7 @@ static int plan_jacobian_block(const mtb_problem* pb, const mtb_modules* md, con
     const DeviceLimits lim = device_limits();
     auto layout = [&](int ring) -> size_t {
         int off = 0;
+        prm.off_pos = off;  off += 2 * prm.NP4;
         prm.off_ctl = off;  off += round_up(2 * prm.T, 4);
         prm.off_ego = off;  off += (prm.T + 1) * 4;
         prm.off_mus = off;  off += prm.T * prm.N * 4;

@@ -32,9 +32,10 @@ struct BParams {
     int T, N, P, G, MW, NM1, GR;      // GR = round_up(G, 32): threads of the forward role
     long long num_evals;
     int rows_control, rows_speed, rows_mind, rows_ell, R;
-    float pair_cut2;
+    float pair_cut_above;             // the float after the largest d^2 whose sqrtf is <= radius (radius_bits4)
+    int NP4;                          // round_up(N, 4)
     // float offsets into dynamic shared memory
-    int off_ctl, off_ego, off_mus, off_var, off_pw, off_q, off_lin, off_nbr, off_pool, off_tan, off_mud;
+    int off_pos, off_ctl, off_ego, off_mus, off_var, off_pw, off_q, off_lin, off_nbr, off_pool, off_tan, off_mud;
 };
 
 // tangent of the ego state at time index t w.r.t. control j (same component): (d p, d v)   [SURVEY A.1]
@@ -94,6 +95,8 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
     float4* ego = reinterpret_cast<float4*>(sm + prm.off_ego);        // [T+1]
     float4* mus = reinterpret_cast<float4*>(sm + prm.off_mus);        // [T][N] means of every level
     float2* varl = reinterpret_cast<float2*>(sm + prm.off_var);       // [T][N] scales of every level (ellipsoid rows)
+    float* posx = sm + prm.off_pos;                                   // [NP4] x then [NP4] y of the current means (SoA rows of the radius
+    float* posy = posx + prm.NP4;                                     //       tests, padded with +inf; owned by the forward warps)
     float* pwb = sm + prm.off_pw;                                     // [G] particle weights
     float2* qbuf = reinterpret_cast<float2*>(sm + prm.off_q);         // [G] weighted velocities of the step
     float4* lin = reinterpret_cast<float4*>(sm + prm.off_lin);        // [2][G][kLinRows]                          (ring of two steps)
@@ -107,8 +110,6 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
     const bool tangents = want_mind && ENV != MTB_ENV_KALMAN;         // (ellipsoid rows need the forward state only)
     const int base_mind = prm.rows_control + prm.rows_speed;
     const int base_ell = base_mind + prm.rows_mind;
-    // (k, j) of a tangent thread's first row entry and the increments of one stride of NTT entries over [N][T]
-    const int row_k0 = ttid / T, row_j0 = ttid - row_k0 * T, row_qs = NTT / T, row_rs = NTT - row_qs * T;
 
     for (long long ev = blockIdx.x; ev < prm.num_evals; ev += gridDim.x) {
         const int s = (int)(ev / (long long)prm.pb.num_candidates);
@@ -124,9 +125,14 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
             for (int t = tid; t <= T; t += NT) ego[t] = *reinterpret_cast<const float4*>(x_g + t * 4);
         }
         const float* ado0_s = prm.pb.ado0 + (size_t)s * N * 4;
-        for (int k = tid; k < N; k += NT) {
-            mus[k] = *reinterpret_cast<const float4*>(ado0_s + k * 4);
-            varl[k] = make_float2(prm.pb.var_initial, prm.pb.var_initial);
+        for (int k = tid; k < prm.NP4; k += NT) {
+            float4 a0 = make_float4(INFINITY, INFINITY, 0.f, 0.f);
+            if (k < N) {
+                a0 = *reinterpret_cast<const float4*>(ado0_s + k * 4);
+                mus[k] = a0;
+                varl[k] = make_float2(prm.pb.var_initial, prm.pb.var_initial);
+            }
+            posx[k] = a0.x; posy[k] = a0.y;
         }
         if (tangents) {
             const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -180,8 +186,9 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
         __syncthreads();
 
         // ------------------------------------------------------------ constant rows: control | speed (whole lines)
+        const float inv_two_t = 1.0f / (float)two_t;                  // (rows x 2T < 2^16: small_div is exact)
         for (int idx = tid; idx < prm.rows_control * two_t; idx += NT) {
-            const int r = idx / two_t, dg = idx - r * two_t;
+            const int r = small_div(idx, inv_two_t), dg = idx - r * two_t;
             float val;
             if (ego_kind == MTB_EGO_DOUBLE_INTEGRATOR) {
                 val = (r == dg) ? 1.f : 0.f;                          // control_limits.py:62-68 (identity, also for u < 0)
@@ -196,7 +203,7 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
             jac[idx] = val;
         }
         for (int idx = tid; idx < prm.rows_speed * two_t; idx += NT) {
-            const int r = idx / two_t, dg = idx - r * two_t;
+            const int r = small_div(idx, inv_two_t), dg = idx - r * two_t;
             const float val = ((r & 1) == (dg & 1)) ? ego_tangent(ego_kind, dt, r >> 1, dg >> 1).y : 0.f;
             jac[(size_t)prm.rows_control * two_t + idx] = val;
         }
@@ -215,11 +222,15 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
                     float4 Ap = zero4, Av = zero4, Er = zero4, Ew = zero4, C = zero4;
                     unsigned bits0 = 0u, bits1 = 0u;
                     if (ENV == MTB_ENV_SOCIAL_FORCES) {
-                        for (int k = 0; k < N; ++k) {                 // same gate as evaluate_kernel: norm <= radius, never the own ado
-                            const float4 mu = mus_t[k];
-                            const float dx = p.x - mu.x, dy = p.y - mu.y;
-                            const bool in = (k != m) && (fmaf(dx, dx, dy * dy) <= prm.pair_cut2);
-                            if (in) { if (k < 32) bits0 |= 1u << k; else bits1 |= 1u << (k - 32); }
+                        for (int wd = 0; wd < MW; ++wd) {             // same gate as evaluate_kernel: norm <= radius, never the own ado
+                            unsigned bits = 0u;
+                            const int kbase = wd << 5;
+                            const int kend = (prm.NP4 - kbase) < 32 ? (prm.NP4 - kbase) : 32;
+                            for (int k0 = kend - 4; k0 >= 0; k0 -= 4)
+                                bits = radius_bits4(bits, *reinterpret_cast<const float4*>(posx + kbase + k0),
+                                                    *reinterpret_cast<const float4*>(posy + kbase + k0), p.x, p.y, prm.pair_cut_above);
+                            if ((m >> 5) == wd) bits &= ~(1u << (m & 31));
+                            if (wd == 0) bits0 = bits; else bits1 = bits;
                         }
                         const V2 fgoal = goal_force(p, v, goal, inv_tau, prm.pb.sf_goal_radius);
                         if (live) {
@@ -305,7 +316,9 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
                     const float4 c = mus_t[m];
                     const float inv_p = 1.0f / (float)P;
                     const float mx = sx * inv_p, my = sy * inv_p;
-                    mus[(t + 1) * N + m] = make_float4(fmaf(c.z, dt, c.x), fmaf(c.w, dt, c.y), mx, my);
+                    const float npx = fmaf(c.z, dt, c.x), npy = fmaf(c.w, dt, c.y);
+                    mus[(t + 1) * N + m] = make_float4(npx, npy, mx, my);
+                    posx[m] = npx; posy[m] = npy;
                     if (prm.rows_ell > 0 && ENV != MTB_ENV_KALMAN) {   // unbiased variance of the weighted velocities (particle.py:175)
                         float vx = 0.f, vy = 0.f;
                         for (int jj = 0; jj < P; ++jj) {
@@ -324,41 +337,100 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
             // ======================================================== tangent warps: maps -> tangents -> rows
             // rows of time index `level` (means and their tangents complete): min-distance and ellipsoid lines, both directions of a
             // control step per store
+            const bool one_pass_rows = N * T <= NTT;                  // a level's N x T entries fit into one pass of the tangent threads
+            const float inv_T = 1.0f / (float)T;
             auto write_rows = [&](int level, const float4* mud_l) {
                 const float4* mus_l = mus + level * N;
                 const float2* var_l = varl + level * N;
                 const float4 eg = ego[level];
-                int k = row_k0, j = row_j0;
-                for (int idx = ttid; idx < N * T; idx += NTT) {
+                if (one_pass_rows) {
+                    // small shapes: one entry per thread, zeros and values in the same pass (three loop set-ups would cost more
+                    // than the arithmetic they save: config-1 shape 1.29 vs 1.45 ms per 65536 Jacobians)
+                    if (ttid < N * T) {
+                        const int k = small_div(ttid, inv_T), j = ttid - k * T;
+                        const float4 mu = mus_l[k];
+                        const float ep = ego_tangent(ego_kind, dt, level, j).x;
+                        const float dx = eg.x - mu.x, dy = eg.y - mu.y;
+                        const size_t col = (size_t)(k * T + level) * two_t + 2 * j;
+                        if (prm.rows_ell > 0) {
+                            float2 sv = var_l[k];
+                            if (ENV == MTB_ENV_KALMAN) sv.x = sv.y = fmaf(prm.pb.kalman_noise, (float)level, prm.pb.var_initial);
+                            const float vx = 2.0f * dx / fmaxf(sv.x, prm.md.ellipsoid_min_scale) * ep;
+                            const float vy = 2.0f * dy / fmaxf(sv.y, prm.md.ellipsoid_min_scale) * ep;
+                            *reinterpret_cast<float2*>(jac + (size_t)base_ell * two_t + col) = make_float2(sanitize(vx), sanitize(vy));
+                        }
+                        if (want_mind) {
+                            float vx = 0.f, vy = 0.f;
+                            if (j < level || j == 0) {
+                                const float nn = sqrtf(dx * dx + dy * dy);
+                                if (cons != nullptr && j == 0) cons[k * T + level] = nn;
+                                if (nn > 0.f && j < level) {
+                                    float4 mp = make_float4(0.f, 0.f, 0.f, 0.f);
+                                    if (tangents) mp = mud_l[2 * (k * T + j)];
+                                    const float inv_nn = 1.0f / nn;
+                                    vx = (dx * (ep - mp.x) + dy * (0.f - mp.z)) * inv_nn;
+                                    vy = (dx * (0.f - mp.y) + dy * (ep - mp.w)) * inv_nn;
+                                }
+                            }
+                            *reinterpret_cast<float2*>(jac + (size_t)base_mind * two_t + col) = make_float2(sanitize(vx), sanitize(vy));
+                        }
+                    }
+                    return;
+                }
+                if (want_mind && cons != nullptr) {
+                    for (int k = ttid; k < N; k += NTT) {
+                        const float4 mu = mus_l[k];
+                        const float dx = eg.x - mu.x, dy = eg.y - mu.y;
+                        cons[k * T + level] = sqrtf(dx * dx + dy * dy);
+                    }
+                }
+                // structural zeros: the columns of the control steps j >= level (they act on later time indices only)
+                {
+                    const int w = T - level;
+                    const float inv_w = 1.0f / (float)w;
+                    int k = small_div(ttid, inv_w), jj = ttid - k * w;
+                    const int qs = small_div(NTT, inv_w), rs = NTT - qs * w;
+                    const float2 zero2 = make_float2(0.f, 0.f);
+                    for (int idx = ttid; idx < N * w; idx += NTT) {
+                        const size_t col = (size_t)(k * T + level) * two_t + 2 * (level + jj);
+                        if (want_mind) *reinterpret_cast<float2*>(jac + (size_t)base_mind * two_t + col) = zero2;
+                        if (prm.rows_ell > 0) *reinterpret_cast<float2*>(jac + (size_t)base_ell * two_t + col) = zero2;
+                        k += qs; jj += rs;
+                        if (jj >= w) { jj -= w; ++k; }
+                    }
+                }
+                if (level < 1) return;
+                const float inv_l = 1.0f / (float)level;
+                int k = small_div(ttid, inv_l), j = ttid - k * level;
+                const int qs = small_div(NTT, inv_l), rs = NTT - qs * level;
+                for (int idx = ttid; idx < N * level; idx += NTT) {
                     const float4 mu = mus_l[k];
                     const float ep = ego_tangent(ego_kind, dt, level, j).x;
                     const float dx = eg.x - mu.x, dy = eg.y - mu.y;
+                    const size_t col = (size_t)(k * T + level) * two_t + 2 * j;
                     if (prm.rows_ell > 0) {
                         float2 sv = var_l[k];
                         if (ENV == MTB_ENV_KALMAN) sv.x = sv.y = fmaf(prm.pb.kalman_noise, (float)level, prm.pb.var_initial);
                         const float vx = 2.0f * dx / fmaxf(sv.x, prm.md.ellipsoid_min_scale) * ep;
                         const float vy = 2.0f * dy / fmaxf(sv.y, prm.md.ellipsoid_min_scale) * ep;
-                        *reinterpret_cast<float2*>(jac + (size_t)(base_ell + k * T + level) * two_t + 2 * j) = make_float2(sanitize(vx), sanitize(vy));
+                        *reinterpret_cast<float2*>(jac + (size_t)base_ell * two_t + col) = make_float2(sanitize(vx), sanitize(vy));
                     }
                     if (want_mind) {
                         float vx = 0.f, vy = 0.f;
-                        if (j < level || j == 0) {                    // (columns of later controls are structural zeros)
-                            const float nn = sqrtf(dx * dx + dy * dy);
-                            if (cons != nullptr && j == 0) cons[k * T + level] = nn;
-                            if (nn > 0.f && j < level) {
-                                float4 mp = make_float4(0.f, 0.f, 0.f, 0.f);
-                                if (tangents) mp = mud_l[2 * (k * T + j)];
-                                const float inv_nn = 1.0f / nn;
-                                vx = (dx * (ep - mp.x) + dy * (0.f - mp.z)) * inv_nn;
-                                vy = (dx * (0.f - mp.y) + dy * (ep - mp.w)) * inv_nn;
-                            }
+                        const float nn = sqrtf(dx * dx + dy * dy);
+                        if (nn > 0.f) {
+                            float4 mp = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (tangents) mp = mud_l[2 * (k * T + j)];
+                            const float inv_nn = 1.0f / nn;
+                            vx = (dx * (ep - mp.x) + dy * (0.f - mp.z)) * inv_nn;
+                            vy = (dx * (0.f - mp.y) + dy * (ep - mp.w)) * inv_nn;
                         }
                         // np.nan_to_num of compute_gradient_auto_grad (optimization_module.py:440-446): a tangent poisoned by a
                         // non-finite local derivative (a sampled sigma <= 0, DESIGN.md "parity domain") is reported as 0, never as NaN
-                        *reinterpret_cast<float2*>(jac + (size_t)(base_mind + k * T + level) * two_t + 2 * j) = make_float2(sanitize(vx), sanitize(vy));
+                        *reinterpret_cast<float2*>(jac + (size_t)base_mind * two_t + col) = make_float2(sanitize(vx), sanitize(vy));
                     }
-                    k += row_qs; j += row_rs;
-                    if (j >= T) { j -= T; ++k; }
+                    k += qs; j += rs;
+                    if (j >= level) { j -= level; ++k; }
                 }
             };
             write_rows(0, mud);

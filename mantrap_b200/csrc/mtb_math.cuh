@@ -56,6 +56,33 @@ MTB_DEV float sanitize(float x) {       // np.nan_to_num (optimization_module.py
     return x;
 }
 
+// Radius test of one particle against four ado means (SoA rows X, Y), appended to a running bit mask: the mask is shifted
+// left by four and the new low bits 3..0 are the tests of X.w .. X.x (callers walk the ados from high to low, so that bit k of
+// the finished word is ado k). A test is  fmaf(dx, dx, dy * dy) < cut_above  with (dx, dy) = p - mean, cut_above = the float
+// after the largest d^2 whose sqrtf is <= radius, i.e. exactly `norm <= radius`. Device: packed FP32 (two tests per
+// instruction); the sign bit of d^2 - cut_above is funnel-shifted into the mask (no predicates, no selects).
+MTB_DEV unsigned radius_bits4(unsigned acc, float4 X, float4 Y, float px, float py, float cut_above) {
+#if !defined(MTB_HOST_EMUL) && !defined(MTB_NO_F32X2)
+    const float2 m1 = make_float2(-1.f, -1.f), pxx = make_float2(px, px), pyy = make_float2(py, py);
+    const float2 nc = make_float2(-cut_above, -cut_above);
+    const float2 dx01 = __ffma2_rn(make_float2(X.x, X.y), m1, pxx), dx23 = __ffma2_rn(make_float2(X.z, X.w), m1, pxx);
+    const float2 dy01 = __ffma2_rn(make_float2(Y.x, Y.y), m1, pyy), dy23 = __ffma2_rn(make_float2(Y.z, Y.w), m1, pyy);
+    const float2 s01 = __fadd2_rn(__ffma2_rn(dx01, dx01, __fmul2_rn(dy01, dy01)), nc);
+    const float2 s23 = __fadd2_rn(__ffma2_rn(dx23, dx23, __fmul2_rn(dy23, dy23)), nc);
+    acc = __funnelshift_l(__float_as_uint(s23.y), acc, 1);
+    acc = __funnelshift_l(__float_as_uint(s23.x), acc, 1);
+    acc = __funnelshift_l(__float_as_uint(s01.y), acc, 1);
+    acc = __funnelshift_l(__float_as_uint(s01.x), acc, 1);
+    return acc;
+#else
+    const float d0 = fmaf(px - X.x, px - X.x, (py - Y.x) * (py - Y.x));
+    const float d1 = fmaf(px - X.y, px - X.y, (py - Y.y) * (py - Y.y));
+    const float d2 = fmaf(px - X.z, px - X.z, (py - Y.z) * (py - Y.z));
+    const float d3 = fmaf(px - X.w, px - X.w, (py - Y.w) * (py - Y.w));
+    return (acc << 4) | (d0 < cut_above ? 1u : 0u) | (d1 < cut_above ? 2u : 0u) | (d2 < cut_above ? 4u : 0u) | (d3 < cut_above ? 8u : 0u);
+#endif
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Social-forces repulsion  F = dV/dr,  V = v0 exp(-b/sigma),  b = 1/2 sqrt((|r| + |r - w dt|)^2 - (dt |w|)^2)
 // ---------------------------------------------------------------------------------------------------------
