@@ -191,7 +191,7 @@ int mtb_query_launch(const mtb_problem* problem, int want_grad, mtb_launch_info*
  * ellipsoid rows = 2 (ego_p - mu_p) / max(scale, min) through the ego rollout only (means detached).
  * cons (optional, may be NULL) receives the un-normalised min-distance values [S,C,N*T].
  * Two kernels behind this entry point, same results up to rounding: jacobian_block_kernel (one evaluation per block, tangents
- * in shared memory; taken whenever jac is 8-byte aligned, N * P <= 224 and its shared-memory layout leaves two blocks per SM)
+ * in shared memory; taken whenever jac is 8-byte aligned, N * P <= 224 and its shared-memory layout fits one block)
  * and jacobian_kernel (chunks of 8 control directions in registers) for everything else. No workspace is needed by either. */
 int mtb_constraint_jacobian(const mtb_problem* problem, const mtb_modules* modules, float* cons,
                             float* jac, void* workspace, size_t workspace_bytes, void* stream);

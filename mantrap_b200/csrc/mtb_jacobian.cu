@@ -448,10 +448,12 @@ static int jac_env(const char* name) {
 static int jac_knob() { return jac_env("MTB_JAC"); }        // development knob MTB_JAC: 1 = always jacobian_kernel
 static int jac_block_knob() { return jac_env("MTB_JAC_BLOCK"); }   // development knob: threads per block of jacobian_block_kernel
 static int jac_ring_knob() { return jac_env("MTB_JAC_RING"); }     // development knob: 1 = one ring slot
+static int jac_full_knob() { return jac_env("MTB_JAC_FULL"); }     // development knob: 2 = only layouts that leave two blocks per SM
 #else
 static constexpr int jac_knob() { return 0; }
 static constexpr int jac_block_knob() { return 0; }
 static constexpr int jac_ring_knob() { return 0; }
+static constexpr int jac_full_knob() { return 0; }
 #endif
 
 // 0: launch geometry filled in; 1: the shape does not fit (use jacobian_kernel); < 0: error
@@ -494,7 +496,7 @@ static int plan_jacobian_block(const mtb_problem* pb, const mtb_modules* md, con
         prm.off_nbr = off;  off += tangents ? round_up(ring * prm.G * prm.MW, 4) : 0;
         prm.off_pool = off; off += pairs ? ring * prm.G * prm.NM1 * 8 : 0;
         prm.off_tan = off;  off += tangents ? prm.G * prm.T * 8 : 0;
-        prm.off_mud = off;  off += tangents ? 2 * prm.N * prm.T * 8 : 0;
+        prm.off_mud = off;  off += tangents ? prm.N * prm.T * 8 : 0;
         prm.ring = ring;
         return (size_t)off * sizeof(float);
     };
@@ -502,10 +504,13 @@ static int plan_jacobian_block(const mtb_problem* pb, const mtb_modules* md, con
     // two ring slots (the forward warps one full step ahead) unless the second slot costs a resident block per SM
     {
         const size_t one = layout(1), two = layout(2);
-        const int ring = (resident(two) < resident(one) || two > (size_t)lim.max_smem / 2 || jac_ring_knob() == 1) ? 1 : 2;
+        const int ring = (resident(two) < resident(one) || two > (size_t)lim.max_smem || jac_ring_knob() == 1) ? 1 : 2;
         smem = layout(ring);
     }
-    if (smem > (size_t)lim.max_smem / 2) return 1;                       // fewer than two resident blocks per SM: not this kernel's shape
+    // Even ONE resident block per SM beats the chunked kernel (measured on B200: SF N = 20, P = 3, T = 40, 1024 Jacobians of
+    // 962 x 80: 3.14 ms chunked, 1.18 ms here), so the only limit is the opt-in shared memory of a block.
+    const size_t smem_limit = jac_full_knob() == 2 ? (size_t)lim.max_smem / 2 : (size_t)lim.max_smem;
+    if (smem > smem_limit) return 1;                       // fewer than two resident blocks per SM: not this kernel's shape
     // threads: GR = round_up(G, 32) for the forward role + the tangent warps, whose work items are (particle, live control step):
     // G * t of them at step t, N * T row entries per level
     prm.GR = round_up(prm.G, 32);

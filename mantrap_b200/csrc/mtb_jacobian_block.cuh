@@ -103,7 +103,7 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
     unsigned* nbr = reinterpret_cast<unsigned*>(sm + prm.off_nbr);    // [2][G][MW] neighbour bits of the step      (ring)
     float4* pool = reinterpret_cast<float4*>(sm + prm.off_pool);      // [2][G][N-1][2]: d force / d r, d force / d w per executed pair (ring)
     float4* tang = reinterpret_cast<float4*>(sm + prm.off_tan);       // [G][T][2]: (px_dx, px_dy, py_dx, py_dy), (vx_dx, vx_dy, vy_dx, vy_dy)
-    float4* mud = reinterpret_cast<float4*>(sm + prm.off_mud);        // [2][N][T][2] tangents of the means, same packing
+    float4* mud = reinterpret_cast<float4*>(sm + prm.off_mud);        // [N][T][2] tangents of the means of the current level, same packing (updated in place)
     const int lin_slot = G * kLinRows, nbr_slot = G * MW, pool_slot = 2 * G * prm.NM1;
 
     const bool want_mind = prm.rows_mind > 0;
@@ -137,7 +137,7 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
         if (tangents) {
             const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
             for (int idx = tid; idx < 2 * G * T; idx += NT) tang[idx] = zero4;
-            for (int idx = tid; idx < 4 * N * T; idx += NT) mud[idx] = zero4;
+            for (int idx = tid; idx < 2 * N * T; idx += NT) mud[idx] = zero4;
         }
         __syncthreads();
         if (traj_given) {                                             // controls by inverse dynamics (roll_trajectory)
@@ -436,8 +436,10 @@ __global__ void __launch_bounds__(256, 3) jacobian_block_kernel(const BParams pr
             write_rows(0, mud);
             for (int t = 0; t < T - 1; ++t) {
                 const int slot = prm.ring == 2 ? (t & 1) : 0;
-                const float4* mud_t = mud + (t & 1) * 2 * N * T;
-                float4* mud_n = mud + ((t & 1) ^ 1) * 2 * N * T;
+                // one level of mean tangents, updated in place: the maps read level t before the first tangent barrier, the collapse
+                // rewrites each (k, j) row by the thread that read it, the rows read level t + 1 after the second barrier
+                const float4* mud_t = mud;
+                float4* mud_n = mud;
                 const bool live = tangents && t >= 1;
                 if (slot) mtb_bar_sync_id<kBarFull + 1>(NT); else mtb_bar_sync_id<kBarFull>(NT);                   // step t of the forward warps: maps in the slot, means of level t+1
                 // ------------------------------------------------ the maps applied to the live tangents (g, j < t)
