@@ -447,7 +447,7 @@ static int jac_env(const char* name) {
 }
 static int jac_knob() { return jac_env("MTB_JAC"); }        // development knob MTB_JAC: 1 = always jacobian_kernel
 static int jac_block_knob() { return jac_env("MTB_JAC_BLOCK"); }   // development knob: threads per block of jacobian_block_kernel
-static int jac_ring_knob() { return jac_env("MTB_JAC_RING"); }     // development knob: 1 = one ring slot
+static int jac_ring_knob() { return jac_env("MTB_JAC_RING"); }     // development knob: 1 = one ring slot, 2 = two slots even if that costs a resident block
 static int jac_full_knob() { return jac_env("MTB_JAC_FULL"); }     // development knob: 2 = only layouts that leave two blocks per SM
 #else
 static constexpr int jac_knob() { return 0; }
@@ -504,7 +504,7 @@ static int plan_jacobian_block(const mtb_problem* pb, const mtb_modules* md, con
     // two ring slots (the forward warps one full step ahead) unless the second slot costs a resident block per SM
     {
         const size_t one = layout(1), two = layout(2);
-        const int ring = (resident(two) < resident(one) || two > (size_t)lim.max_smem || jac_ring_knob() == 1) ? 1 : 2;
+        const int ring = jac_ring_knob() == 2 && two <= (size_t)lim.max_smem ? 2 : ((resident(two) < resident(one) || two > (size_t)lim.max_smem || jac_ring_knob() == 1) ? 1 : 2);
         smem = layout(ring);
     }
     // Even ONE resident block per SM beats the chunked kernel (measured on B200: SF N = 20, P = 3, T = 40, 1024 Jacobians of

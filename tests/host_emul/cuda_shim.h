@@ -107,6 +107,7 @@ static inline unsigned __ballot_sync(unsigned, int pred) {
     w.bar.arrive_and_wait();
     return r;
 }
+static inline int __any_sync(unsigned mask, int pred) { return __ballot_sync(mask, pred) != 0u; }
 
 static inline float atomicAdd(float* addr, float val) {
     uint32_t* a = reinterpret_cast<uint32_t*>(addr);
