@@ -541,10 +541,16 @@ static int launch_jacobian_block(const BParams& prm, int block, size_t smem, cud
     if (per_sm < 1) per_sm = 1;
 #ifndef MTB_HOST_EMUL
     {
+        // (function attributes and occupancy are per device: cached per device of the calling thread)
+        constexpr int kMaxDevices = 64;
         static std::mutex mu;
-        static int smem_opt_in = 0;
-        static std::map<std::pair<int, size_t>, int> resident;
+        static int smem_opt_in_dev[kMaxDevices] = {};
+        static std::map<std::pair<int, size_t>, int> resident_dev[kMaxDevices];
+        int device = 0;
+        if (cudaGetDevice(&device) != cudaSuccess || device < 0 || device >= kMaxDevices) { (void)cudaGetLastError(); device = 0; }
         std::lock_guard<std::mutex> lock(mu);
+        int& smem_opt_in = smem_opt_in_dev[device];
+        std::map<std::pair<int, size_t>, int>& resident = resident_dev[device];
         if ((int)smem > smem_opt_in) {
             const cudaError_t err = cudaFuncSetAttribute(jacobian_block_kernel<ENV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
             if (err != cudaSuccess) return (int)err;
