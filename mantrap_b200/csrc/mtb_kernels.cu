@@ -187,8 +187,9 @@ MTB_DEV float4 objective_seed(const KParams& prm, const float* misc, const float
     return sd;
 }
 
-// MAXT / MINB: register budget of the instantiation (__launch_bounds__). Blocks of <= 256 threads come in two
-// flavours: MINB = 3 (<= 80 registers) when shared memory allows three or more resident blocks per SM, else MINB = 2.
+// MAXT / MINB: register budget of the instantiation (__launch_bounds__). Blocks of <= 256 threads come in three
+// flavours: MINB = 4 (<= 64 registers), 3 (<= 80) and 2 (<= 128); pick_variant() chooses by the number of blocks shared memory
+// admits and the group size.
 template <int ENV, bool GRAD, int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB) evaluate_kernel(const KParams prm) {
     MTB_SHARED_FLOAT4(smem4);
@@ -939,7 +940,7 @@ static constexpr int env_flag(const char*) { return 0; }
 struct Variant {
     int maxt, minb;
 };
-static Variant pick_variant(int block, int blocks_by_smem, int evals_per_thread) {
+static Variant pick_variant(int block, int blocks_by_smem, int evals_per_thread, int group, bool variance_modules, bool social_forces) {
     if (block > kDefaultBlock) return {kMaxThreads, 1};
     if (evals_per_thread == 2) {                              // pair kernel: 128 registers, two blocks of <= 256 threads
 #ifdef MTB_DEV_KNOBS
@@ -947,9 +948,24 @@ static Variant pick_variant(int block, int blocks_by_smem, int evals_per_thread)
 #endif
         return {kDefaultBlock, 2};
     }
+    // evaluate_kernel<SOCIAL_FORCES>, measured on the 64 sweep shapes it runs (B200, `profiles/r02zz_sweep_minb*.csv`):
+    //  * shared memory admits >= 4 blocks: the 64-register variant (4 x 256 threads) beats the 80-register one on all 25 such
+    //    shapes, by 3 - 10 %;
+    //  * it admits 3 and a group has <= 8 threads: the 128-register variant (2 x 256 threads, no spills) wins by 2 - 6 % -- these
+    //    tiny groups keep many evaluations per warp, the spills of the 80-register variant cost more than the third block buys;
+    //  * otherwise 80 registers for 3 blocks, 128 registers when shared memory admits only 1 - 2.
     const int force = env_flag("MTB_MINB");
     if (force == 4) return {kDefaultBlock, 4};
-    if (force == 3 || (force == 0 && blocks_by_smem >= 3)) return {kDefaultBlock, 3};
+    if (force == 3) return {kDefaultBlock, 3};
+    if (force == 2) return {kDefaultBlock, 2};
+    // The variance-based modules (interaction probability, ellipsoid rows) divide by variances of order 1e-3: their values move
+    // by ~1e-4 relative with the FMA contraction pattern ptxas picks under another register budget (sf_prob_n4_t6: 2.4e-4 with 64
+    // registers against a float32 conditioning floor of 4e-5), so they keep the variants their goldens were pinned on.
+    // The potential field (no pair loops, measured only on the config-2 shape: 9.4e7 -> 8.7e7 evals/s with 64 registers) and
+    // Kalman keep them too.
+    if (variance_modules || !social_forces) return blocks_by_smem >= 3 ? Variant{kDefaultBlock, 3} : Variant{kDefaultBlock, 2};
+    if (blocks_by_smem >= 4) return {kDefaultBlock, 4};
+    if (blocks_by_smem == 3) return group <= 8 ? Variant{kDefaultBlock, 2} : Variant{kDefaultBlock, 3};
     return {kDefaultBlock, 2};
 }
 // launch + residency query of one instantiation (filled in below the kernel)
@@ -1159,7 +1175,7 @@ static int plan(const mtb_problem* pb, const mtb_modules* md, const mtb_outputs*
     // The grid is persistent: exactly one resident wave. Shared memory alone over-estimates the residency of the
     // register-limited instantiations (80 registers x 256 threads: 3 blocks, not the 7 shared memory would admit), which
     // left a ragged third wave; ask the runtime for the instantiation that will be launched (cached per geometry).
-    const Variant variant = pick_variant(block, blocks_per_sm, EV);
+    const Variant variant = pick_variant(block, blocks_per_sm, EV, prm.GP, prm.keep_var != 0, pb->env_kind == MTB_ENV_SOCIAL_FORCES);
     info.variant_maxt = variant.maxt;
     info.variant_minb = variant.minb;
     {
@@ -1269,9 +1285,7 @@ struct Inst {
 template <int ENV, bool GRAD>
 static const InstOps* select_variant(Variant v) {
     if (v.maxt > kDefaultBlock) return Inst<ENV, GRAD, kMaxThreads, 1>::ops();
-#ifdef MTB_DEV_KNOBS
     if (v.minb == 4) return Inst<ENV, GRAD, kDefaultBlock, 4>::ops();
-#endif
     if (v.minb == 3) return Inst<ENV, GRAD, kDefaultBlock, 3>::ops();
     return Inst<ENV, GRAD, kDefaultBlock, 2>::ops();
 }
